@@ -1,0 +1,101 @@
+"""Hot ops.  CUDA tensors run the hand-written sm_100a kernels in `csrc/` (loaded through the
+C ABI declared in `include/distriflow_b200.h`); CPU tensors run a plain PyTorch restatement,
+which is also the numerics oracle of the kernel tests.
+
+There is no silent fallback on a GPU: if a tensor is on CUDA and the native library is
+missing or a shape is unsupported by every kernel, the op raises.
+
+Reference call sites replaced: K1 Dense forward, K2 Conv2D / MaxPool forward,
+K3 loss, K4 backward, K11 metrics — all of which the reference delegates to tf.js
+(`/root/reference/src/common/models.ts:137-142`).
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+import torch.nn.functional as F
+
+__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "softmax_cross_entropy", "native_available",
+           "same_padding"]
+
+
+def native_available() -> bool:
+    from . import _lib
+    return _lib.available()
+
+
+def _act_cpu(y: torch.Tensor, activation: Optional[str]) -> torch.Tensor:
+    if activation is None:
+        return y
+    if activation == "relu":
+        return F.relu(y)
+    if activation == "gelu":
+        return F.gelu(y, approximate="tanh")
+    raise ValueError(f"unsupported fused activation {activation}")
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
+           activation: Optional[str] = None) -> torch.Tensor:
+    """`act(x @ weight + bias)` with `weight` in tf.js layout `[in, out]`."""
+    if x.is_cuda:
+        from .linear import linear_cuda
+        return linear_cuda(x, weight, bias, activation)
+    y = x @ weight.to(x.dtype)
+    if bias is not None:
+        y = y + bias.to(y.dtype)
+    return _act_cpu(y, activation)
+
+
+def same_padding(size: int, k: int, s: int) -> Tuple[int, int]:
+    """TensorFlow 'same' padding (begin, end) along one axis."""
+    out = -(-size // s)
+    total = max((out - 1) * s + k - size, 0)
+    return total // 2, total - total // 2
+
+
+def conv2d_nhwc(x: torch.Tensor, kernel: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                strides: Sequence[int] = (1, 1), padding: str = "valid",
+                activation: Optional[str] = None) -> torch.Tensor:
+    """NHWC input, HWIO filter, NHWC output."""
+    if x.is_cuda:
+        from .conv import conv2d_cuda
+        return conv2d_cuda(x, kernel, bias, tuple(strides), padding, activation)
+    kh, kw = kernel.shape[0], kernel.shape[1]
+    xc = x.permute(0, 3, 1, 2)
+    if padding == "same":
+        pt, pb = same_padding(x.shape[1], kh, strides[0])
+        pl, pr = same_padding(x.shape[2], kw, strides[1])
+        xc = F.pad(xc, (pl, pr, pt, pb))
+    elif padding != "valid":
+        raise ValueError(f"padding {padding}")
+    y = F.conv2d(xc, kernel.permute(3, 2, 0, 1).to(x.dtype), None if bias is None else bias.to(x.dtype),
+                 stride=tuple(strides))
+    return _act_cpu(y.permute(0, 2, 3, 1).contiguous(), activation)
+
+
+def maxpool2d_nhwc(x: torch.Tensor, pool: Sequence[int] = (2, 2), strides: Optional[Sequence[int]] = None,
+                   padding: str = "valid") -> torch.Tensor:
+    strides = tuple(strides or pool)
+    if x.is_cuda:
+        from .conv import maxpool2d_cuda
+        return maxpool2d_cuda(x, tuple(pool), strides, padding)
+    xc = x.permute(0, 3, 1, 2)
+    if padding == "same":
+        pt, pb = same_padding(x.shape[1], pool[0], strides[0])
+        pl, pr = same_padding(x.shape[2], pool[1], strides[1])
+        xc = F.pad(xc, (pl, pr, pt, pb), value=float("-inf"))
+    y = F.max_pool2d(xc, tuple(pool), strides)
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+def layer_norm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5) -> torch.Tensor:
+    if x.is_cuda:
+        from .norm import layer_norm_cuda
+        return layer_norm_cuda(x, gamma, beta, eps)
+    return F.layer_norm(x.float(), (x.shape[-1],), gamma.float(), beta.float(), eps).to(x.dtype)
+
+
+def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    from .softmax_ce import softmax_cross_entropy as f
+    return f(logits, labels)

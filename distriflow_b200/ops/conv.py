@@ -1,0 +1,183 @@
+"""NHWC Conv2D / MaxPool on CUDA through the hand-written implicit-GEMM kernels.
+
+Filters are HWIO and activations NHWC, as tf.js stores them, so checkpoints of
+`/root/reference/experiment/mnist/model.json` map without a transpose.  bf16 with channel counts that are
+multiples of 16 takes the tcgen05 implicit-GEMM kernel (`csrc/conv_sm100.cu`, TMA gathers the shifted NHWC
+slab of every filter tap); the rest takes the CUDA-core implicit GEMM (`csrc/conv_simt.cu`).
+Replaces K2/K4 of SURVEY §2.5.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import c_int, c_void_p, check, dt, ptr, stream
+from .linear import ACT, colsum
+
+
+def _sigs():
+    L = _lib.lib()
+    if not getattr(L, "_dfb_conv_sigs", False):
+        L.dfb_conv2d_simt.restype = c_int
+        L.dfb_conv2d_simt.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p]
+        L.dfb_maxpool_nhwc.restype = c_int
+        L.dfb_maxpool_nhwc.argtypes = [c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
+        L.dfb_maxpool_nhwc_bwd.restype = c_int
+        L.dfb_maxpool_nhwc_bwd.argtypes = [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
+        if hasattr(L, "dfb_conv2d_tc"):
+            L.dfb_conv2d_tc.restype = c_int
+            L.dfb_conv2d_tc.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p, ctypes.c_size_t, c_void_p]
+        L._dfb_conv_sigs = True
+    return L
+
+
+def _geometry(H: int, W: int, kh: int, kw: int, strides: Tuple[int, int], padding: str):
+    from . import same_padding
+    sh, sw = strides
+    if padding == "same":
+        pt, _ = same_padding(H, kh, sh)
+        pl, _ = same_padding(W, kw, sw)
+        OH, OW = -(-H // sh), -(-W // sw)
+    elif padding == "valid":
+        pt = pl = 0
+        OH, OW = (H - kh) // sh + 1, (W - kw) // sw + 1
+    else:
+        raise ValueError(f"padding {padding}")
+    return OH, OW, pt, pl
+
+
+def _tc_eligible(x: torch.Tensor, C: int, K: int) -> bool:
+    L = _lib.lib()
+    return hasattr(L, "dfb_conv2d_tc") and x.dtype == torch.bfloat16 and C % 16 == 0 and K % 16 == 0
+
+
+def _conv_call(mode: int, a, b, out, bias, geom, act, ksplit=1):
+    L = _sigs()
+    (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
+    check(L.dfb_conv2d_simt(mode, ptr(a), ptr(b), ptr(out), ptr(bias), dt(bias) if bias is not None else 0,
+                            N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl, dt(a), 1 if out.dtype == torch.float32 else 0,
+                            ACT[act], ksplit, stream()), "dfb_conv2d_simt")
+    return out
+
+
+def _conv_tc(mode: int, a, b, out, bias, geom, act):
+    L = _sigs()
+    (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
+    ws_bytes = int(L.dfb_conv2d_tc_workspace_bytes(mode, N, H, W, C, OH, OW, K, kh, kw)) if hasattr(L, "dfb_conv2d_tc_workspace_bytes") else 0
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=a.device) if ws_bytes else None
+    rc = L.dfb_conv2d_tc(mode, ptr(a), ptr(b), ptr(out), ptr(bias), dt(bias) if bias is not None else 0,
+                         N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl, dt(a), 1 if out.dtype == torch.float32 else 0,
+                         ACT[act], 0, ptr(ws), ctypes.c_size_t(ws_bytes), stream())
+    return rc
+
+
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, kernel, bias, strides, padding, activation):
+        x = x.contiguous()
+        N, H, W, C = x.shape
+        kh, kw, C2, K = kernel.shape
+        assert C == C2, f"input has {C} channels, filter expects {C2}"
+        OH, OW, pt, pl = _geometry(H, W, kh, kw, strides, padding)
+        geom = (N, H, W, C, OH, OW, K, kh, kw, strides[0], strides[1], pt, pl)
+        w = kernel if kernel.dtype == x.dtype else kernel.to(x.dtype)
+        w = w.contiguous()
+        y = torch.empty((N, OH, OW, K), device=x.device, dtype=x.dtype)
+        done = False
+        if _tc_eligible(x, C, K):
+            done = _conv_tc(0, x, w, y, bias, geom, activation) == 0
+        if not done:
+            _conv_call(0, x, w, y, bias, geom, activation)
+        ctx.geom, ctx.activation = geom, activation
+        ctx.kernel_ref, ctx.bias_ref = kernel, bias
+        ctx.save_for_backward(x, w, y if activation == "relu" else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .linear import act_op
+        x, w, y = ctx.saved_tensors
+        geom = ctx.geom
+        (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
+        dy = dy.contiguous()
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        if ctx.activation == "relu":
+            dy = act_op(dy, y, 2)
+        dx = dw = db = None
+        kernel, bias = ctx.kernel_ref, ctx.bias_ref
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            done = False
+            if _tc_eligible(x, C, K):
+                done = _conv_tc(1, dy, w, dx, None, geom, None) == 0
+            if not done:
+                _conv_call(1, dy, w, dx, None, geom, None)
+        if ctx.needs_input_grad[1]:
+            pixels = N * OH * OW
+            tiles = (-(-(kh * kw * C) // 64)) * (-(-K // 64))
+            ksplit = max(1, min(64, (148 * 4) // max(tiles, 1), pixels // 256))
+            dw32 = torch.empty((kh, kw, C, K), device=x.device, dtype=torch.float32)
+            done = False
+            if _tc_eligible(x, C, K):
+                done = _conv_tc(2, x, dy, dw32, None, geom, None) == 0
+            if not done:
+                _conv_call(2, x, dy, dw32, None, geom, None, ksplit)
+            sink = getattr(kernel, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.view(kh, kw, C, K).copy_(dw32)
+                kernel._dfb_grad_ready()
+            else:
+                dw = dw32.to(kernel.dtype)
+        if bias is not None and ctx.needs_input_grad[2]:
+            db = colsum(dy.reshape(-1, K))
+            sink = getattr(bias, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.copy_(db)
+                bias._dfb_grad_ready()
+                db = None
+            else:
+                db = db.to(bias.dtype)
+        return dx, dw, db, None, None, None
+
+
+def conv2d_cuda(x, kernel, bias, strides, padding, activation):
+    return _Conv2dFn.apply(x, kernel, bias, tuple(strides), padding, activation)
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, pool, strides, padding):
+        L = _sigs()
+        x = x.contiguous()
+        N, H, W, C = x.shape
+        OH, OW, pt, pl = _geometry(H, W, pool[0], pool[1], strides, padding)
+        y = torch.empty((N, OH, OW, C), device=x.device, dtype=x.dtype)
+        check(L.dfb_maxpool_nhwc(ptr(x), ptr(y), N, H, W, C, OH, OW, pool[0], pool[1], strides[0], strides[1], pt, pl, dt(x),
+                                 stream()), "dfb_maxpool_nhwc")
+        ctx.args = (N, H, W, C, OH, OW, pool[0], pool[1], strides[0], strides[1], pt, pl)
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _sigs()
+        (x,) = ctx.saved_tensors
+        N, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl = ctx.args
+        dy = dy.contiguous()
+        overlap = sh < kh or sw < kw
+        if overlap and x.dtype != torch.float32:
+            x32, dy32 = x.float(), dy.float()
+            dx = torch.empty_like(x32)
+            check(L.dfb_maxpool_nhwc_bwd(ptr(x32), ptr(dy32), ptr(dx), *ctx.args, 0, stream()), "dfb_maxpool_nhwc_bwd")
+            return dx.to(x.dtype), None, None, None
+        dx = torch.empty_like(x)
+        check(L.dfb_maxpool_nhwc_bwd(ptr(x), ptr(dy), ptr(dx), *ctx.args, dt(x), stream()), "dfb_maxpool_nhwc_bwd")
+        return dx, None, None, None
+
+
+def maxpool2d_cuda(x, pool, strides, padding):
+    return _MaxPoolFn.apply(x, tuple(pool), tuple(strides), padding)

@@ -1,0 +1,461 @@
+// Dense GEMM for sm_100a: persistent, warp-specialised, TMA -> shared memory -> tcgen05.mma with the
+// accumulator in TMEM, epilogue TMEM -> registers -> swizzled shared memory -> TMA store.
+//
+//   D[M,N] = act(A[M,K] * B[N,K]^T + bias[N])          bf16 inputs, fp32 accumulate, bf16 or fp32 output
+//
+// Either operand may be K-major (contraction index contiguous) or MN-major (row index contiguous), which
+// covers the three products of a Dense layer whose kernel is stored `[in, out]` as in tf.js:
+//   forward  Y  = X  * W      : A = X  (K-major),  B = W  (MN-major)
+//   dgrad    dX = dY * W^T    : A = dY (K-major),  B = W  (K-major)
+//   wgrad    dW = X^T * dY    : A = X  (MN-major), B = dY (MN-major), long K -> split-K
+// Reference call sites this replaces: `predictOnBatch` / `tf.variableGrads` on the Dense layers of
+// /root/reference/src/common/models.ts:137-142.
+//
+// Roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator + MMA issuer
+// (one elected lane), warps 2..5 = epilogue (warp w reads TMEM lanes 32*(w%4)..+31).
+// Pipelines: smem ring full/empty (TMA <-> MMA), TMEM double buffer full/empty (MMA <-> epilogue).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace dfb {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;                 // 64 bf16 = 128 B = one SWIZZLE_128B row
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 192;
+constexpr int kEpiThreads = 128;
+constexpr int kATileBytes = kBlockM * kBlockK * 2;      // 16 KiB
+constexpr int kStageOutBytes = 128 * 128;               // 128 rows x 128 B staging for the TMA store
+constexpr int kAtomBytes = kBlockK * 128;               // one 64(MN) x 64(K) MN-major box = 8 KiB
+
+template <int BLOCK_N>
+struct GemmCfg {
+  static constexpr int kBTileBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kStages = (BLOCK_N == 256) ? 4 : 6;
+  static constexpr int kTmemCols = 2 * BLOCK_N;         // double-buffered fp32 accumulator
+  static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kStageOutBytes + BLOCK_N * 4 + 256 + 1024;
+};
+
+struct GemmParams {
+  const void* bias;     // nullptr, fp32[N] or bf16[N]
+  int bias_dtype;
+  int M, N, K;
+  int a_mn, b_mn;       // 1 = MN-major operand
+  int act;
+  int splits;           // split-K factor (1 = none)
+  int kb_per_split;     // k-blocks per split
+  int split_rows;       // row offset between splits in the fp32 workspace (multiple of 128)
+};
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * x * (1.0f + t);
+}
+
+template <int BLOCK_N, typename OutT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+  using Cfg = GemmCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kChunkN = 128 / (int)sizeof(OutT);       // columns per 128-byte staging row
+  constexpr int kChunks = BLOCK_N / kChunkN;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kATileBytes;
+  uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
+  float* smem_bias = reinterpret_cast<float*>(smem_out + 2 * kStageOutBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_bias + BLOCK_N);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp_idx = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_blocks = ceil_div(p.M, kBlockM);
+  const int n_blocks = ceil_div(p.N, BLOCK_N);
+  const int kb_total = ceil_div(p.K, kBlockK);
+  const int tiles_mn = m_blocks * n_blocks;
+  const int num_tiles = tiles_mn * p.splits;
+
+  if (warp_idx == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmD);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);     // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp_idx == 1) tmem_alloc<Cfg::kTmemCols>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  // tile -> (m_blk, n_blk, split): groups of 8 m-blocks sweep n, so concurrently resident CTAs share A and B tiles in L2
+  auto decode_tile = [&](int tile, int& m_blk, int& n_blk, int& split) {
+    split = tile / tiles_mn;
+    int t = tile - split * tiles_mn;
+    const int group = 8 * n_blocks;
+    int g = t / group;
+    int first_m = g * 8;
+    int gsz = min(8, m_blocks - first_m);
+    int r = t - g * group;
+    m_blk = first_m + r % gsz;
+    n_blk = r / gsz;
+  };
+
+  if (warp_idx == 0) {
+    // ===================================================================== TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int m_blk, n_blk, split;
+        decode_tile(tile, m_blk, n_blk, split);
+        const int m0 = m_blk * kBlockM, n0 = n_blk * BLOCK_N;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          uint8_t* sa = smem_a + stage * kATileBytes;
+          uint8_t* sb = smem_b + stage * Cfg::kBTileBytes;
+          const int k0 = kb * kBlockK;
+          if (p.a_mn) {
+#pragma unroll
+            for (int i = 0; i < kBlockM / 64; ++i) tma_load_2d(sa + i * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * i, k0);
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          }
+          if (p.b_mn) {
+#pragma unroll
+            for (int i = 0; i < BLOCK_N / 64; ++i) tma_load_2d(sb + i * kAtomBytes, &tmB, &full_bar[stage], n0 + 64 * i, k0);
+          } else {
+            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp_idx == 1) {
+    // ===================================================================== MMA issuer
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(kBlockM, BLOCK_N, (uint32_t)p.a_mn, (uint32_t)p.b_mn);
+      // K-major SW128: 8-row groups 1024 B apart, one 128 B swizzle row per matrix row, k-step = 32 B.
+      // MN-major SW128: 64-element MN atoms kAtomBytes apart (LBO), 8-k-row groups 1024 B apart (SBO), k-step = 16 rows.
+      const uint32_t a_lbo = p.a_mn ? kAtomBytes : 0, b_lbo = p.b_mn ? kAtomBytes : 0;
+      const uint32_t a_kstep = p.a_mn ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+      const uint32_t b_kstep = p.b_mn ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int m_blk, n_blk, split;
+        decode_tile(tile, m_blk, n_blk, split);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, kb_total);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t a_desc = make_smem_desc_sw128(smem_u32(smem_a + stage * kATileBytes), a_lbo, 1024);
+          const uint64_t b_desc = make_smem_desc_sw128(smem_u32(smem_b + stage * Cfg::kBTileBytes), b_lbo, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            umma_f16(tmem_d, a_desc + (uint64_t)(k * a_kstep), b_desc + (uint64_t)(k * b_kstep), idesc,
+                     (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);            // frees the smem slot once these MMAs have read it
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[acc]);                // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================================================================== epilogue (warps 2..5)
+    const int quarter = warp_idx & 3;                 // TMEM lane quarter this warp may read
+    const int row = quarter * 32 + lane;              // row inside the 128-row tile
+    const int epi_tid = threadIdx.x - 64;
+    const bool issuer = (epi_tid == 0);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t out_iter = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk, split;
+      decode_tile(tile, m_blk, n_blk, split);
+      const int m0 = m_blk * kBlockM, n0 = n_blk * BLOCK_N;
+      const int out_row0 = m0 + split * p.split_rows;
+      if (p.bias != nullptr) {
+        for (int i = epi_tid; i < BLOCK_N; i += kEpiThreads) {
+          int n = n0 + i;
+          float b = 0.f;
+          if (n < p.N)
+            b = p.bias_dtype == DT_F32 ? reinterpret_cast<const float*>(p.bias)[n]
+                                       : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n]);
+          smem_bias[i] = b;
+        }
+      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c) {
+        float v[kChunkN];
+        {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c * kChunkN, r);
+          if constexpr (kChunkN == 64) {
+            uint32_t r2[32];
+            tmem_ld_32x32(taddr + c * kChunkN + 32, r2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[32 + j] = __uint_as_float(r2[j]);
+          } else {
+            tmem_ld_wait();
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        }
+        if (c == kChunks - 1) {                        // whole accumulator is in registers: release TMEM early
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        }
+        uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
+        if (issuer) tma_store_wait_read<1>();          // the store that last used this buffer has drained
+        named_bar_sync(1, kEpiThreads);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < kChunkN; ++j) v[j] += smem_bias[c * kChunkN + j];
+        }
+        if (p.act == ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < kChunkN; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (p.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < kChunkN; ++j) v[j] = gelu_tanh(v[j]);
+        }
+        uint8_t* row_ptr = stage_out + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {                  // eight 16-byte pieces per row, XOR-swizzled like SWIZZLE_128B
+          uint4 q;
+          if constexpr (sizeof(OutT) == 2) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j + 0], v[8 * j + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+            q.x = *reinterpret_cast<uint32_t*>(&h0);
+            q.y = *reinterpret_cast<uint32_t*>(&h1);
+            q.z = *reinterpret_cast<uint32_t*>(&h2);
+            q.w = *reinterpret_cast<uint32_t*>(&h3);
+          } else {
+            q.x = __float_as_uint(v[4 * j + 0]);
+            q.y = __float_as_uint(v[4 * j + 1]);
+            q.z = __float_as_uint(v[4 * j + 2]);
+            q.w = __float_as_uint(v[4 * j + 3]);
+          }
+          *reinterpret_cast<uint4*>(row_ptr + ((j ^ (row & 7)) << 4)) = q;
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, kEpiThreads);
+        if (issuer) {
+          tma_store_2d(&tmD, stage_out, n0 + c * kChunkN, out_row0);
+          tma_store_commit();
+        }
+        ++out_iter;
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (issuer) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp_idx == 1) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// out[m, n] = act(sum_s ws[s*split_rows + m, n] + bias[n]); ws fp32 with row pitch ldw.
+template <typename OutT>
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, OutT* __restrict__ out, const void* __restrict__ bias,
+                                     int bias_dtype, int M, int N, int ldw, int ldd, int splits, int split_rows, int act) {
+  const int n4 = N >> 2;
+  const long total = (long)M * n4;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int m = (int)(i / n4), n = (int)(i - (long)m * n4) << 2;
+    float4 acc = *reinterpret_cast<const float4*>(ws + (size_t)m * ldw + n);
+    for (int s = 1; s < splits; ++s) {
+      float4 t = *reinterpret_cast<const float4*>(ws + ((size_t)s * split_rows + m) * ldw + n);
+      acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+    }
+    float v[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (bias != nullptr)
+        v[j] += bias_dtype == DT_F32 ? reinterpret_cast<const float*>(bias)[n + j]
+                                     : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(bias)[n + j]);
+      if (act == ACT_RELU) v[j] = fmaxf(v[j], 0.f);
+      else if (act == ACT_GELU) v[j] = gelu_tanh(v[j]);
+    }
+    if constexpr (sizeof(OutT) == 2) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+      uint2 q = {*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1)};
+      *reinterpret_cast<uint2*>(out + (size_t)m * ldd + n) = q;
+    } else {
+      *reinterpret_cast<float4*>(out + (size_t)m * ldd + n) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+  }
+}
+
+template <int BLOCK_N, typename OutT>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const GemmParams& p,
+                       int max_ctas, cudaStream_t stream) {
+  using Cfg = GemmCfg<BLOCK_N>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, OutT>;
+  static bool configured = false;      // per instantiation; attribute is per device function (all devices of one kind)
+  if (!configured) {
+    DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int tiles = ceil_div(p.M, kBlockM) * ceil_div(p.N, BLOCK_N) * p.splits;
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  kern<<<grid, kThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmD, p);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+static int make_operand_map(CUtensorMap* tm, const void* ptr, int rows, int K, int ld, int mn_major, int block_rows) {
+  if (mn_major) {       // memory [K][rows]: inner = rows
+    uint64_t dims[2] = {(uint64_t)rows, (uint64_t)K};
+    uint64_t str[1] = {(uint64_t)ld * 2};
+    uint32_t box[2] = {64, (uint32_t)kBlockK};
+    return encode_tmap(tm, ptr, 0, 2, dims, str, box, nullptr, 1);
+  }
+  uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+  uint64_t str[1] = {(uint64_t)ld * 2};
+  uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)block_rows};
+  return encode_tmap(tm, ptr, 0, 2, dims, str, box, nullptr, 1);
+}
+
+}  // namespace dfb
+
+using namespace dfb;
+
+// Bytes of fp32 scratch dfb_gemm_bf16 needs for a given problem and split factor (0 when splits <= 1).
+DFB_API size_t dfb_gemm_workspace_bytes(int M, int N, int splits) {
+  if (splits <= 1) return 0;
+  size_t mpad = (size_t)ceil_div(M, kBlockM) * kBlockM;
+  return (size_t)splits * mpad * (size_t)N * sizeof(float);
+}
+
+// Heuristic split-K factor: fill the SMs when the MN tile count is small and K is long.
+DFB_API int dfb_gemm_pick_splits(int M, int N, int K, int block_n, int sms) {
+  int tiles = ceil_div(M, kBlockM) * ceil_div(N, block_n);
+  int kb = ceil_div(K, kBlockK);
+  if (tiles * 2 > sms || kb < 16) return 1;
+  int s = sms / tiles;
+  if (s > kb / 8) s = kb / 8;
+  if (s > 16) s = 16;
+  return s < 1 ? 1 : s;
+}
+
+// See include/distriflow_b200.h.  `workspace` (fp32 scratch) is required iff splits > 1.
+DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K,
+                          int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n,
+                          int splits, void* workspace, size_t workspace_bytes, int max_ctas, cudaStream_t stream) {
+  DFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d x %d x %d", M, N, K);
+  DFB_REQUIRE(block_n == 128 || block_n == 256, "gemm: block_n must be 128 or 256");
+  DFB_REQUIRE(out_dtype == DT_BF16 || out_dtype == DT_F32, "gemm: out dtype");
+  DFB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16-byte pitch)");
+  DFB_REQUIRE((ldd * (out_dtype == DT_BF16 ? 2 : 4)) % 16 == 0, "gemm: output pitch must be a multiple of 16 bytes");
+  DFB_REQUIRE(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0 && ((uintptr_t)D % 16) == 0, "gemm: 16-byte alignment");
+  const int kb_total = ceil_div(K, kBlockK);
+  if (splits < 1) splits = 1;
+  if (splits > kb_total) splits = kb_total;
+  int kb_per = ceil_div(kb_total, splits);
+  splits = ceil_div(kb_total, kb_per);
+
+  GemmParams p;
+  p.bias = bias; p.bias_dtype = bias_dtype; p.M = M; p.N = N; p.K = K; p.a_mn = a_mn_major ? 1 : 0; p.b_mn = b_mn_major ? 1 : 0;
+  p.act = act; p.splits = splits; p.kb_per_split = kb_per; p.split_rows = 0;
+
+  CUtensorMap tmA, tmB, tmD;
+  if (make_operand_map(&tmA, A, M, K, lda, p.a_mn, kBlockM)) return 4;
+  if (make_operand_map(&tmB, B, N, K, ldb, p.b_mn, block_n)) return 4;
+
+  if (splits > 1) {
+    DFB_REQUIRE((N % 4) == 0, "gemm split-K: N must be a multiple of 4");
+    const size_t need = dfb_gemm_workspace_bytes(M, N, splits);
+    DFB_REQUIRE(workspace != nullptr && workspace_bytes >= need, "gemm split-K: workspace of %zu bytes required, got %zu",
+                need, workspace_bytes);
+    const int mpad = ceil_div(M, kBlockM) * kBlockM;
+    p.split_rows = mpad;
+    GemmParams pk = p;
+    pk.bias = nullptr; pk.act = ACT_NONE;
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)splits * mpad};
+    uint64_t str[1] = {(uint64_t)N * 4};
+    uint32_t box[2] = {32, 128};
+    if (encode_tmap(&tmD, workspace, 1, 2, dims, str, box, nullptr, 1)) return 4;
+    int rc = block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, pk, max_ctas, stream)
+                            : launch_gemm<128, float>(tmA, tmB, tmD, pk, max_ctas, stream);
+    if (rc) return rc;
+    const long total = (long)M * (N / 4);
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+    if (out_dtype == DT_BF16)
+      splitk_reduce_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>((const float*)workspace, (__nv_bfloat16*)D, bias,
+                                                                      bias_dtype, M, N, N, ldd, splits, mpad, act);
+    else
+      splitk_reduce_kernel<float><<<blocks, 256, 0, stream>>>((const float*)workspace, (float*)D, bias, bias_dtype, M, N, N,
+                                                              ldd, splits, mpad, act);
+    DFB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
+
+  {
+    const int esz = out_dtype == DT_BF16 ? 2 : 4;
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)ldd * esz};
+    uint32_t box[2] = {(uint32_t)(128 / esz), 128};
+    if (encode_tmap(&tmD, D, out_dtype == DT_BF16 ? 0 : 1, 2, dims, str, box, nullptr, 1)) return 4;
+  }
+  if (out_dtype == DT_BF16)
+    return block_n == 256 ? launch_gemm<256, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream)
+                          : launch_gemm<128, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream);
+  return block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, p, max_ctas, stream)
+                        : launch_gemm<128, float>(tmA, tmB, tmD, p, max_ctas, stream);
+}

@@ -1,0 +1,191 @@
+"""Dense layer on CUDA: forward, dgrad and wgrad through the hand-written GEMMs.
+
+`weight` is `[in, out]` (tf.js Dense kernel layout), so no transpose is materialised:
+the three products differ only in which operand is MN-major (see `csrc/gemm_sm100.cu`).
+bf16 with 16-byte-aligned pitches runs the tcgen05/TMEM/TMA kernel; everything else (fp32 MNIST models,
+N = 10 / N = 5 heads) runs the CUDA-core kernel.  Replaces K1/K4 of SURVEY §2.5
+(`/root/reference/src/common/models.ts:137-142`).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import c_int, c_size_t, c_void_p, check, dt, ptr, stream
+
+ACT = {None: 0, "relu": 1, "gelu": 2}
+NUM_SMS = 148
+_MAX_CTAS = 0            # 0 = all SMs; the engine lowers this while a comm kernel needs SMs
+
+
+def set_max_ctas(n: int) -> None:
+    global _MAX_CTAS
+    _MAX_CTAS = int(n)
+
+
+def _tc_ok(*mats: torch.Tensor) -> bool:
+    for t in mats:
+        if t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1 or t.stride(0) % 8 != 0 or t.data_ptr() % 16 != 0:
+            return False
+    return True
+
+
+def pick_tile(M: int, N: int, K: int) -> Tuple[int, int]:
+    mb = -(-M // 128)
+    t256 = mb * -(-N // 256)
+    bn = 256 if (t256 >= NUM_SMS and N >= 256) else 128
+    splits = _lib.lib().dfb_gemm_pick_splits(M, N, K, bn, NUM_SMS)
+    return bn, int(splits)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int, N: int, K: int,
+         bias: Optional[torch.Tensor] = None, act: Optional[str] = None, out: Optional[torch.Tensor] = None,
+         out_dtype: Optional[torch.dtype] = None, block_n: Optional[int] = None, splits: Optional[int] = None) -> torch.Tensor:
+    """D[M,N] = act(A·Bᵀ + bias).  A is `[M,K]` memory if not a_mn else `[K,M]`; B is `[N,K]` if not b_mn else `[K,N]`."""
+    L = _lib.lib()
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=out_dtype or a.dtype)
+    assert out.stride(1) == 1
+    use_tc = _tc_ok(a, b) and out.dtype in (torch.bfloat16, torch.float32) and \
+        (out.stride(0) * out.element_size()) % 16 == 0 and out.data_ptr() % 16 == 0 and N >= 16
+    if bias is not None and bias.dtype not in (torch.float32, torch.bfloat16):
+        bias = bias.float()
+    if use_tc:
+        bn, sp = pick_tile(M, N, K)
+        bn = block_n or bn
+        sp = sp if splits is None else splits
+        if N % 4 != 0:
+            sp = 1
+        ws, ws_bytes = None, 0
+        if sp > 1:
+            ws_bytes = int(L.dfb_gemm_workspace_bytes(M, N, sp))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=a.device)
+        check(L.dfb_gemm_bf16(ptr(a), ptr(b), ptr(out), ptr(bias), c_int(dt(bias) if bias is not None else 0),
+                              M, N, K, a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn), dt(out), ACT[act],
+                              bn, sp, ptr(ws), c_size_t(ws_bytes), _MAX_CTAS, stream()), "dfb_gemm_bf16")
+        return out
+    # CUDA-core path: general strides
+    if a.dtype != b.dtype:
+        b = b.to(a.dtype)
+    sa_m, sa_k = (a.stride(1), a.stride(0)) if a_mn else (a.stride(0), a.stride(1))
+    sb_n, sb_k = (b.stride(1), b.stride(0)) if b_mn else (b.stride(0), b.stride(1))
+    check(L.dfb_gemm_simt(ptr(a), ptr(b), ptr(out), ptr(bias), c_int(dt(bias) if bias is not None else 0), M, N, K,
+                          ctypes.c_long(sa_m), ctypes.c_long(sa_k), ctypes.c_long(sb_n), ctypes.c_long(sb_k),
+                          ctypes.c_long(out.stride(0)), dt(a), dt(b), dt(out), ACT[act], 1, stream()), "dfb_gemm_simt")
+    return out
+
+
+def colsum(x2d: torch.Tensor) -> torch.Tensor:
+    L = _lib.lib()
+    M, N = x2d.shape
+    out = torch.empty(N, dtype=torch.float32, device=x2d.device)
+    vn = 8 if x2d.dtype == torch.bfloat16 else 4
+    if x2d.dtype not in (torch.bfloat16, torch.float32) or x2d.stride(0) % vn != 0 or x2d.stride(1) != 1 \
+            or x2d.data_ptr() % 16 != 0:
+        return x2d.float().sum(0)
+    check(L.dfb_colsum(ptr(x2d), ptr(out), M, N, ctypes.c_long(x2d.stride(0)), dt(x2d), stream()), "dfb_colsum")
+    return out
+
+
+def act_op(a: torch.Tensor, b: Optional[torch.Tensor], mode: int) -> torch.Tensor:
+    L = _lib.lib()
+    a = a.contiguous()
+    b = b.contiguous() if b is not None else a
+    out = torch.empty_like(a)
+    check(L.dfb_act(ptr(a), ptr(b), ptr(out), ctypes.c_long(a.numel()), dt(a), mode, stream()), "dfb_act")
+    return out
+
+
+def _init_sigs() -> None:
+    L = _lib.lib()
+    if getattr(L, "_dfb_linear_sigs", False):
+        return
+    L.dfb_gemm_workspace_bytes.restype = ctypes.c_size_t
+    L.dfb_gemm_workspace_bytes.argtypes = [c_int, c_int, c_int]
+    L.dfb_gemm_pick_splits.restype = c_int
+    L.dfb_gemm_pick_splits.argtypes = [c_int] * 5
+    L.dfb_gemm_bf16.restype = c_int
+    L.dfb_gemm_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_void_p]
+    L.dfb_gemm_simt.restype = c_int
+    L.dfb_gemm_simt.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int] + [ctypes.c_long] * 5 + \
+        [c_int] * 5 + [c_void_p]
+    L.dfb_colsum.restype = c_int
+    L.dfb_colsum.argtypes = [c_void_p, c_void_p, c_int, c_int, ctypes.c_long, c_int, c_void_p]
+    L.dfb_act.restype = c_int
+    L.dfb_act.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_long, c_int, c_int, c_void_p]
+    L._dfb_linear_sigs = True
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, activation):
+        _init_sigs()
+        K, N = weight.shape
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        w = weight if weight.dtype == x2.dtype else weight.to(x2.dtype)
+        M = x2.shape[0]
+        saved_act = None
+        if activation == "gelu":
+            pre = gemm(x2, w, a_mn=False, b_mn=True, M=M, N=N, K=K, bias=bias)
+            y = act_op(pre, None, 0)
+            saved_act = pre
+        else:
+            y = gemm(x2, w, a_mn=False, b_mn=True, M=M, N=N, K=K, bias=bias, act=activation)
+            if activation == "relu":
+                saved_act = y
+        ctx.activation = activation
+        ctx.has_bias = bias is not None
+        ctx.bias_ref = bias
+        ctx.weight_ref = weight
+        ctx.save_for_backward(x2, w, saved_act)
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, saved_act = ctx.saved_tensors
+        K, N = w.shape
+        M = x2.shape[0]
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if dy2.dtype != x2.dtype:
+            dy2 = dy2.to(x2.dtype)
+        if ctx.activation == "gelu":
+            dy2 = act_op(dy2, saved_act, 1)
+        elif ctx.activation == "relu":
+            dy2 = act_op(dy2, saved_act, 2)
+        dx = dw = db = None
+        weight = ctx.weight_ref
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, w, a_mn=False, b_mn=False, M=M, N=K, K=N).reshape(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            sink = getattr(weight, "_dfb_grad_sink", None)      # engine: write straight into the flat gradient bucket
+            if sink is not None:
+                gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out=sink.view(K, N))
+                weight._dfb_grad_ready()
+            else:
+                dw = gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out_dtype=weight.dtype)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            bias = ctx.bias_ref
+            db = colsum(dy2)
+            sink = getattr(bias, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.copy_(db)
+                bias._dfb_grad_ready()
+                db = None
+            else:
+                db = db.to(bias.dtype)
+        return dx, dw, db, None
+
+
+def linear_cuda(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], activation: Optional[str]) -> torch.Tensor:
+    if activation not in ACT:
+        raise ValueError(f"unsupported fused activation {activation}")
+    return _LinearFn.apply(x, weight, bias, activation)

@@ -1,0 +1,214 @@
+"""CPU oracle: a from-scratch restatement of the reference's tf.js math and training schedules.
+
+The reference cannot run here (no node, no tf.js), so parity is claimed against this module:
+NumPy fp32 forward/backward of the MNIST dense model
+(`/root/reference/experiment/mnist/mnist_server.ts:16-22`), the swapped-argument loss of
+`/root/reference/src/common/models.ts:139` with both gradient variants, plain SGD
+(`models.ts:128-135`), and single-process simulators of the two schedules:
+  * `simulate_async`  — `/root/reference/src/server/asynchronousSGD_server.ts:65-80` with the intended
+    FCFS-per-worker dispatch (Q6) and an optional staleness bound (Q7);
+  * `simulate_sync`   — `/root/reference/src/server/federated_server.ts:71-116` with
+    `minUpdatesPerVersion = #workers` (synchronous batch gradient descent).
+It is deliberately independent of `torch.autograd` and of this package's ops so it can serve as their check,
+and it is the timed CPU baseline of BASELINE.md.
+"""
+from __future__ import annotations
+
+import time
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+__all__ = ["MlpOracle", "log_softmax", "softmax", "ref_compat_loss_and_grad", "softmax_ce_loss_and_grad",
+           "simulate_async", "simulate_sync", "synthetic_mnist"]
+
+
+def log_softmax(z: np.ndarray) -> np.ndarray:
+    m = z.max(-1, keepdims=True)
+    return z - m - np.log(np.exp(z - m).sum(-1, keepdims=True))
+
+
+def softmax(z: np.ndarray) -> np.ndarray:
+    return np.exp(log_softmax(z))
+
+
+def ref_compat_loss_and_grad(pred: np.ndarray, y: np.ndarray, variant: str = "custom") -> Tuple[float, np.ndarray]:
+    """tfjs `softmaxCrossEntropy(onehotLabels=pred, logits=y).mean()` and d/dpred.
+
+    custom: `dy*(labels - softmax(logits))` — the customGrad of tfjs-core 1.2.x for its first argument.
+    true  : `-log_softmax(y)` — the derivative of the value itself."""
+    b = pred.shape[0]
+    lp = log_softmax(y.astype(np.float32))
+    loss = float((-(pred * lp).sum(-1)).mean())
+    g = (pred - np.exp(lp)) / b if variant == "custom" else -lp / b
+    return loss, g.astype(np.float32)
+
+
+def softmax_ce_loss_and_grad(logits: np.ndarray, y: np.ndarray) -> Tuple[float, np.ndarray]:
+    b = logits.shape[0]
+    lp = log_softmax(logits.astype(np.float32))
+    loss = float((-(y * lp).sum(-1)).mean())
+    return loss, ((np.exp(lp) * y.sum(-1, keepdims=True) - y) / b).astype(np.float32)
+
+
+class MlpOracle:
+    """Flatten -> Dense(hidden, relu) -> Dense(classes, softmax); weights `[in,out]` like tf.js."""
+
+    def __init__(self, in_features: int = 784, hidden: int = 10, classes: int = 10, seed: int = 0,
+                 loss: str = "referenceCompat", lr: float = 0.001):
+        rng = np.random.default_rng(seed)
+
+        def glorot(i, o):
+            lim = np.sqrt(6.0 / (i + o))
+            return rng.uniform(-lim, lim, size=(i, o)).astype(np.float32)
+
+        self.vars: List[np.ndarray] = [glorot(in_features, hidden), np.zeros(hidden, np.float32),
+                                       glorot(hidden, classes), np.zeros(classes, np.float32)]
+        self.loss, self.lr = loss, lr
+
+    def get_vars(self) -> List[np.ndarray]:
+        return [v.copy() for v in self.vars]
+
+    def set_vars(self, vs: Sequence[np.ndarray]) -> None:
+        self.vars = [np.asarray(v, np.float32).copy() for v in vs]
+
+    def forward(self, x: np.ndarray):
+        w1, b1, w2, b2 = self.vars
+        x2 = x.reshape(x.shape[0], -1).astype(np.float32)
+        h_pre = x2 @ w1 + b1
+        h = np.maximum(h_pre, 0)
+        z = h @ w2 + b2
+        return x2, h_pre, h, z, softmax(z)
+
+    def predict(self, x: np.ndarray) -> np.ndarray:
+        return self.forward(x)[-1]
+
+    def fit(self, x: np.ndarray, y: np.ndarray) -> Tuple[float, List[np.ndarray]]:
+        """Loss and gradients for one micro-batch; weights untouched (`models.ts:137-142`)."""
+        w1, b1, w2, b2 = self.vars
+        x2, h_pre, h, z, p = self.forward(x)
+        y = y.astype(np.float32)
+        if self.loss in ("referenceCompat", "referenceCompatTrueGrad"):
+            loss, dp = ref_compat_loss_and_grad(p, y, "custom" if self.loss == "referenceCompat" else "true")
+            dz = p * (dp - (dp * p).sum(-1, keepdims=True))          # back through the model's own softmax layer
+        elif self.loss == "softmaxCrossEntropy":                     # standard CE on the logits
+            loss, dz = softmax_ce_loss_and_grad(z, y)
+        elif self.loss == "categoricalCrossentropy":
+            b = x2.shape[0]
+            loss = float((-(y * np.log(np.clip(p, 1e-7, 1 - 1e-7))).sum(-1)).mean())
+            dz = (p * y.sum(-1, keepdims=True) - y) / b
+        elif self.loss == "meanSquaredError":
+            loss = float(((y - p) ** 2).mean())
+            dp = 2 * (p - y) / p.size
+            dz = p * (dp - (dp * p).sum(-1, keepdims=True))
+        else:
+            raise ValueError(self.loss)
+        dw2, db2 = h.T @ dz, dz.sum(0)
+        dh = (dz @ w2.T) * (h_pre > 0)
+        dw1, db1 = x2.T @ dh, dh.sum(0)
+        return loss, [g.astype(np.float32) for g in (dw1, db1, dw2, db2)]
+
+    def update(self, grads: Sequence[np.ndarray], lr: Optional[float] = None) -> None:
+        lr = self.lr if lr is None else lr
+        self.vars = [v - np.float32(lr) * g for v, g in zip(self.vars, grads)]
+
+    def evaluate(self, x: np.ndarray, y: np.ndarray) -> List[float]:
+        p = self.predict(x)
+        return [float(((y - p) ** 2).mean()), float((p.argmax(-1) == y.argmax(-1)).mean())]
+
+
+def synthetic_mnist(n: int = 512, classes: int = 10, seed: int = 0, raw_0_255: bool = True):
+    """Synthetic MNIST-shaped data `[n,28,28,1]` float32 in 0..255 (Q4) with one-hot int labels: class-dependent
+    blobs, so a model can actually reduce the loss."""
+    rng = np.random.default_rng(seed)
+    labels = rng.integers(0, classes, size=n)
+    protos = rng.uniform(0, 1, size=(classes, 28, 28, 1)).astype(np.float32)
+    x = protos[labels] * 0.7 + rng.uniform(0, 0.3, size=(n, 28, 28, 1)).astype(np.float32)
+    if raw_0_255:
+        x = np.floor(x * 255.0).astype(np.float32)
+    y = np.eye(classes, dtype=np.float32)[labels]
+    return x, y
+
+
+def _batches(n: int, bs: int) -> int:
+    return n // bs
+
+
+def simulate_async(model: MlpOracle, x: np.ndarray, y: np.ndarray, *, batch_size: int = 32, epochs: int = 1,
+                   workers: int = 1, maximum_staleness: Optional[int] = None,
+                   order: Optional[Callable[[int], int]] = None) -> Dict[str, list]:
+    """Round-robin (or `order(step) -> worker`) completion order; every worker holds (weights snapshot, batch).
+
+    Returns per-applied-update `loss` (the worker's training loss on its stale weights), `staleness`, `dropped`."""
+    nb = _batches(x.shape[0], batch_size)
+    queue = [(e, b) for e in range(epochs) for b in range(nb)]
+    qi = 0
+    version = 0
+    hold: List[Optional[Tuple[List[np.ndarray], int, Tuple[int, int]]]] = [None] * workers
+    for w in range(workers):
+        if qi < len(queue):
+            hold[w] = (model.get_vars(), version, queue[qi])
+            qi += 1
+    out = {"loss": [], "staleness": [], "dropped": 0, "versions": 0}
+    step = 0
+    retry: List[Tuple[int, int]] = []
+    while any(h is not None for h in hold):
+        w = order(step) % workers if order else step % workers
+        step += 1
+        if hold[w] is None:
+            continue
+        snap, v, (e, b) = hold[w]
+        server_vars = model.get_vars()
+        model.set_vars(snap)
+        loss, grads = model.fit(x[b * batch_size:(b + 1) * batch_size], y[b * batch_size:(b + 1) * batch_size])
+        model.set_vars(server_vars)
+        staleness = version - v
+        if maximum_staleness is not None and staleness > maximum_staleness:
+            out["dropped"] += 1
+            retry.append((e, b))
+        else:
+            model.update(grads)
+            version += 1
+            out["loss"].append(loss)
+            out["staleness"].append(staleness)
+        nxt = None
+        if qi < len(queue):
+            nxt = queue[qi]
+            qi += 1
+        elif retry:
+            nxt = retry.pop(0)
+        hold[w] = (model.get_vars(), version, nxt) if nxt is not None else None
+    out["versions"] = version
+    return out
+
+
+def simulate_sync(model: MlpOracle, x: np.ndarray, y: np.ndarray, *, batch_size: int = 32, epochs: int = 1,
+                  workers: int = 2) -> Dict[str, list]:
+    """Synchronous batch GD: `workers` micro-batches per version, mean of their gradients, one SGD step."""
+    nb = _batches(x.shape[0], batch_size)
+    out = {"loss": [], "versions": 0}
+    for _ in range(epochs):
+        for b0 in range(0, nb - nb % workers if nb >= workers else nb, workers):
+            losses, acc = [], None
+            group = list(range(b0, min(b0 + workers, nb)))
+            for b in group:
+                loss, grads = model.fit(x[b * batch_size:(b + 1) * batch_size], y[b * batch_size:(b + 1) * batch_size])
+                losses.append(loss)
+                acc = grads if acc is None else [a + g for a, g in zip(acc, grads)]
+            model.update([a / len(group) for a in acc])
+            out["loss"].append(float(np.mean(losses)))
+            out["versions"] += 1
+    return out
+
+
+def timed_cpu_baseline(steps: int = 200, batch_size: int = 32, seed: int = 0) -> Dict[str, float]:
+    """Samples/s of the oracle on this CPU for the MNIST dense config (the 'timed CPU baseline' of BASELINE.md)."""
+    x, y = synthetic_mnist(batch_size * 8, seed=seed)
+    m = MlpOracle(seed=seed)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        b = s % 8
+        _, g = m.fit(x[b * batch_size:(b + 1) * batch_size], y[b * batch_size:(b + 1) * batch_size])
+        m.update(g)
+    dt = time.perf_counter() - t0
+    return {"samples_per_sec": steps * batch_size / dt, "ms_per_step": dt / steps * 1e3}

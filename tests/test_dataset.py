@@ -1,0 +1,80 @@
+"""DistriDataset dispatcher properties (reference src/server/dataset.ts:43-67)."""
+import pytest
+import torch
+
+from distriflow_b200 import DistriDataset
+
+
+def make(n=10, bs=2, epochs=2, small=False):
+    x = torch.arange(n, dtype=torch.float32).reshape(n, 1)
+    return DistriDataset(x, x.clone(), {"batchSize": bs, "epochs": epochs, "smallLastBatch": small})
+
+
+def test_fcfs_order_and_epoch_advance():
+    ds = make()
+    assert ds.batches == 5
+    seen = []
+    for _ in range(5):
+        b = ds.next()
+        seen.append(b.batch)
+        assert b.epoch == 0 and torch.equal(b.x[:, 0], torch.tensor([2.0 * b.batch, 2.0 * b.batch + 1]))
+        ds.complete_batch(b.batch)
+    assert seen == [0, 1, 2, 3, 4]
+    b = ds.next()
+    assert b.epoch == 1 and b.batch == 0 and len(ds.CompletedEpochs) == 1
+
+
+def test_incomplete_batches_are_reissued_and_epoch_waits():
+    ds = make(epochs=1)
+    got = [ds.next().batch for _ in range(5)]
+    for b in got:
+        if b not in (1, 3):
+            ds.complete_batch(b)
+    # fresh ones ran out: stragglers 1 and 3 are handed out again, epoch does not advance
+    assert ds.next().batch == 1
+    assert ds.next().batch == 3
+    assert ds.next().batch == 1
+    assert ds.epoch == 0
+    ds.complete_batch(1)
+    assert ds.next().batch == 3
+    ds.complete_batch(3)
+    assert ds.next().done
+
+
+def test_complete_is_idempotent_and_epoch_checked():
+    ds = make()
+    b = ds.next()
+    assert ds.complete_batch(b.batch) is True
+    assert ds.complete_batch(b.batch) is False and ds.duplicates == 1
+    assert ds.complete_batch(1, epoch=7) is False
+    assert 1 in ds.incompleteBatches
+
+
+def test_done_after_last_epoch():
+    ds = make(n=4, bs=2, epochs=2)
+    n = 0
+    for b in ds:
+        ds.complete_batch(b.batch)
+        n += 1
+    assert n == 4 and ds.next().done
+
+
+def test_ragged_last_batch():
+    ds = make(n=5, bs=2, epochs=1, small=True)
+    assert ds.batches == 3
+    sizes = []
+    for b in ds:
+        sizes.append(b.x.shape[0])
+        ds.complete_batch(b.batch)
+    assert sizes == [2, 2, 1]
+    ds = make(n=5, bs=2, epochs=1, small=False)
+    assert ds.batches == 2
+
+
+def test_uuid_ids_and_preprocess():
+    ds = make()
+    assert len(set(ds.epochIDs)) == 2 and len(ds.microBatchIDs) == 5
+    ds.add_preprocess_callback(lambda b: type(b)(b.batch, b.epoch, b.x * 2, b.y, b.batchId, b.epochId))
+    b = ds.next()
+    assert torch.equal(b.x[:, 0], torch.tensor([0.0, 2.0])) and b.batchId == ds.microBatchIDs[0]
+    assert ds.queuedMicroBatch == [1, 2, 3, 4]
