@@ -1,0 +1,240 @@
+#!/usr/bin/env python
+"""Headline benchmark: synchronous data-parallel training throughput (samples/sec) of GPT-2 small (124M),
+sequence 1024, bf16 — BASELINE.json config 5 — through `distriflow_b200.parallel.DataParallelEngine`.
+
+    python bench.py --gpus N --steps K --warmup W            # N = 1
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+Prints ONE JSON line on rank 0 (contract in the task statement).  `--impl reference` prints the
+"unavailable" line: the reference is TypeScript on tf.js/socket.io and has no Python package
+(`pip install ... /root/reference` -> "Neither 'setup.py' nor 'pyproject.toml' found"; no node/npm offline).
+`--impl ddp` runs the PyTorch DDP + NCCL (+cuBLAS) baseline of the identical model and schedule
+(BASELINE.json "Baselines"); `--model` / `--mode` select the other BASELINE configs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
+    ap.add_argument("--model", default="gpt2-small", choices=["gpt2-small", "gpt2-tiny", "resnet50", "resnet20", "mnist-cnn",
+                                                               "mnist-mlp"])
+    ap.add_argument("--mode", default="sync", choices=["sync", "async"])
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU micro-batch (0 = model default)")
+    ap.add_argument("--seq", type=int, default=1024)
+    ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--optimizer", default="adam")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm = sorted(int(r[1]) for r in self.rows if len(r) >= 9 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) >= 9 and r[2].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(args, device, torch):
+    """Returns (model, loss_fn, make_host_batch(), samples_per_batch, config_dict)."""
+    import distriflow_b200  # noqa: F401
+    if args.model.startswith("gpt2"):
+        from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+        cfg = GPT2Config.small() if args.model == "gpt2-small" else GPT2Config.tiny()
+        seq = min(args.seq, cfg.n_positions)
+        bs = args.batch or (32 if args.model == "gpt2-small" else 8)
+        torch.manual_seed(1234)
+        model = GPT2(cfg).to(device)
+
+        def make():
+            idx = torch.randint(0, cfg.vocab_size, (bs, seq + 1))
+            return idx[:, :-1].contiguous().pin_memory(), idx[:, 1:].contiguous().pin_memory()
+
+        return model, gpt2_loss, make, bs, {"model": "gpt2-small-124M" if args.model == "gpt2-small" else "gpt2-tiny",
+                                            "seq_len": seq, "per_gpu_batch": bs}
+    if args.model in ("resnet50", "resnet20"):
+        from distriflow_b200.models.resnet import resnet20, resnet50, resnet_loss
+        torch.manual_seed(1234)
+        if args.model == "resnet50":
+            model, hw, classes, bs = resnet50().to(device), 224, 1000, args.batch or 64
+        else:
+            model, hw, classes, bs = resnet20().to(device), 32, 10, args.batch or 256
+
+        def make():
+            return torch.randn(bs, hw, hw, 3).pin_memory(), torch.randint(0, classes, (bs,)).pin_memory()
+
+        return model, resnet_loss, make, bs, {"model": args.model, "image": hw, "per_gpu_batch": bs}
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.models import mnist_cnn, mnist_mlp
+    torch.manual_seed(1234)
+    model = (mnist_cnn(10, softmax_output=False) if args.model == "mnist-cnn" else mnist_mlp(softmax_output=False)).to(device)
+    bs = args.batch or 32
+    ce = get_loss("softmaxCrossEntropy")
+
+    def loss_fn(m, x, y):
+        return ce(y, m(x))
+
+    def make():
+        return (torch.rand(bs, 28, 28, 1) * 255).pin_memory(), torch.randint(0, 10, (bs,)).pin_memory()
+
+    return model, loss_fn, make, bs, {"model": args.model, "per_gpu_batch": bs}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable": "reference is TypeScript on tf.js/socket.io: no setup.py/pyproject "
+                          "(pip: 'not installable'), and node/npm/tfjs are absent offline; see DESIGN.md"}))
+        return 0
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:            # convenience: re-launch under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
+            return subprocess.call(cmd)
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    model, loss_fn, make_batch, bs, wcfg = build_workload(args, device, torch)
+    from distriflow_b200.ops import _lib
+
+    if args.impl == "ours":
+        if args.mode == "async":
+            from distriflow_b200.parallel.async_engine import AsyncEngine
+            engine = AsyncEngine(model, loss_fn, {"optimizer": args.optimizer if args.optimizer != "adam" else "sgd",
+                                                  "learningRate": 1e-3, "maximumStaleness": 4, "mode": "async"},
+                                 rank=rank, world=world, device=device)
+        else:
+            from distriflow_b200.parallel.engine import DataParallelEngine
+            engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
+                                                         "bucketBytes": int(args.bucket_mb * (1 << 20))},
+                                        rank=rank, world=world, device=device)
+        step = engine.step
+    else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)
+        from baseline.ddp_baseline import make_ddp_step
+        step = make_ddp_step(model, loss_fn, args.optimizer, 3e-4, world, device, int(args.bucket_mb))
+
+    host = [make_batch() for _ in range(4)]
+    dev = [(x.to(device, non_blocking=True), y.to(device, non_blocking=True)) for x, y in host]
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(*dev[i % len(dev)])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.LAUNCHES[0]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loss = None
+    for i in range(args.steps):
+        loss = step(*dev[i % len(dev)])
+    e1.record()
+    barrier()
+    launches = _lib.LAUNCHES[0] - l0
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end-to-end through the public API: pinned host inputs -> H2D -> step -> loss D2H, every step
+    e2e = None
+    if not args.no_e2e:
+        barrier()
+        t0 = time.perf_counter()
+        last = 0.0
+        for i in range(args.steps):
+            hx, hy = host[i % len(host)]
+            x = hx.to(device, non_blocking=True)
+            y = hy.to(device, non_blocking=True)
+            last = float(step(x, y).item())
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        hx, hy = host[0]
+        e2e = (e2e_ms, hx.numel() * hx.element_size() + hy.numel() * hy.element_size(), 4, last)
+
+    t = torch.tensor([ms, e2e[0] if e2e else 0.0], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    if rank == 0:
+        gb = bs * world
+        value = gb * args.steps / (ms / 1e3)
+        out = {"metric": "samples/sec sync DP" if args.mode == "sync" else "samples/sec async DP", "value": value,
+               "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "bf16" if args.model.startswith(("gpt2", "resnet")) else "fp32", "data": "synthetic",
+               "impl": args.impl,
+               "config": {**wcfg, "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
+                          "optimizer": args.optimizer, "bucket_mb": args.bucket_mb,
+                          "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
+                          "loss": float(loss)},
+               "clocks": clocks, "gpu_launches": int(launches)}
+        if e2e:
+            out["e2e"] = {"value": gb * args.steps / (e2e_ms / 1e3), "unit": "samples/s", "h2d_bytes_per_step": e2e[1],
+                          "d2h_bytes_per_step": e2e[2], "ms_per_step": e2e_ms / args.steps}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

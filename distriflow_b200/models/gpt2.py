@@ -1,0 +1,100 @@
+"""GPT-2 (BASELINE.json config 5: GPT-2 small, 124M, sequence 1024, bf16, synchronous DP).
+
+Not in the reference (it ships only the MNIST models); needed as a named workload.  All projections are Dense
+layers in the `[in, out]` layout (GPT-2's own Conv1D layout) running the tcgen05 GEMM, GELU and the bias are in
+the GEMM path, the tied LM head runs the same kernel on the `[vocab, d]` embedding table (K-major B operand), the
+loss is the fused softmax-CE kernel writing the logit gradient in place.  Attention, LayerNorm and the
+embedding gather stay on PyTorch ops (SURVEY §2.5 last paragraph).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import ops
+from . import layers as L
+
+
+@dataclass
+class GPT2Config:
+    vocab_size: int = 50257
+    n_positions: int = 1024
+    n_embd: int = 768
+    n_layer: int = 12
+    n_head: int = 12
+    padded_vocab: int = 50304          # multiple of 128: aligned TMA pitches for the LM head / CE kernel
+
+    @staticmethod
+    def small() -> "GPT2Config":
+        return GPT2Config()
+
+    @staticmethod
+    def tiny() -> "GPT2Config":
+        return GPT2Config(vocab_size=500, n_positions=128, n_embd=128, n_layer=2, n_head=4, padded_vocab=512)
+
+
+class Block(nn.Module):
+    def __init__(self, c: GPT2Config, i: int):
+        super().__init__()
+        d = c.n_embd
+        self.n_head = c.n_head
+        self.ln_1 = L.LayerNorm(d, name=f"h{i}/ln_1")
+        self.c_attn = L.Dense(d, 3 * d, name=f"h{i}/attn/c_attn")
+        self.c_proj = L.Dense(d, d, name=f"h{i}/attn/c_proj")
+        self.ln_2 = L.LayerNorm(d, name=f"h{i}/ln_2")
+        self.c_fc = L.Dense(d, 4 * d, activation="gelu", name=f"h{i}/mlp/c_fc")
+        self.c_proj2 = L.Dense(4 * d, d, name=f"h{i}/mlp/c_proj")
+        for lin, std in ((self.c_attn, 0.02), (self.c_fc, 0.02), (self.c_proj, 0.02 / math.sqrt(2 * c.n_layer)),
+                         (self.c_proj2, 0.02 / math.sqrt(2 * c.n_layer))):
+            nn.init.normal_(lin.kernel, std=std)
+
+    def forward(self, x):
+        B, T, D = x.shape
+        h = self.ln_1(x)
+        qkv = self.c_attn(h)
+        q, k, v = qkv.view(B, T, 3, self.n_head, D // self.n_head).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        a = a.transpose(1, 2).reshape(B, T, D)
+        x = x + self.c_proj(a)
+        x = x + self.c_proj2(self.c_fc(self.ln_2(x)))
+        return x
+
+
+class GPT2(nn.Module):
+    def __init__(self, config: Optional[GPT2Config] = None):
+        super().__init__()
+        c = self.config = config or GPT2Config.small()
+        self.wte = nn.Parameter(torch.empty(c.padded_vocab, c.n_embd))
+        self.wpe = nn.Parameter(torch.empty(c.n_positions, c.n_embd))
+        nn.init.normal_(self.wte, std=0.02)
+        nn.init.normal_(self.wpe, std=0.02)
+        self.wte._dfb_shared = True          # used by the embedding gather AND the LM head: autograd accumulates
+        self.h = nn.ModuleList([Block(c, i) for i in range(c.n_layer)])
+        self.ln_f = L.LayerNorm(c.n_embd, name="ln_f")
+        self.input_shape = [c.n_positions]
+        self.output_shape = [c.n_positions, c.padded_vocab]
+
+    def num_params(self) -> int:
+        c = self.config
+        return sum(p.numel() for p in self.parameters()) - (c.padded_vocab - c.vocab_size) * c.n_embd
+
+    def forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor] = None):
+        B, T = idx.shape
+        pos = torch.arange(T, device=idx.device)
+        x = F.embedding(idx, self.wte) + self.wpe[pos]
+        for blk in self.h:
+            x = blk(x)
+        x = self.ln_f(x)
+        logits = ops.linear(x, self.wte, None, None, transposed=True)
+        if targets is None:
+            return logits
+        return ops.softmax_cross_entropy(logits, targets, inplace=True, unit_grad=True)
+
+
+def gpt2_loss(model: GPT2, idx: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+    return model(idx, targets)

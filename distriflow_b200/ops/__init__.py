@@ -36,12 +36,13 @@ def _act_cpu(y: torch.Tensor, activation: Optional[str]) -> torch.Tensor:
 
 
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
-           activation: Optional[str] = None) -> torch.Tensor:
-    """`act(x @ weight + bias)` with `weight` in tf.js layout `[in, out]`."""
+           activation: Optional[str] = None, transposed: bool = False) -> torch.Tensor:
+    """`act(x @ weight + bias)` with `weight` in tf.js layout `[in, out]` (`transposed=True`: `[out, in]`)."""
     if x.is_cuda:
         from .linear import linear_cuda
-        return linear_cuda(x, weight, bias, activation)
-    y = x @ weight.to(x.dtype)
+        return linear_cuda(x, weight, bias, activation, transposed)
+    w = weight.to(x.dtype)
+    y = x @ (w.t() if transposed else w)
     if bias is not None:
         y = y + bias.to(y.dtype)
     return _act_cpu(y, activation)
@@ -96,6 +97,7 @@ def layer_norm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: fl
     return F.layer_norm(x.float(), (x.shape[-1],), gamma.float(), beta.float(), eps).to(x.dtype)
 
 
-def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, ignore_index: Optional[int] = None,
+                          inplace: bool = False, unit_grad: bool = False) -> torch.Tensor:
     from .softmax_ce import softmax_cross_entropy as f
-    return f(logits, labels)
+    return f(logits, labels, ignore_index, inplace, unit_grad)

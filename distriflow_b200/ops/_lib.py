@@ -44,7 +44,11 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+LAUNCHES = [0]        # native calls issued (each is at least one kernel launch of this library); bench.py reports it
+
+
 def check(rc: int, what: str = "") -> None:
+    LAUNCHES[0] += 1
     if rc != 0:
         msg = lib().dfb_last_error()
         raise NativeError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")

@@ -34,7 +34,8 @@ struct GemmCfg {
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
   static constexpr int kStages = (BLOCK_N == 256) ? 4 : 6;
   static constexpr int kTmemCols = 2 * BLOCK_N;         // double-buffered fp32 accumulator
-  static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kStageOutBytes + BLOCK_N * 4 + 256 + 1024;
+  // <= 233472 - 2*1024 (two CTA reserves) so that a small comm/optimizer CTA can share the SM with a GEMM CTA
+  static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kStageOutBytes + 256 + 1024;
 };
 
 struct GemmParams {
@@ -70,8 +71,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kATileBytes;
   uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
-  float* smem_bias = reinterpret_cast<float*>(smem_out + 2 * kStageOutBytes);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_bias + BLOCK_N);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + 2 * kStageOutBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -213,16 +213,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       decode_tile(tile, m_blk, n_blk, split);
       const int m0 = m_blk * kBlockM, n0 = n_blk * BLOCK_N;
       const int out_row0 = m0 + split * p.split_rows;
-      if (p.bias != nullptr) {
-        for (int i = epi_tid; i < BLOCK_N; i += kEpiThreads) {
-          int n = n0 + i;
-          float b = 0.f;
-          if (n < p.N)
-            b = p.bias_dtype == DT_F32 ? reinterpret_cast<const float*>(p.bias)[n]
-                                       : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[n]);
-          smem_bias[i] = b;
-        }
-      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BLOCK_N;
@@ -252,9 +242,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
         if (issuer) tma_store_wait_read<1>();          // the store that last used this buffer has drained
         named_bar_sync(1, kEpiThreads);
-        if (p.bias != nullptr) {
+        if (p.bias != nullptr) {      // same addresses for every lane: L1 broadcast loads
+          const int nb = n0 + c * kChunkN;
+          if (p.bias_dtype == DT_F32) {
+            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+            if (nb + kChunkN <= p.N && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-          for (int j = 0; j < kChunkN; ++j) v[j] += smem_bias[c * kChunkN + j];
+              for (int j = 0; j < kChunkN / 4; ++j) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + j);
+                v[4 * j] += b4.x; v[4 * j + 1] += b4.y; v[4 * j + 2] += b4.z; v[4 * j + 3] += b4.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __ldg(bp + j) : 0.f;
+            }
+          } else {
+            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+#pragma unroll
+            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __bfloat162float(bp[j]) : 0.f;
+          }
         }
         if (p.act == ACT_RELU) {
 #pragma unroll

@@ -121,10 +121,15 @@ def _init_sigs() -> None:
 
 
 class _LinearFn(torch.autograd.Function):
+    """`transposed=False`: weight `[in, out]` (tf.js Dense).  `transposed=True`: weight `[out, in]` (tied LM head)."""
+
     @staticmethod
-    def forward(ctx, x, weight, bias, activation):
+    def forward(ctx, x, weight, bias, activation, transposed):
         _init_sigs()
-        K, N = weight.shape
+        if transposed:
+            N, K = weight.shape
+        else:
+            K, N = weight.shape
         x2 = x.reshape(-1, K)
         if not x2.is_contiguous():
             x2 = x2.contiguous()
@@ -132,17 +137,19 @@ class _LinearFn(torch.autograd.Function):
         M = x2.shape[0]
         saved_act = None
         if activation == "gelu":
-            pre = gemm(x2, w, a_mn=False, b_mn=True, M=M, N=N, K=K, bias=bias)
+            pre = gemm(x2, w, a_mn=False, b_mn=not transposed, M=M, N=N, K=K, bias=bias)
             y = act_op(pre, None, 0)
             saved_act = pre
         else:
-            y = gemm(x2, w, a_mn=False, b_mn=True, M=M, N=N, K=K, bias=bias, act=activation)
+            y = gemm(x2, w, a_mn=False, b_mn=not transposed, M=M, N=N, K=K, bias=bias, act=activation)
             if activation == "relu":
                 saved_act = y
         ctx.activation = activation
         ctx.has_bias = bias is not None
         ctx.bias_ref = bias
         ctx.weight_ref = weight
+        ctx.transposed = transposed
+        ctx.dims = (M, N, K)
         ctx.save_for_backward(x2, w, saved_act)
         ctx.x_shape = x.shape
         return y.reshape(*x.shape[:-1], N)
@@ -150,8 +157,8 @@ class _LinearFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x2, w, saved_act = ctx.saved_tensors
-        K, N = w.shape
-        M = x2.shape[0]
+        M, N, K = ctx.dims
+        tr = ctx.transposed
         dy2 = dy.reshape(M, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
@@ -164,14 +171,20 @@ class _LinearFn(torch.autograd.Function):
         dx = dw = db = None
         weight = ctx.weight_ref
         if ctx.needs_input_grad[0]:
-            dx = gemm(dy2, w, a_mn=False, b_mn=False, M=M, N=K, K=N).reshape(ctx.x_shape)
+            # dX[M,K] = dY[M,N] . W ; contraction over N: W[in,out] is K-major for it, W[out,in] is MN-major
+            dx = gemm(dy2, w, a_mn=False, b_mn=tr, M=M, N=K, K=N).reshape(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             sink = getattr(weight, "_dfb_grad_sink", None)      # engine: write straight into the flat gradient bucket
+            if tr:      # dW[out,in] = dY^T . X
+                args = dict(a=dy2, b=x2, M=N, N=K)
+            else:       # dW[in,out] = X^T . dY
+                args = dict(a=x2, b=dy2, M=K, N=N)
             if sink is not None:
-                gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out=sink.view(K, N))
+                gemm(args["a"], args["b"], a_mn=True, b_mn=True, M=args["M"], N=args["N"], K=M,
+                     out=sink.view(args["M"], args["N"]))
                 weight._dfb_grad_ready()
             else:
-                dw = gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out_dtype=weight.dtype)
+                dw = gemm(args["a"], args["b"], a_mn=True, b_mn=True, M=args["M"], N=args["N"], K=M, out_dtype=weight.dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             bias = ctx.bias_ref
             db = colsum(dy2)
@@ -182,10 +195,11 @@ class _LinearFn(torch.autograd.Function):
                 db = None
             else:
                 db = db.to(bias.dtype)
-        return dx, dw, db, None
+        return dx, dw, db, None, None
 
 
-def linear_cuda(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], activation: Optional[str]) -> torch.Tensor:
+def linear_cuda(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], activation: Optional[str],
+                transposed: bool = False) -> torch.Tensor:
     if activation not in ACT:
         raise ValueError(f"unsupported fused activation {activation}")
-    return _LinearFn.apply(x, weight, bias, activation)
+    return _LinearFn.apply(x, weight, bias, activation, transposed)

@@ -1,0 +1,222 @@
+"""Asynchronous SGD with bounded staleness over peer memory — no host round trip on the data path.
+
+Reference behaviour replaced (`/root/reference/src/server/asynchronousSGD_server.ts:65-108`,
+`/root/reference/src/client/asynchronousSGD_client.ts:43-84`): a worker uploads a gradient, the server
+applies it at once and hands out fresh weights.  Here every rank is a worker AND owns 1/R of the server:
+
+  pull   worker reads every owner's slice of the working weights with P2P loads and records the owners'
+         version counters (`seen_version`);
+  push   worker adds its gradient slice by slice into the owners' open accumulation buffers with P2P
+         `red.add`, but only where `owner_version - seen_version <= maximumStaleness` (device-side guard —
+         the `maximumStaleness` of `/root/reference/README.md:27`, which the reference never implemented);
+  apply  owner flips its double-buffered accumulator, waits for in-flight pushers of the closed half, applies the
+         accumulated gradients in place (SGD / momentum / Adam on the fp32 master shard), refreshes its slice of
+         the working weights and bumps its version by the number of gradients applied.
+
+`AsyncShardState` wraps the three kernels (and can emulate R ranks on one GPU for tests); `AsyncEngine` is the
+training loop: device work-queue ticket -> gather batch -> pull -> fit -> push -> apply -> complete ticket.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Any, Callable, Dict, List, Optional
+
+import torch
+import torch.nn as nn
+
+from ..config import engine_config
+from ..ops import _lib
+from ..ops._lib import c_void_p, check, dt, ptr
+from .engine import _OPT, _TORCH_DT, _comm_sigs, _round_up
+from .symm import PAD_BYTES, SymmetricHeap
+
+__all__ = ["AsyncShardState", "AsyncEngine"]
+
+
+class _Local:
+    pass
+
+
+class AsyncShardState:
+    def __init__(self, heaps: List[SymmetricHeap], ranks: List[int], world: int, n: int, grad_dtype, param_dtype, lr: float,
+                 max_staleness: int, optimizer: str = "sgd", policy: str = "drop", cfg: Optional[Dict[str, Any]] = None,
+                 ctas: int = 32):
+        self.L = _comm_sigs()
+        self.heaps, self.ranks, self.world = heaps, ranks, world
+        self.n = _round_up(n, world * 64)
+        self.shard = self.n // world
+        self.grad_dtype, self.param_dtype = grad_dtype, param_dtype
+        self.lr, self.max_staleness, self.optimizer, self.policy = lr, max_staleness, optimizer, policy
+        self.cfg = cfg or {"momentum": 0.9, "beta1": 0.9, "beta2": 0.999, "eps": 1e-8, "weightDecay": 0.0}
+        self.ctas = ctas
+        self.steps = 0
+        psz = torch.empty((), dtype=param_dtype).element_size()
+        self.psz = psz
+        self.loc: Dict[int, _Local] = {}
+        for h, r in zip(heaps, ranks):
+            lo = _Local()
+            lo.heap = h
+            lo.p_off = h.alloc(self.n * psz)
+            lo.a0_off = h.alloc(self.shard * 4)
+            lo.a1_off = h.alloc(self.shard * 4)
+            lo.params = h.view(lo.p_off, (self.n,), param_dtype)
+            lo.acc0 = h.view(lo.a0_off, (self.shard,), torch.float32)
+            lo.acc1 = h.view(lo.a1_off, (self.shard,), torch.float32)
+            d = h.device
+            lo.master = torch.zeros(self.shard, device=d)
+            lo.m = torch.zeros(self.shard, device=d) if optimizer in ("momentum", "adam") else None
+            lo.v = torch.zeros(self.shard, device=d) if optimizer == "adam" else None
+            lo.seen = torch.zeros(8, dtype=torch.int32, device=d)
+            lo.push_state = torch.zeros(16, dtype=torch.int32, device=d)
+            lo.scratch = torch.zeros(2, dtype=torch.int32, device=d)
+            self.loc[r] = lo
+
+    @classmethod
+    def emulated(cls, world: int, n: int, **kw) -> "AsyncShardState":
+        npad = _round_up(n, world * 64)
+        psz = torch.empty((), dtype=kw.get("param_dtype", torch.float32)).element_size()
+        heaps = SymmetricHeap.emulated(world, npad * psz + 8 * (npad // world) + 65536)
+        return cls(heaps, list(range(world)), world, n, **kw)
+
+    # ------------------------------------------------------------------------------------------
+    def init_weights(self, w: torch.Tensor) -> None:
+        """Same full-precision weights on every rank; each rank keeps its slice as fp32 master."""
+        for r, lo in self.loc.items():
+            lo.params.zero_()
+            lo.params[:w.numel()].copy_(w.reshape(-1))
+            full = torch.zeros(self.n, device=w.device)
+            full[:w.numel()] = w.reshape(-1).float()
+            lo.master.copy_(full[r * self.shard:(r + 1) * self.shard])
+
+    def _one(self, rank: Optional[int]) -> int:
+        return self.ranks[0] if rank is None else rank
+
+    def pull(self, rank: Optional[int] = None) -> None:
+        r = self._one(rank)
+        lo = self.loc[r]
+        h = lo.heap
+        check(self.L.dfb_async_pull(h.ptrs(lo.p_off), h.ptrs(0), ptr(lo.params), ptr(lo.seen), self.n * self.psz,
+                                    self.shard * self.psz, r, self.world, self.ctas, _lib.stream()), "dfb_async_pull")
+
+    def push(self, rank: Optional[int], grad: torch.Tensor, scale: float = 1.0) -> None:
+        r = self._one(rank)
+        lo = self.loc[r]
+        h = lo.heap
+        assert grad.numel() == self.n and grad.is_contiguous(), (grad.numel(), self.n)
+        check(self.L.dfb_async_push(ptr(grad), h.ptrs(lo.a0_off), h.ptrs(lo.a1_off), h.ptrs(0), ptr(lo.seen), ptr(lo.push_state),
+                                    self.n, self.shard, r, self.world, self.max_staleness, scale,
+                                    1 if self.policy == "scale" else 0, dt(grad), self.ctas, _lib.stream()), "dfb_async_push")
+
+    def apply(self, rank: Optional[int] = None) -> None:
+        r = self._one(rank)
+        lo = self.loc[r]
+        c = self.cfg
+        self.steps += 1
+        shard_view = lo.params[r * self.shard:(r + 1) * self.shard]
+        check(self.L.dfb_async_apply(ptr(lo.acc0), ptr(lo.acc1), lo.heap.pad_ptr(r), ptr(lo.master), ptr(lo.m), ptr(lo.v),
+                                     ptr(shard_view), ptr(lo.scratch), self.shard, dt(lo.params), _OPT[self.optimizer], self.lr,
+                                     c["momentum"], c["beta1"], c["beta2"], c["eps"], c["weightDecay"], self.steps, self.ctas,
+                                     _lib.stream()), "dfb_async_apply")
+
+    def read_ctl(self, rank: Optional[int] = None) -> Dict[str, Any]:
+        r = self._one(rank)
+        pad = self.loc[r].heap.pad
+        torch.cuda.synchronize()
+        w = [int(x) & 0xffffffff for x in pad[32:41].tolist()]
+        return {"version": w[0], "active": w[1], "inflight": [w[2], w[3]], "arrived": [w[4], w[5]], "applied": w[6],
+                "dropped": w[7], "max_staleness_seen": w[8]}
+
+    def full_master(self) -> torch.Tensor:
+        if len(self.loc) == self.world:
+            return torch.cat([self.loc[r].master for r in range(self.world)])
+        import torch.distributed as dist
+        mine = self.loc[self.ranks[0]].master
+        parts = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(parts, mine)
+        return torch.cat(parts)
+
+    def local_weights(self, rank: Optional[int] = None) -> torch.Tensor:
+        return self.loc[self._one(rank)].params
+
+    def close(self) -> None:
+        for h in self.heaps:
+            h.close()
+
+
+class AsyncEngine:
+    """One rank's asynchronous training loop.  `step(*batch)` = pull -> fit -> push -> apply; with a
+    `DeviceWorkQueue` + device-resident dataset, `run_dataset()` drives whole epochs without host round trips."""
+
+    def __init__(self, model: nn.Module, loss_fn: Callable[..., torch.Tensor], config: Optional[Dict[str, Any]] = None,
+                 rank: int = 0, world: int = 1, group=None, device: Optional[torch.device] = None):
+        self.cfg = engine_config({**(config or {}), "mode": "async"})
+        self.model, self.loss_fn, self.rank, self.world, self.group = model, loss_fn, rank, world, group
+        self.device = device or next(model.parameters()).device
+        self.param_dtype = _TORCH_DT[self.cfg["dtype"]]
+        self.grad_dtype = _TORCH_DT[self.cfg["gradDtype"]]
+        self.params: List[nn.Parameter] = []
+        seen = set()
+        for p in model.parameters():
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                self.params.append(p)
+        self.offsets, n = [], 0
+        for p in self.params:
+            self.offsets.append(n)
+            n += _round_up(p.numel(), 64)
+        psz = torch.empty((), dtype=self.param_dtype).element_size()
+        npad = _round_up(n, world * 64)
+        heap = SymmetricHeap(npad * psz + 8 * (npad // world) + 65536, rank, world, group, self.device)
+        self.state = AsyncShardState([heap], [rank], world, n, grad_dtype=self.grad_dtype, param_dtype=self.param_dtype,
+                                     lr=float(self.cfg["learningRate"]), max_staleness=int(self.cfg["maximumStaleness"]),
+                                     optimizer=self.cfg["optimizer"], policy="drop", cfg=self.cfg)
+        flat = torch.zeros(self.state.n, device=self.device)
+        for p, off in zip(self.params, self.offsets):
+            flat[off:off + p.numel()] = p.data.reshape(-1).float()
+        if world > 1:
+            import torch.distributed as dist
+            dist.broadcast(flat, src=0, group=group)
+        self.state.init_weights(flat)
+        lo = self.state.loc[rank]
+        self.grad_flat = torch.zeros(self.state.n, dtype=self.grad_dtype, device=self.device)
+        for p, off in zip(self.params, self.offsets):
+            p.data = lo.params[off:off + p.numel()].view(p.shape)
+            if not getattr(p, "_dfb_shared", False):
+                p._dfb_grad_sink = self.grad_flat[off:off + p.numel()]
+            p._dfb_grad_ready = lambda: None
+
+            def hook(param, sink=self.grad_flat[off:off + p.numel()]):
+                sink.copy_(param.grad.reshape(-1))
+                param.grad = None
+
+            p.register_post_accumulate_grad_hook(hook)
+        self.version = 0
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=group)
+
+    def step(self, *batch: Any) -> torch.Tensor:
+        self.state.pull()
+        loss = self.loss_fn(self.model, *batch)
+        loss.backward()
+        self.state.push(None, self.grad_flat)
+        self.state.apply()
+        self.version += 1
+        return loss.detach()
+
+    def drain(self) -> None:
+        """Apply whatever is still in flight (call on every rank after the last step, then barrier)."""
+        if self.world > 1:
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
+        self.state.apply()
+        self.state.apply()
+        torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
+        self.state.pull()
+
+    def counters(self) -> Dict[str, Any]:
+        return self.state.read_ctl()

@@ -1,0 +1,732 @@
+// Communication runtime + fused collective kernels over NVLink 5 / NVSwitch peer memory.
+//
+// What the reference does with websocket messages becomes loads and stores on
+// peer-mapped device memory issued from inside kernels:
+//   * upload + mean + `update` + broadcast of new weights, synchronous mode
+//     (/root/reference/src/server/federated_server.ts:71-116)          -> sync_rs_opt_ag_kernel:
+//     every rank owns 1/R of each bucket, PULLS that slice of everybody's gradients with P2P loads, reduces in
+//     fp32 in a fixed order, scales by 1/R, applies SGD / momentum / Adam to its fp32 master shard in place and
+//     PUSHES the refreshed working weights to every rank with P2P stores (reduce-scatter + optimizer +
+//     all-gather in ONE launch; no NCCL on the path).
+//   * upload + immediate `update`, asynchronous mode
+//     (/root/reference/src/server/asynchronousSGD_server.ts:65-108)    -> async_push / async_apply / async_pull:
+//     workers add gradients into the owner shard's accumulation buffer with P2P reductions guarded by a
+//     device-side staleness counter, the owner applies them in place, workers pull weights with P2P loads.
+//   * `dataset.next()` / `completeBatch()` (/root/reference/src/server/dataset.ts:43-67) -> device work queue.
+// Bootstrap (exchange of cudaIpc handles) is done by the Python side through torch.distributed.
+#include "common.cuh"
+#include "device_utils.cuh"
+
+namespace dfb {
+
+constexpr int kMaxRanks = 8;
+
+struct PeerPtrs {
+  void* p[kMaxRanks];
+};
+
+// ---------------------------------------------------------------- system-scope signalling
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {       // peer data: never trust a cached line
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_v4(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void red_add_f32_sys(float* p, float v) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;\n" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_v4_f32_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Signal pad layout (uint32 words) inside every rank's symmetric heap:
+//   [0, 8)    arrive-in  flags, one per source rank      [8, 16)   arrive-out flags
+//   [16]      local block counter                        [32, ...) async / work-queue words (see below)
+constexpr int kSigIn = 0, kSigOut = 8, kSigBlocks = 16;
+
+// Every block waits until all ranks have published `epoch` in this rank's `which` flags; block 0 publishes ours.
+__device__ __forceinline__ void rank_barrier(const PeerPtrs& sig, int rank, int R, int which, uint32_t epoch, bool do_signal) {
+  if (do_signal && threadIdx.x < R) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(sig.p[threadIdx.x]) + which + rank, epoch);
+  }
+  if (threadIdx.x < R) {
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(sig.p[rank]) + which + threadIdx.x;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------- optimizer on 4/8 fp32 lanes
+enum Opt : int { OPT_SGD = 0, OPT_MOMENTUM = 1, OPT_ADAM = 2, OPT_NONE = 3 };
+
+struct OptParams {
+  int kind;
+  float lr, momentum, beta1, beta2, eps, weight_decay;
+  float bias_c1, bias_c2;       // 1 - beta^t (host computed)
+};
+
+__device__ __forceinline__ float opt_step(float w, float g, float* m, float* v, const OptParams& o) {
+  if (o.weight_decay != 0.f) g += o.weight_decay * w;
+  if (o.kind == OPT_SGD) return w - o.lr * g;                    // /root/reference/src/common/models.ts:128-135
+  if (o.kind == OPT_MOMENTUM) {
+    float mm = o.momentum * (*m) + g;
+    *m = mm;
+    return w - o.lr * mm;
+  }
+  if (o.kind == OPT_ADAM) {
+    float mm = o.beta1 * (*m) + (1.f - o.beta1) * g;
+    float vv = o.beta2 * (*v) + (1.f - o.beta2) * g * g;
+    *m = mm;
+    *v = vv;
+    return w - o.lr * (mm / o.bias_c1) / (sqrtf(vv / o.bias_c2) + o.eps);
+  }
+  return w;
+}
+
+// ---------------------------------------------------------------- sync: reduce-scatter + 1/R + optimizer + all-gather
+struct SyncArgs {
+  PeerPtrs grads;        // base of this bucket's gradient buffer on every rank (TG)
+  PeerPtrs params;       // base of this bucket's working-weight buffer on every rank (TP)
+  PeerPtrs sig;          // signal pads
+  float* master;         // fp32 master weights of the OWNED slice (local)
+  float* m;              // optimizer state of the owned slice (local; may be null)
+  float* v;
+  void* reduced_out;     // optional: owned slice of the mean gradient, TG (for tests / OPT_NONE)
+  long n;                // elements in the bucket
+  long shard;            // elements per rank slice (multiple of 8)
+  int rank, R;
+  uint32_t epoch;        // barrier generation, strictly increasing per launch; 0 = no cross-rank barriers (emulation)
+  int push;              // 1 = push refreshed weights to every rank, 0 = only write the local copy
+  OptParams opt;
+};
+
+template <typename TG, typename TP, int R_T>
+__global__ void __launch_bounds__(512) sync_rs_opt_ag_kernel(const SyncArgs a) {
+  const int R = R_T > 0 ? R_T : a.R;
+  if (a.epoch) rank_barrier(a.sig, a.rank, R, kSigIn, a.epoch, blockIdx.x == 0);   // everybody's gradients are final
+  using VG = Vec16<TG>;
+  constexpr int VN = 8;                       // elements per thread-iteration (16 B of bf16, or 2 x 16 B of fp32)
+  constexpr int GV = VN / VG::kN;             // 16-byte loads per peer per iteration
+  const long lo = (long)a.rank * a.shard;
+  const long hi = min(a.n, lo + a.shard);
+  const long nvec = hi > lo ? (hi - lo + VN - 1) / VN : 0;
+  const float inv_r = 1.f / (float)R;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    const long e = lo + i * VN;               // first element (bucket-relative)
+    VG g[kMaxRanks][GV];
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q) {
+      if (q < R) {
+        const TG* src = reinterpret_cast<const TG*>(a.grads.p[q]) + e;
+#pragma unroll
+        for (int h = 0; h < GV; ++h) g[q][h].raw = ld_peer_v4(src + h * VG::kN);
+      }
+    }
+    float acc[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q) {     // fixed order -> bitwise reproducible, identical on every rank
+      if (q < R) {
+#pragma unroll
+        for (int h = 0; h < GV; ++h)
+#pragma unroll
+          for (int j = 0; j < VG::kN; ++j) acc[h * VG::kN + j] += g[q][h].get(j);
+      }
+    }
+    const long s = i * VN;                    // shard-relative
+    float w[VN];
+    {
+      const float4 w0 = *reinterpret_cast<const float4*>(a.master + s);
+      const float4 w1 = *reinterpret_cast<const float4*>(a.master + s + 4);
+      w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+    }
+    float mm[VN], vv[VN];
+    if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
+      const float4 m0 = *reinterpret_cast<const float4*>(a.m + s), m1 = *reinterpret_cast<const float4*>(a.m + s + 4);
+      mm[0] = m0.x; mm[1] = m0.y; mm[2] = m0.z; mm[3] = m0.w; mm[4] = m1.x; mm[5] = m1.y; mm[6] = m1.z; mm[7] = m1.w;
+    }
+    if (a.opt.kind == OPT_ADAM) {
+      const float4 v0 = *reinterpret_cast<const float4*>(a.v + s), v1 = *reinterpret_cast<const float4*>(a.v + s + 4);
+      vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
+    }
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      acc[j] *= inv_r;
+      w[j] = opt_step(w[j], acc[j], &mm[j], &vv[j], a.opt);
+    }
+    if (a.opt.kind != OPT_NONE) {
+      *reinterpret_cast<float4*>(a.master + s) = make_float4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<float4*>(a.master + s + 4) = make_float4(w[4], w[5], w[6], w[7]);
+      if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
+        *reinterpret_cast<float4*>(a.m + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(a.m + s + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+      }
+      if (a.opt.kind == OPT_ADAM) {
+        *reinterpret_cast<float4*>(a.v + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(a.v + s + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+      }
+    }
+    if (a.reduced_out != nullptr) {
+      VG o[GV];
+#pragma unroll
+      for (int h = 0; h < GV; ++h) {
+#pragma unroll
+        for (int j = 0; j < VG::kN; ++j) o[h].set(j, acc[h * VG::kN + j]);
+        reinterpret_cast<uint4*>(reinterpret_cast<TG*>(a.reduced_out) + s)[h] = o[h].raw;
+      }
+    }
+    if (a.opt.kind != OPT_NONE) {
+      using VP = Vec16<TP>;
+      constexpr int PV = VN / VP::kN;
+      VP o[PV];
+#pragma unroll
+      for (int h = 0; h < PV; ++h)
+#pragma unroll
+        for (int j = 0; j < VP::kN; ++j) o[h].set(j, w[h * VP::kN + j]);
+#pragma unroll
+      for (int q = 0; q < kMaxRanks; ++q) {
+        if (q < R && (a.push || q == a.rank)) {
+          TP* dst = reinterpret_cast<TP*>(a.params.p[q]) + e;
+#pragma unroll
+          for (int h = 0; h < PV; ++h) st_peer_v4(dst + h * VP::kN, o[h].raw);
+        }
+      }
+    }
+  }
+  if (a.epoch) {
+    // all blocks done -> the last one publishes "my slice is everywhere" and waits for everybody else's
+    __shared__ bool last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t* cnt = reinterpret_cast<uint32_t*>(a.sig.p[a.rank]) + kSigBlocks;
+      last = (atomicAdd(cnt, 1u) == gridDim.x - 1);
+      if (last) *cnt = 0;
+    }
+    __syncthreads();
+    if (last) rank_barrier(a.sig, a.rank, R, kSigOut, a.epoch, true);
+  }
+}
+
+// ---------------------------------------------------------------- standalone all-gather (push own shard to everybody)
+struct GatherArgs {
+  PeerPtrs bufs;
+  PeerPtrs sig;
+  long n_bytes;          // bytes in the buffer
+  long shard_bytes;      // bytes per rank slice (multiple of 16)
+  int rank, R;
+  uint32_t epoch;
+};
+
+__global__ void __launch_bounds__(512) allgather_push_kernel(const GatherArgs a) {
+  const long lo = (long)a.rank * a.shard_bytes, hi = min(a.n_bytes, lo + a.shard_bytes);
+  const long nvec = hi > lo ? (hi - lo) / 16 : 0;
+  const char* src = reinterpret_cast<const char*>(a.bufs.p[a.rank]) + lo;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+    uint4 v = *reinterpret_cast<const uint4*>(src + i * 16);
+    for (int q = 0; q < a.R; ++q)
+      if (q != a.rank) st_peer_v4(reinterpret_cast<char*>(a.bufs.p[q]) + lo + i * 16, v);
+  }
+  if (a.epoch) {
+    __shared__ bool last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t* cnt = reinterpret_cast<uint32_t*>(a.sig.p[a.rank]) + kSigBlocks;
+      last = (atomicAdd(cnt, 1u) == gridDim.x - 1);
+      if (last) *cnt = 0;
+    }
+    __syncthreads();
+    if (last) rank_barrier(a.sig, a.rank, a.R, kSigOut, a.epoch, true);
+  }
+}
+
+// Cross-rank barrier on its own (bootstrap, tests, end of async runs).
+__global__ void barrier_kernel(PeerPtrs sig, int rank, int R, uint32_t epoch) { rank_barrier(sig, rank, R, kSigIn, epoch, true); }
+
+// ---------------------------------------------------------------- async: push / apply / pull
+// Per-rank async control block (uint32 words at kAsyncBase in the signal pad of the OWNER rank):
+//   [0] version   : number of gradients applied to this shard so far (the device-side staleness counter)
+//   [1] active    : index (0/1) of the accumulation buffer currently open for pushes
+//   [2],[3]       : in-flight pusher count per buffer
+//   [4],[5]       : arrived (complete) pushes per buffer
+//   [6] applied   : total gradients applied           [7] dropped_here : pushes refused by the staleness guard
+constexpr int kAsyncBase = 32;
+enum { A_VERSION = 0, A_ACTIVE = 1, A_INFLIGHT = 2, A_ARRIVED = 4, A_APPLIED = 6, A_DROPPED = 7, A_MAXSEEN = 8 };
+
+struct AsyncPushArgs {
+  const void* grad;      // this worker's full gradient, TG, n elements (local)
+  PeerPtrs acc0, acc1;   // owner accumulation buffers (fp32, shard elements each) on every rank
+  PeerPtrs sig;
+  const uint32_t* seen_version;   // [R] shard versions this worker's weights were pulled at (local device memory)
+  uint32_t* push_state;  // [R] scratch: chosen buffer per owner, or 0xffffffff if refused (local device memory)
+  long n, shard;
+  int rank, R;
+  int max_staleness;
+  float scale;           // multiplies the gradient (1.0, or 1/(1+staleness) is applied per owner when policy = scale)
+  int policy_scale;
+};
+
+// Phase 1 (one block): per owner, read its version, apply the staleness guard, register as in-flight pusher.
+__global__ void async_push_begin_kernel(const AsyncPushArgs a) {
+  const int o = threadIdx.x;
+  if (o >= a.R) return;
+  uint32_t* ctl = reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase;
+  const uint32_t ver = ld_acquire_sys(ctl + A_VERSION);
+  const int staleness = (int)(ver - a.seen_version[o]);
+  if (staleness > a.max_staleness) {
+    atomicAdd_system(ctl + A_DROPPED, 1u);
+    a.push_state[o] = 0xffffffffu;
+    a.push_state[kMaxRanks + o] = (uint32_t)staleness;
+    return;
+  }
+  uint32_t b;
+  while (true) {                                        // register on the buffer that is open *now*
+    b = ld_acquire_sys(ctl + A_ACTIVE) & 1u;
+    atomicAdd_system(ctl + A_INFLIGHT + b, 1u);
+    __threadfence_system();
+    if ((ld_acquire_sys(ctl + A_ACTIVE) & 1u) == b) break;
+    atomicSub_system(ctl + A_INFLIGHT + b, 1u);         // the owner flipped in between: retry on the new one
+  }
+  a.push_state[o] = b;
+  a.push_state[kMaxRanks + o] = (uint32_t)staleness;
+  atomicMax_system(ctl + A_MAXSEEN, (uint32_t)staleness);
+}
+
+// Phase 2: add every slice of the gradient into its owner's open accumulation buffer with P2P reductions.
+template <typename TG>
+__global__ void __launch_bounds__(512) async_push_data_kernel(const AsyncPushArgs a) {
+  using VG = Vec16<TG>;
+  const long nv = (a.n + VG::kN - 1) / VG::kN;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+    const long e = i * VG::kN;
+    const int o = (int)(e / a.shard);
+    const uint32_t b = a.push_state[o];
+    if (b == 0xffffffffu) continue;
+    float sc = a.scale;
+    if (a.policy_scale) sc *= 1.f / (1.f + (float)a.push_state[kMaxRanks + o]);
+    VG g;
+    g.raw = *reinterpret_cast<const uint4*>(reinterpret_cast<const TG*>(a.grad) + e);
+    float* dst = reinterpret_cast<float*>(b ? a.acc1.p[o] : a.acc0.p[o]) + (e - (long)o * a.shard);
+    if constexpr (VG::kN == 8) {
+      red_add_v4_f32_sys(dst, g.get(0) * sc, g.get(1) * sc, g.get(2) * sc, g.get(3) * sc);
+      red_add_v4_f32_sys(dst + 4, g.get(4) * sc, g.get(5) * sc, g.get(6) * sc, g.get(7) * sc);
+    } else {
+      red_add_v4_f32_sys(dst, g.get(0) * sc, g.get(1) * sc, g.get(2) * sc, g.get(3) * sc);
+    }
+  }
+}
+
+// Phase 3 (one block): publish completion — arrived++ then inflight-- on every owner we pushed to.
+__global__ void async_push_end_kernel(const AsyncPushArgs a) {
+  const int o = threadIdx.x;
+  if (o >= a.R) return;
+  const uint32_t b = a.push_state[o];
+  if (b == 0xffffffffu) return;
+  uint32_t* ctl = reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase;
+  __threadfence_system();
+  atomicAdd_system(ctl + A_ARRIVED + b, 1u);
+  __threadfence_system();
+  atomicSub_system(ctl + A_INFLIGHT + b, 1u);
+}
+
+struct AsyncApplyArgs {
+  float* acc0;           // local accumulation buffers (fp32, shard elements)
+  float* acc1;
+  uint32_t* ctl;         // local control block (signal pad + kAsyncBase)
+  float* master;         // fp32 master shard
+  float* m;
+  float* v;
+  void* param_shard;     // this rank's slice inside its own working-weight buffer (TP)
+  uint32_t* scratch;     // [2] device scratch: {buffer to drain, count}
+  long shard_elems;
+  OptParams opt;
+};
+
+// Phase 1 (one block, one thread): flip the open buffer, wait until nobody is still adding into the closed one.
+__global__ void async_apply_begin_kernel(const AsyncApplyArgs a) {
+  if (threadIdx.x != 0) return;
+  const uint32_t old = ld_acquire_sys(a.ctl + A_ACTIVE) & 1u;
+  if (ld_acquire_sys(a.ctl + A_ARRIVED + old) == 0 && ld_acquire_sys(a.ctl + A_INFLIGHT + old) == 0) {
+    a.scratch[0] = old;
+    a.scratch[1] = 0;                                   // nothing to apply
+    return;
+  }
+  st_release_sys(a.ctl + A_ACTIVE, old ^ 1u);
+  __threadfence_system();
+  while (ld_acquire_sys(a.ctl + A_INFLIGHT + old) != 0) {
+  }                                                     // pushers are running kernels that never wait: bounded
+  a.scratch[0] = old;
+  a.scratch[1] = ld_acquire_sys(a.ctl + A_ARRIVED + old);
+}
+
+// Phase 2: apply the accumulated gradient sum in place, refresh the working-weight slice, clear the buffer.
+template <typename TP>
+__global__ void __launch_bounds__(512) async_apply_data_kernel(const AsyncApplyArgs a) {
+  const uint32_t cnt = a.scratch[1];
+  if (cnt == 0) return;
+  float* acc = a.scratch[0] ? a.acc1 : a.acc0;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < a.shard_elems; i += (long)gridDim.x * blockDim.x) {
+    float g = acc[i];
+    acc[i] = 0.f;
+    float mm = a.m ? a.m[i] : 0.f, vv = a.v ? a.v[i] : 0.f;
+    float w = opt_step(a.master[i], g, &mm, &vv, a.opt);
+    a.master[i] = w;
+    if (a.m && a.opt.kind != OPT_SGD) a.m[i] = mm;
+    if (a.v && a.opt.kind == OPT_ADAM) a.v[i] = vv;
+    reinterpret_cast<TP*>(a.param_shard)[i] = from_f32<TP>(w);
+  }
+}
+
+// Phase 3 (one thread): version += count, arrived = 0.
+__global__ void async_apply_end_kernel(const AsyncApplyArgs a) {
+  if (threadIdx.x != 0) return;
+  const uint32_t cnt = a.scratch[1];
+  if (cnt == 0) return;
+  const uint32_t b = a.scratch[0];
+  atomicExch_system(a.ctl + A_ARRIVED + b, 0u);
+  atomicAdd_system(a.ctl + A_APPLIED, cnt);
+  __threadfence_system();
+  atomicAdd_system(a.ctl + A_VERSION, cnt);             // publish last: a reader that sees the version sees the weights
+}
+
+struct AsyncPullArgs {
+  PeerPtrs params;       // working-weight buffers on every rank (each rank's OWN slice is authoritative)
+  PeerPtrs sig;
+  void* dst;             // local working-weight buffer (full model)
+  uint32_t* seen_version;  // [R] out
+  long n_bytes, shard_bytes;
+  int rank, R;
+};
+
+__global__ void __launch_bounds__(512) async_pull_kernel(const AsyncPullArgs a) {
+  if (blockIdx.x == 0 && threadIdx.x < a.R)             // version first: staleness is then never under-estimated
+    a.seen_version[threadIdx.x] = ld_acquire_sys(reinterpret_cast<const uint32_t*>(a.sig.p[threadIdx.x]) + kAsyncBase + A_VERSION);
+  __syncthreads();
+  const long nv = a.n_bytes / 16;
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < nv; i += (long)gridDim.x * blockDim.x) {
+    const long off = i * 16;
+    const int o = (int)(off / a.shard_bytes);
+    if (o == a.rank) continue;                          // own slice is already in place
+    uint4 v = ld_peer_v4(reinterpret_cast<const char*>(a.params.p[o]) + off);
+    *reinterpret_cast<uint4*>(reinterpret_cast<char*>(a.dst) + off) = v;
+  }
+}
+
+// ---------------------------------------------------------------- device work queue (dataset dispatcher)
+// Words at kWqBase in the signal pad of the queue's home rank:
+//   [0] ticket (next fresh batch of this epoch)   [1] completed count   [2] epoch   [3] batches   [4] epochs
+//   [5] done flag   [6] reissue cursor            [16 ...] completion bitmap (1 bit per batch)
+constexpr int kWqBase = 64;
+enum { W_TICKET = 0, W_COMPLETED = 1, W_EPOCH = 2, W_BATCHES = 3, W_EPOCHS = 4, W_DONE = 5, W_CURSOR = 6, W_LOCK = 7, W_BITMAP = 16 };
+
+__global__ void wq_init_kernel(uint32_t* wq, uint32_t batches, uint32_t epochs, int bitmap_words) {
+  for (int i = threadIdx.x; i < W_BITMAP + bitmap_words; i += blockDim.x) wq[i] = 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    wq[W_BATCHES] = batches;
+    wq[W_EPOCHS] = epochs;
+  }
+}
+
+// One thread takes a ticket.  out[0] = batch index or 0xffffffff when the dataset is exhausted, out[1] = epoch.
+// FCFS in index order; when the fresh tickets of the epoch are gone, still-incomplete batches are re-issued
+// (round-robin scan of the bitmap) exactly like DistributedDataset.next() (dataset.ts:57-60).
+__global__ void wq_take_kernel(uint32_t* wq, uint32_t* out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  while (true) {
+    if (ld_acquire_sys(wq + W_DONE)) { out[0] = 0xffffffffu; out[1] = ld_acquire_sys(wq + W_EPOCH); return; }
+    const uint32_t batches = wq[W_BATCHES];
+    const uint32_t epoch = ld_acquire_sys(wq + W_EPOCH);
+    const uint32_t t = atomicAdd_system(wq + W_TICKET, 1u);
+    if (t < batches) {
+      if (ld_acquire_sys(wq + W_EPOCH) == epoch) { out[0] = t; out[1] = epoch; return; }
+      continue;                                       // epoch rolled over under us: take again
+    }
+    // fresh ones ran out: re-issue something still incomplete
+    const uint32_t start = atomicAdd_system(wq + W_CURSOR, 1u);
+    for (uint32_t k = 0; k < batches; ++k) {
+      const uint32_t b = (start + k) % batches;
+      const uint32_t word = ld_acquire_sys(wq + W_BITMAP + (b >> 5));
+      if (!((word >> (b & 31)) & 1u)) {
+        if (ld_acquire_sys(wq + W_EPOCH) != epoch) break;
+        out[0] = b; out[1] = epoch; return;
+      }
+    }
+    // everything complete (or epoch rolled): loop and look again
+  }
+}
+
+// Mark `batch` of `epoch` complete (idempotent).  The completion that finishes the epoch advances it.
+__global__ void wq_complete_kernel(uint32_t* wq, const uint32_t* ticket) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const uint32_t b = ticket[0], epoch = ticket[1];
+  if (b == 0xffffffffu) return;
+  if (ld_acquire_sys(wq + W_EPOCH) != epoch) return;    // stale completion from a previous epoch: ignored
+  const uint32_t bit = 1u << (b & 31);
+  const uint32_t old = atomicOr_system(wq + W_BITMAP + (b >> 5), bit);
+  if (old & bit) return;                                // duplicate
+  const uint32_t batches = wq[W_BATCHES];
+  const uint32_t done = atomicAdd_system(wq + W_COMPLETED, 1u) + 1;
+  if (done == batches) {                                // last one of the epoch: roll over
+    const int words = (batches + 31) / 32;
+    if (epoch + 1 >= wq[W_EPOCHS]) {
+      st_release_sys(wq + W_DONE, 1u);
+    } else {
+      for (int i = 0; i < words; ++i) atomicExch_system(wq + W_BITMAP + i, 0u);
+      atomicExch_system(wq + W_COMPLETED, 0u);
+      atomicExch_system(wq + W_CURSOR, 0u);
+      atomicExch_system(wq + W_TICKET, 0u);
+      __threadfence_system();
+      st_release_sys(wq + W_EPOCH, epoch + 1);
+    }
+  }
+}
+
+// Gather the rows of batch `ticket[0]` from a device-resident dataset: dst[r, :] = src[(b*bs + r) % rows, :].
+__global__ void __launch_bounds__(256) gather_batch_kernel(const char* __restrict__ src, char* __restrict__ dst,
+                                                           const uint32_t* __restrict__ ticket, long row_bytes, int batch_size,
+                                                           long rows) {
+  const uint32_t b = ticket[0];
+  if (b == 0xffffffffu) return;
+  const long vec_per_row = row_bytes / 16;
+  const long total = vec_per_row * batch_size;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+    const long r = i / vec_per_row, c = i - r * vec_per_row;
+    const long sr = ((long)b * batch_size + r) % rows;
+    reinterpret_cast<uint4*>(dst + r * row_bytes)[c] = reinterpret_cast<const uint4*>(src + sr * row_bytes)[c];
+  }
+}
+
+}  // namespace dfb
+
+using namespace dfb;
+
+// ============================================================================================ C ABI
+DFB_API int dfb_symm_alloc(size_t bytes, void** base_out) {
+  void* p = nullptr;
+  DFB_CUDA_CHECK(cudaMalloc(&p, bytes));
+  DFB_CUDA_CHECK(cudaMemset(p, 0, bytes));
+  DFB_CUDA_CHECK(cudaDeviceSynchronize());
+  *base_out = p;
+  return 0;
+}
+DFB_API int dfb_symm_free(void* base) {
+  DFB_CUDA_CHECK(cudaFree(base));
+  return 0;
+}
+DFB_API int dfb_symm_get_handle(void* base, void* handle_out64) {
+  cudaIpcMemHandle_t h;
+  DFB_CUDA_CHECK(cudaIpcGetMemHandle(&h, base));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t size");
+  memcpy(handle_out64, &h, 64);
+  return 0;
+}
+DFB_API int dfb_symm_open_handle(const void* handle64, void** peer_ptr_out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DFB_CUDA_CHECK(cudaIpcOpenMemHandle(peer_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+DFB_API int dfb_symm_close_handle(void* peer_ptr) {
+  DFB_CUDA_CHECK(cudaIpcCloseMemHandle(peer_ptr));
+  return 0;
+}
+DFB_API int dfb_enable_peer_access(int peer_device) {
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return 0;
+  }
+  DFB_CUDA_CHECK(e);
+  return 0;
+}
+
+static void fill_peers(PeerPtrs& d, void* const* src, int R) {
+  for (int i = 0; i < kMaxRanks; ++i) d.p[i] = i < R ? src[i] : nullptr;
+}
+
+// Fused reduce-scatter + 1/R + optimizer + all-gather for one bucket.  grads/params/sig: arrays of R base pointers
+// (peer-mapped).  master/m/v: local fp32 slices.  grad_dtype/param_dtype: DT_*.  epoch = 0 disables the cross-rank
+// barriers (single-GPU emulation: launch once per rank, in any order, gradients must already be final).
+DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
+                               void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
+                               int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
+                               float weight_decay, int step, int ctas, cudaStream_t stream) {
+  DFB_REQUIRE(R >= 1 && R <= kMaxRanks && rank >= 0 && rank < R, "sync: bad rank %d / world %d", rank, R);
+  DFB_REQUIRE(shard > 0 && (shard % 8) == 0, "sync: shard must be a positive multiple of 8 elements");
+  DFB_REQUIRE(shard * R >= n, "sync: shard * R must cover the bucket");
+  DFB_REQUIRE(opt_kind >= 0 && opt_kind <= 3, "sync: optimizer kind");
+  SyncArgs a;
+  fill_peers(a.grads, grads, R);
+  fill_peers(a.params, params, R);
+  if (sig) fill_peers(a.sig, sig, R); else memset(&a.sig, 0, sizeof(a.sig));
+  DFB_REQUIRE(epoch == 0 || sig != nullptr, "sync: barriers need signal pads");
+  a.master = master; a.m = m; a.v = v; a.reduced_out = reduced_out; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
+  a.epoch = epoch; a.push = push;
+  a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
+  a.opt.weight_decay = weight_decay;
+  a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));
+  a.opt.bias_c2 = 1.f - powf(beta2, (float)(step < 1 ? 1 : step));
+  DFB_REQUIRE(opt_kind == OPT_SGD || opt_kind == OPT_NONE || m != nullptr, "sync: optimizer state missing");
+  DFB_REQUIRE(opt_kind != OPT_ADAM || v != nullptr, "sync: Adam second moment missing");
+  const long lo = (long)rank * shard, hi = lo + shard < n ? lo + shard : n;
+  long nvec = hi > lo ? (hi - lo + 7) / 8 : 0;
+  int grid = ctas > 0 ? ctas : 32;
+  long need = (nvec + 511) / 512;
+  if (need < 1) need = 1;
+  if (grid > need) grid = (int)need;
+#define DFB_SYNC_LAUNCH(TG, TP)                                                     \
+  do {                                                                               \
+    if (R == 8) sync_rs_opt_ag_kernel<TG, TP, 8><<<grid, 512, 0, stream>>>(a);       \
+    else if (R == 4) sync_rs_opt_ag_kernel<TG, TP, 4><<<grid, 512, 0, stream>>>(a);  \
+    else if (R == 2) sync_rs_opt_ag_kernel<TG, TP, 2><<<grid, 512, 0, stream>>>(a);  \
+    else sync_rs_opt_ag_kernel<TG, TP, 0><<<grid, 512, 0, stream>>>(a);              \
+  } while (0)
+  if (grad_dtype == DT_BF16 && param_dtype == DT_BF16) DFB_SYNC_LAUNCH(__nv_bfloat16, __nv_bfloat16);
+  else if (grad_dtype == DT_F32 && param_dtype == DT_F32) DFB_SYNC_LAUNCH(float, float);
+  else if (grad_dtype == DT_F32 && param_dtype == DT_BF16) DFB_SYNC_LAUNCH(float, __nv_bfloat16);
+  else if (grad_dtype == DT_BF16 && param_dtype == DT_F32) DFB_SYNC_LAUNCH(__nv_bfloat16, float);
+  else {
+    set_error("sync: unsupported dtypes grad=%d param=%d", grad_dtype, param_dtype);
+    return 2;
+  }
+#undef DFB_SYNC_LAUNCH
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R,
+                               unsigned epoch, int ctas, cudaStream_t stream) {
+  DFB_REQUIRE(R >= 1 && R <= kMaxRanks && (shard_bytes % 16) == 0, "allgather: bad arguments");
+  GatherArgs a;
+  fill_peers(a.bufs, bufs, R);
+  if (sig) fill_peers(a.sig, sig, R); else memset(&a.sig, 0, sizeof(a.sig));
+  a.n_bytes = n_bytes; a.shard_bytes = shard_bytes; a.rank = rank; a.R = R; a.epoch = epoch;
+  int grid = ctas > 0 ? ctas : 32;
+  allgather_push_kernel<<<grid, 512, 0, stream>>>(a);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, cudaStream_t stream) {
+  PeerPtrs s;
+  fill_peers(s, sig, R);
+  barrier_kernel<<<1, 32, 0, stream>>>(s, rank, R, epoch);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void* const* sig,
+                           const unsigned* seen_version, unsigned* push_state, long n, long shard, int rank, int R,
+                           int max_staleness, float scale, int policy_scale, int grad_dtype, int ctas, cudaStream_t stream) {
+  DFB_REQUIRE(R >= 1 && R <= kMaxRanks && (shard % 8) == 0, "async_push: bad arguments");
+  AsyncPushArgs a;
+  a.grad = grad;
+  fill_peers(a.acc0, acc0, R);
+  fill_peers(a.acc1, acc1, R);
+  fill_peers(a.sig, sig, R);
+  a.seen_version = seen_version; a.push_state = push_state; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
+  a.max_staleness = max_staleness; a.scale = scale; a.policy_scale = policy_scale;
+  async_push_begin_kernel<<<1, 32, 0, stream>>>(a);
+  int grid = ctas > 0 ? ctas : 32;
+  if (grad_dtype == DT_BF16) async_push_data_kernel<__nv_bfloat16><<<grid, 512, 0, stream>>>(a);
+  else if (grad_dtype == DT_F32) async_push_data_kernel<float><<<grid, 512, 0, stream>>>(a);
+  else {
+    set_error("async_push: dtype");
+    return 2;
+  }
+  async_push_end_kernel<<<1, 32, 0, stream>>>(a);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
+                            unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum,
+                            float beta1, float beta2, float eps, float weight_decay, int step, int ctas, cudaStream_t stream) {
+  AsyncApplyArgs a;
+  a.acc0 = acc0; a.acc1 = acc1; a.ctl = ctl_pad + kAsyncBase; a.master = master; a.m = m; a.v = v; a.param_shard = param_shard;
+  a.scratch = scratch; a.shard_elems = shard_elems;
+  a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
+  a.opt.weight_decay = weight_decay;
+  a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));
+  a.opt.bias_c2 = 1.f - powf(beta2, (float)(step < 1 ? 1 : step));
+  async_apply_begin_kernel<<<1, 32, 0, stream>>>(a);
+  int grid = ctas > 0 ? ctas : 32;
+  if (param_dtype == DT_BF16) async_apply_data_kernel<__nv_bfloat16><<<grid, 512, 0, stream>>>(a);
+  else if (param_dtype == DT_F32) async_apply_data_kernel<float><<<grid, 512, 0, stream>>>(a);
+  else {
+    set_error("async_apply: dtype");
+    return 2;
+  }
+  async_apply_end_kernel<<<1, 32, 0, stream>>>(a);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_async_pull(void* const* params, void* const* sig, void* dst, unsigned* seen_version, long n_bytes,
+                           long shard_bytes, int rank, int R, int ctas, cudaStream_t stream) {
+  DFB_REQUIRE(R >= 1 && R <= kMaxRanks && (shard_bytes % 16) == 0 && (n_bytes % 16) == 0, "async_pull: bad arguments");
+  AsyncPullArgs a;
+  fill_peers(a.params, params, R);
+  fill_peers(a.sig, sig, R);
+  a.dst = dst; a.seen_version = seen_version; a.n_bytes = n_bytes; a.shard_bytes = shard_bytes; a.rank = rank; a.R = R;
+  int grid = ctas > 0 ? ctas : 32;
+  async_pull_kernel<<<grid, 512, 0, stream>>>(a);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Read the async counters of a control block into host-visible words: out[0..8] = version, active, inflight0/1,
+// arrived0/1, applied, dropped, max staleness seen.  (cudaMemcpyAsync from the pad; the caller synchronises.)
+DFB_API int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, cudaStream_t stream) {
+  DFB_CUDA_CHECK(cudaMemcpyAsync(host_out9, ctl_pad + kAsyncBase, 9 * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  return 0;
+}
+
+DFB_API int dfb_wq_init(unsigned* pad, unsigned batches, unsigned epochs, cudaStream_t stream) {
+  const int words = (int)((batches + 31) / 32);
+  wq_init_kernel<<<1, 256, 0, stream>>>(pad + kWqBase, batches, epochs, words);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+DFB_API int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, cudaStream_t stream) {
+  wq_take_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket_out2);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+DFB_API int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, cudaStream_t stream) {
+  wq_complete_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket2);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+DFB_API int dfb_wq_pad_words(unsigned batches) { return kWqBase + W_BITMAP + (int)((batches + 31) / 32); }
+DFB_API int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
+                             cudaStream_t stream) {
+  DFB_REQUIRE((row_bytes % 16) == 0, "gather_batch: row size must be a multiple of 16 bytes");
+  long total = row_bytes / 16 * batch_size;
+  long blocks = (total + 255) / 256;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  if (blocks < 1) blocks = 1;
+  gather_batch_kernel<<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, ticket, row_bytes, batch_size, rows);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,324 @@
+"""DataParallelEngine: every worker is a GPU rank, the server is sharded across the ranks.
+
+Roles of the reference mapped onto one 8xB200 box:
+  * `FederatedServer.updateModel` — stack K uploads, mean, SGD step, broadcast
+    (`/root/reference/src/server/federated_server.ts:92-116`) — is ONE kernel per gradient bucket
+    (`csrc/comm.cu: sync_rs_opt_ag_kernel`): rank r owns slice r of every bucket (fp32 master weights +
+    optimizer state), pulls that slice of all ranks' gradients over NVLink, applies the optimizer and pushes
+    the refreshed working weights to everybody.  Buckets are launched on a side stream as soon as backward
+    has produced them, so the collective overlaps the rest of backward.
+  * `DistributedTfModel.fit` (`/root/reference/src/common/models.ts:137-142`) is the user's `loss_fn` +
+    `backward`; weight-gradient GEMMs write straight into the flat gradient bucket (`_dfb_grad_sink`).
+  * `model.version` / `savedGradient` / `maximumStaleness` (`/root/reference/README.md:23-30`) are
+    `engine.version`, the gradient buckets, and the async engine's device-side staleness guard.
+
+Back ends: "p2p" = own kernels over peer memory (the product); "nccl" / "gloo" = bucketed
+`torch.distributed.all_reduce` + the same optimizer math in PyTorch (baseline, and CPU plumbing).
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from ..config import engine_config
+
+__all__ = ["DataParallelEngine", "Bucket"]
+
+_TORCH_DT = {"bf16": torch.bfloat16, "fp32": torch.float32}
+_OPT = {"sgd": 0, "momentum": 1, "adam": 2, "none": 3}
+_ALIGN = 64          # elements; every parameter starts 128-byte aligned inside its bucket (TMA needs 16)
+
+
+class Bucket:
+    def __init__(self, index: int):
+        self.index = index
+        self.params: List[nn.Parameter] = []
+        self.offsets: List[int] = []
+        self.numel = 0            # padded to world * shard
+        self.shard = 0
+        self.param_off = 0        # byte offsets inside the symmetric heap
+        self.grad_off = 0
+        self.param_buf: Optional[torch.Tensor] = None
+        self.grad_buf: Optional[torch.Tensor] = None
+        self.master: Optional[torch.Tensor] = None
+        self.m: Optional[torch.Tensor] = None
+        self.v: Optional[torch.Tensor] = None
+        self.pending = 0
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class DataParallelEngine:
+    def __init__(self, model: nn.Module, loss_fn: Callable[..., torch.Tensor], config: Optional[Dict[str, Any]] = None,
+                 rank: int = 0, world: int = 1, group=None, device: Optional[torch.device] = None, heap=None):
+        self.cfg = engine_config(config)
+        self.model, self.loss_fn = model, loss_fn
+        self.rank, self.world, self.group = rank, world, group
+        self.device = device or next(model.parameters()).device
+        self.backend = self.cfg["backend"]
+        if self.device.type != "cuda" and self.backend == "p2p":
+            self.backend = "gloo"
+        self.param_dtype = _TORCH_DT[self.cfg["dtype"]] if self.device.type == "cuda" else torch.float32
+        self.grad_dtype = _TORCH_DT[self.cfg["gradDtype"]] if self.device.type == "cuda" else torch.float32
+        self.lr = float(self.cfg["learningRate"])
+        self.version = 0                    # number of optimizer steps applied (model version index)
+        self.maximumStaleness = int(self.cfg["maximumStaleness"])
+        self.comm_ctas = 32
+        self._epoch = 0
+        self._launches = 0                  # own-kernel launches issued by the engine (comm/optimizer kernels)
+        self.versionCallbacks: List[Callable[[int, int], None]] = []
+        self._build_buckets(heap)
+        self._install_hooks()
+        if self.device.type == "cuda":
+            self.comm_stream = torch.cuda.Stream(device=self.device)
+
+    # ------------------------------------------------------------------------------------ setup
+    def _build_buckets(self, heap) -> None:
+        params, seen = [], set()
+        for p in self.model.parameters():
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                params.append(p)
+        params.reverse()                                    # approximate backward order
+        cap = max(1, int(self.cfg["bucketBytes"]) // torch.empty((), dtype=self.grad_dtype).element_size())
+        buckets: List[Bucket] = []
+        cur = Bucket(0)
+        for p in params:
+            n = _round_up(p.numel(), _ALIGN)
+            if cur.params and cur.numel + n > cap:
+                buckets.append(cur)
+                cur = Bucket(len(buckets))
+            cur.params.append(p)
+            cur.offsets.append(cur.numel)
+            cur.numel += n
+        if cur.params:
+            buckets.append(cur)
+        R = self.world
+        psz = torch.empty((), dtype=self.param_dtype).element_size()
+        gsz = torch.empty((), dtype=self.grad_dtype).element_size()
+        total = 0
+        for b in buckets:
+            b.numel = _round_up(b.numel, R * _ALIGN)
+            b.shard = b.numel // R
+            total += _round_up(b.numel * psz, 256) + _round_up(b.numel * gsz, 256)
+        self.heap = None
+        if self.backend == "p2p":
+            from .symm import SymmetricHeap
+            self.heap = heap or SymmetricHeap(total + 4096, self.rank, self.world, self.group, self.device)
+        for b in buckets:
+            flat32 = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
+            for p, off in zip(b.params, b.offsets):
+                flat32[off:off + p.numel()].copy_(p.data.reshape(-1).float())
+            if self.world > 1:
+                import torch.distributed as dist
+                if dist.is_available() and dist.is_initialized():
+                    dist.broadcast(flat32, src=0, group=self.group)      # identical start on every rank (bootstrap)
+            if self.heap is not None:
+                b.param_off = self.heap.alloc(b.numel * psz)
+                b.grad_off = self.heap.alloc(b.numel * gsz)
+                b.param_buf = self.heap.view(b.param_off, (b.numel,), self.param_dtype)
+                b.grad_buf = self.heap.view(b.grad_off, (b.numel,), self.grad_dtype)
+            else:
+                b.param_buf = torch.empty(b.numel, dtype=self.param_dtype, device=self.device)
+                b.grad_buf = torch.zeros(b.numel, dtype=self.grad_dtype, device=self.device)
+            b.param_buf.copy_(flat32)
+            lo = self.rank * b.shard
+            owned = (lo, lo + b.shard) if self.backend == "p2p" else (0, b.numel)
+            b.master = flat32[owned[0]:owned[1]].clone()
+            if self.cfg["optimizer"] in ("momentum", "adam"):
+                b.m = torch.zeros_like(b.master)
+            if self.cfg["optimizer"] == "adam":
+                b.v = torch.zeros_like(b.master)
+            for p, off in zip(b.params, b.offsets):
+                p.data = b.param_buf[off:off + p.numel()].view(p.shape)
+                p.grad = None
+            del flat32
+        self.buckets = buckets
+        self._bucket_of = {id(p): b for b in buckets for p in b.params}
+
+    def _install_hooks(self) -> None:
+        for b in self.buckets:
+            for p, off in zip(b.params, b.offsets):
+                sink = b.grad_buf[off:off + p.numel()]
+                if not getattr(p, "_dfb_shared", False):
+                    p._dfb_grad_sink = sink                    # ops write the weight gradient here and call ready()
+                p._dfb_grad_ready = (lambda bb=b: self._param_ready(bb))
+
+                def hook(param, sink=sink, bb=b):              # parameters whose gradient comes from plain autograd
+                    sink.copy_(param.grad.reshape(-1))
+                    param.grad = None
+                    self._param_ready(bb)
+
+                p.register_post_accumulate_grad_hook(hook)
+
+    # ------------------------------------------------------------------------------------ step
+    def on_new_version(self, cb: Callable[[int, int], None]) -> None:
+        self.versionCallbacks.append(cb)
+
+    def _param_ready(self, b: Bucket) -> None:
+        b.pending -= 1
+        if b.pending == 0 and self.cfg["overlap"]:
+            self._launch_bucket(b)
+
+    def zero_pending(self) -> None:
+        for b in self.buckets:
+            b.pending = len(b.params)
+            b.launched = False
+
+    def step(self, *batch: Any) -> torch.Tensor:
+        """One synchronous data-parallel step: forward, backward (+ overlapped bucket collectives), new version."""
+        self.zero_pending()
+        if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"]:
+            from ..ops import linear as _lin
+            _lin.set_max_ctas(_lin.NUM_SMS - self.comm_ctas)   # leave SMs for the collective kernels during backward
+        loss = self.loss_fn(self.model, *batch)
+        loss.backward()
+        for b in self.buckets:                                 # anything not launched from a hook (unused params, overlap off)
+            if not getattr(b, "launched", False):
+                self._launch_bucket(b)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+            from ..ops import linear as _lin
+            _lin.set_max_ctas(0)
+        old = self.version
+        self.version += 1
+        for cb in self.versionCallbacks:
+            cb(old, self.version)
+        return loss.detach()
+
+    def _launch_bucket(self, b: Bucket) -> None:
+        b.launched = True
+        if self.backend == "p2p":
+            self._launch_bucket_p2p(b)
+        else:
+            self._launch_bucket_torch(b)
+
+    def _launch_bucket_p2p(self, b: Bucket) -> None:
+        from ..ops import _lib
+        from ..ops._lib import check, dt, ptr
+        L = _comm_sigs()
+        main = torch.cuda.current_stream()
+        self.comm_stream.wait_stream(main)
+        epoch = 0
+        if self.world > 1:
+            self._epoch += 1
+            epoch = self._epoch
+        c = self.cfg
+        with torch.cuda.stream(self.comm_stream):
+            check(L.dfb_sync_rs_opt_ag(self.heap.ptrs(b.grad_off), self.heap.ptrs(b.param_off), self.heap.ptrs(0),
+                                       ptr(b.master), ptr(b.m), ptr(b.v), None, b.numel, b.shard, self.rank, self.world,
+                                       epoch, 1, dt(b.grad_buf), dt(b.param_buf), _OPT[c["optimizer"]], self.lr,
+                                       c["momentum"], c["beta1"], c["beta2"], c["eps"], c["weightDecay"], self.version + 1,
+                                       self.comm_ctas if self.world > 1 else 148 * 2, _lib.stream()), "dfb_sync_rs_opt_ag")
+        self._launches += 1
+
+    def _launch_bucket_torch(self, b: Bucket) -> None:
+        """Baseline path: all-reduce (NCCL/gloo) + the same optimizer math in PyTorch on a full fp32 master."""
+        g = b.grad_buf
+        if self.world > 1:
+            import torch.distributed as dist
+            g32 = g.float() if self.device.type != "cuda" else g
+            dist.all_reduce(g32, group=self.group)
+            g = g32
+        g = g.float() / self.world
+        c = self.cfg
+        if c["weightDecay"]:
+            g = g + c["weightDecay"] * b.master
+        if c["optimizer"] == "sgd":
+            b.master.add_(g, alpha=-self.lr)
+        elif c["optimizer"] == "momentum":
+            b.m.mul_(c["momentum"]).add_(g)
+            b.master.add_(b.m, alpha=-self.lr)
+        else:
+            t = self.version + 1
+            b.m.mul_(c["beta1"]).add_(g, alpha=1 - c["beta1"])
+            b.v.mul_(c["beta2"]).addcmul_(g, g, value=1 - c["beta2"])
+            mh = b.m / (1 - c["beta1"] ** t)
+            vh = b.v / (1 - c["beta2"] ** t)
+            b.master.addcdiv_(mh, vh.sqrt().add_(c["eps"]), value=-self.lr)
+        b.param_buf.copy_(b.master)
+
+    # ------------------------------------------------------------------------------------ state
+    def full_precision_weights(self) -> List[torch.Tensor]:
+        """fp32 master weights of every parameter, in `model.parameters()` order (gathers the shards)."""
+        out: Dict[int, torch.Tensor] = {}
+        for b in self.buckets:
+            if self.backend == "p2p" and self.world > 1:
+                import torch.distributed as dist
+                parts = [torch.empty_like(b.master) for _ in range(self.world)]
+                dist.all_gather(parts, b.master, group=self.group)
+                flat = torch.cat(parts)
+            else:
+                flat = b.master if b.master.numel() == b.numel else torch.cat([b.master])
+            for p, off in zip(b.params, b.offsets):
+                out[id(p)] = flat[off:off + p.numel()].view(p.shape).clone()
+        seen, res = set(), []
+        for p in self.model.parameters():
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                res.append(out[id(p)])
+        return res
+
+    def save_checkpoint(self, directory: str) -> Optional[str]:
+        """Write the tf.js LayersModel layout from the fp32 master weights (rank 0 writes)."""
+        weights = self.full_precision_weights()
+        if self.rank != 0:
+            return None
+        from ..checkpoint import save_layers_model
+        live = [p for p in self.model.parameters() if p.requires_grad]
+        saved = [p.data for p in live]
+        try:
+            for p, w in zip(live, weights):
+                p.data = w
+            return save_layers_model(self.model, directory)
+        finally:
+            for p, d in zip(live, saved):
+                p.data = d
+
+    def gpu_launches_per_step(self) -> int:
+        return len(self.buckets)
+
+
+def _comm_sigs():
+    import ctypes
+    from ..ops import _lib
+    from ..ops._lib import c_float, c_int, c_void_p
+    L = _lib.lib()
+    if not getattr(L, "_dfb_comm_sigs", False):
+        P = ctypes.POINTER(c_void_p)
+        L.dfb_sync_rs_opt_ag.restype = c_int
+        L.dfb_sync_rs_opt_ag.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int,
+                                         c_int, ctypes.c_uint, c_int, c_int, c_int, c_int, c_float, c_float, c_float, c_float,
+                                         c_float, c_float, c_int, c_int, c_void_p]
+        L.dfb_allgather_push.restype = c_int
+        L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
+        L.dfb_rank_barrier.restype = c_int
+        L.dfb_rank_barrier.argtypes = [P, c_int, c_int, ctypes.c_uint, c_void_p]
+        L.dfb_async_push.restype = c_int
+        L.dfb_async_push.argtypes = [c_void_p, P, P, P, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int, c_int,
+                                     c_float, c_int, c_int, c_int, c_void_p]
+        L.dfb_async_apply.restype = c_int
+        L.dfb_async_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      ctypes.c_long, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int,
+                                      c_int, c_void_p]
+        L.dfb_async_pull.restype = c_int
+        L.dfb_async_pull.argtypes = [P, P, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int, c_int, c_void_p]
+        L.dfb_async_read_ctl.restype = c_int
+        L.dfb_async_read_ctl.argtypes = [c_void_p, c_void_p, c_void_p]
+        L.dfb_wq_init.restype = c_int
+        L.dfb_wq_init.argtypes = [c_void_p, ctypes.c_uint, ctypes.c_uint, c_void_p]
+        L.dfb_wq_take.restype = c_int
+        L.dfb_wq_take.argtypes = [c_void_p, c_void_p, c_void_p]
+        L.dfb_wq_complete.restype = c_int
+        L.dfb_wq_complete.argtypes = [c_void_p, c_void_p, c_void_p]
+        L.dfb_wq_pad_words.restype = c_int
+        L.dfb_wq_pad_words.argtypes = [ctypes.c_uint]
+        L.dfb_gather_batch.restype = c_int
+        L.dfb_gather_batch.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_long, c_int, ctypes.c_long, c_void_p]
+        L._dfb_comm_sigs = True
+    return L

@@ -1,0 +1,108 @@
+/* C ABI of libdistriflow_b200.so (distriflow_b200/ops/libdistriflow_b200.so).
+ *
+ * Every function returns 0 on success; on failure a non-zero code, with a message from dfb_last_error().
+ * Pointers are device pointers unless stated otherwise.  `stream` is a cudaStream_t passed as void*.
+ * dtype codes: 0 = fp32, 1 = bf16, 2 = fp16.  activation codes: 0 = none, 1 = relu, 2 = gelu (tanh form).
+ * The reference (/root/reference) has no native code; each entry names the tf.js call site it replaces.
+ */
+#ifndef DISTRIFLOW_B200_H_
+#define DISTRIFLOW_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dfb_last_error(void);
+int dfb_version(void);
+
+/* ---- Dense GEMM, tcgen05 + TMEM + TMA (csrc/gemm_sm100.cu) --------------------------------------------
+ * D[M,N] = act(A * B^T + bias).  A is [M,K] (a_mn_major = 0, pitch lda) or [K,M] (a_mn_major = 1);
+ * B is [N,K] (b_mn_major = 0, pitch ldb) or [K,N] (b_mn_major = 1).  bf16 inputs, fp32 accumulate, bf16 or
+ * fp32 output.  block_n in {128, 256}.  splits > 1 = split-K through `workspace` (fp32 scratch of
+ * dfb_gemm_workspace_bytes bytes) followed by a reduce kernel.  max_ctas > 0 caps the persistent grid.
+ * Replaces predictOnBatch / variableGrads on Dense layers: /root/reference/src/common/models.ts:137-142. */
+size_t dfb_gemm_workspace_bytes(int M, int N, int splits);
+int dfb_gemm_pick_splits(int M, int N, int K, int block_n, int sms);
+int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda,
+                  int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits,
+                  void* workspace, size_t workspace_bytes, int max_ctas, void* stream);
+
+/* ---- CUDA-core GEMM for fp32 / tiny-N / unaligned shapes (csrc/gemm_simt.cu) ---------------------------
+ * D[m,n] = act(sum_k A[m*sa_m + k*sa_k] * B[n*sb_n + k*sb_k] + bias[n]).  The MNIST heads Dense(10), Dense(5)
+ * of /root/reference/experiment/mnist/mnist_server.ts:16-22 and model.json run here. */
+int dfb_gemm_simt(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, long sa_m,
+                  long sa_k, long sb_n, long sb_k, long ldd, int a_dtype, int b_dtype, int out_dtype, int act, int ksplit,
+                  void* stream);
+
+/* ---- Conv2D, NHWC activations / HWIO filters (csrc/conv_simt.cu, csrc/conv_sm100.cu) ------------------
+ * mode 0 forward, 1 data gradient, 2 filter gradient.  Replaces tf.js conv2d and its gradients for the Conv2D
+ * layers of /root/reference/experiment/mnist/model.json. */
+int dfb_conv2d_simt(int mode, const void* a, const void* b, void* out, const void* bias, int bias_dtype, int N, int H, int W,
+                    int C, int OH, int OW, int K, int kh, int kw, int sh, int sw, int pt, int pl, int dtype, int out_is_f32,
+                    int act, int ksplit, void* stream);
+size_t dfb_conv2d_tc_workspace_bytes(int mode, int N, int H, int W, int C, int OH, int OW, int K, int kh, int kw);
+int dfb_conv2d_tc(int mode, const void* a, const void* b, void* out, const void* bias, int bias_dtype, int N, int H, int W,
+                  int C, int OH, int OW, int K, int kh, int kw, int sh, int sw, int pt, int pl, int dtype, int out_is_f32,
+                  int act, int reserved, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- Fused softmax-cross-entropy forward + backward (csrc/softmax_ce.cu) ------------------------------
+ * Replaces tf.losses.softmaxCrossEntropy(...).mean() + its gradient: /root/reference/src/common/models.ts:139.
+ * mode of the dense form: 0 standard, 1 reference-compat (tfjs custom gradient), 2 reference-compat (true gradient). */
+int dfb_softmax_ce_index(const void* logits, const void* labels, int label_dtype, float* loss_rows, void* dlogits, int rows,
+                         int C, long ld, long ldg, int dtype, float scale, long ignore_index, void* stream);
+int dfb_softmax_ce_dense(const void* z, const void* y, float* loss_rows, void* grad, int rows, int C, long ldz, long ldy,
+                         long ldg, int dtype, float scale, int mode, void* stream);
+
+/* ---- Element-wise / reduction helpers (csrc/elementwise.cu) -------------------------------------------- */
+int dfb_colsum(const void* x, float* out, int M, int N, long ld, int dtype, void* stream);
+int dfb_act(const void* a, const void* b, void* out, long n, int dtype, int mode, void* stream);
+int dfb_maxpool_nhwc(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                     int pt, int pl, int dtype, void* stream);
+int dfb_maxpool_nhwc_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, int OH, int OW, int kh, int kw,
+                         int sh, int sw, int pt, int pl, int dtype, void* stream);
+/* metrics into a device ring slot (replaces model.evaluate(...).dataSync(): models.ts:106-115) */
+int dfb_accuracy(const void* pred, const void* labels, int label_kind, float* slot, int rows, int C, long ldp, long ldl,
+                 int dtype, void* stream);
+
+/* ---- Symmetric heap + collectives over NVLink peer memory (parallel/csrc/comm.cu) ----------------------
+ * Transport replacement for socket.io (/root/reference/src/server/abstract_server.ts:81-89,
+ * /root/reference/src/client/abstract_client.ts:148-173). */
+int dfb_symm_alloc(size_t bytes, void** base_out);
+int dfb_symm_free(void* base);
+int dfb_symm_get_handle(void* base, void* handle_out64 /* host, 64 bytes */);
+int dfb_symm_open_handle(const void* handle64 /* host */, void** peer_ptr_out);
+int dfb_symm_close_handle(void* peer_ptr);
+int dfb_enable_peer_access(int peer_device);
+/* sync path: reduce-scatter + 1/R + optimizer (0 sgd, 1 momentum, 2 adam, 3 none) + all-gather, one launch per bucket
+ * (federated_server.ts:92-116).  grads/params/sig are HOST arrays of R device pointers. */
+int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
+                       void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
+                       int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
+                       float weight_decay, int step, int ctas, void* stream);
+int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
+                       int ctas, void* stream);
+int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
+/* async path (asynchronousSGD_server.ts:65-108): push with staleness guard, in-place apply, pull */
+int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void* const* sig, const unsigned* seen_version,
+                   unsigned* push_state, long n, long shard, int rank, int R, int max_staleness, float scale, int policy_scale,
+                   int grad_dtype, int ctas, void* stream);
+int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
+                    unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum, float beta1,
+                    float beta2, float eps, float weight_decay, int step, int ctas, void* stream);
+int dfb_async_pull(void* const* params, void* const* sig, void* dst, unsigned* seen_version, long n_bytes, long shard_bytes,
+                   int rank, int R, int ctas, void* stream);
+int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, void* stream);
+/* device work queue (dataset.ts:43-67) */
+int dfb_wq_init(unsigned* pad, unsigned batches, unsigned epochs, void* stream);
+int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, void* stream);
+int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, void* stream);
+int dfb_wq_pad_words(unsigned batches);
+int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DISTRIFLOW_B200_H_ */

@@ -1,0 +1,148 @@
+"""Models and engines end to end on one B200: numerics against the CPU oracle / a PyTorch restatement."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+def test_mnist_mlp_fit_matches_oracle_on_gpu():
+    """K1/K3/K4/K5 on the reference's own shapes ([32,784]x[784,10], N=10) through the hand-written kernels."""
+    from distriflow_b200 import DistriTorchModel
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.oracle import MlpOracle, synthetic_mnist
+    x, y = synthetic_mnist(32, seed=1)
+    for loss in ("referenceCompat", "referenceCompatTrueGrad", "softmaxCrossEntropy"):
+        oracle = MlpOracle(seed=3, loss=loss, lr=0.001)
+        net = mnist_mlp(softmax_output=(loss != "softmaxCrossEntropy")).to(dev())
+        with torch.no_grad():
+            for p, v in zip(net.parameters(), oracle.vars):
+                p.copy_(torch.from_numpy(v))
+        m = DistriTorchModel(net, {"loss": loss, "learningRate": 0.001})
+        grads = m.fit(torch.from_numpy(x).to(dev()), torch.from_numpy(y).to(dev()))
+        ref_loss, ref_grads = oracle.fit(x, y)
+        assert abs(float(m.lastLoss) - ref_loss) < 1e-3 * max(1.0, abs(ref_loss)), loss
+        for g, r in zip(grads, ref_grads):
+            scale = max(float(np.abs(r).max()), 1e-6)
+            assert float((g.cpu() - torch.from_numpy(r)).abs().max()) / scale < 2e-3, loss
+        m.update(grads)
+        oracle.update(ref_grads)
+        for p, v in zip(m.get_vars(), oracle.vars):
+            assert np.allclose(p.cpu().numpy(), v, rtol=1e-3, atol=1e-5)
+
+
+def test_mnist_cnn_forward_backward_gpu_vs_cpu():
+    from distriflow_b200.models import mnist_cnn
+    torch.manual_seed(0)
+    cpu = mnist_cnn(5, dropout=False)
+    gpu = mnist_cnn(5, dropout=False)
+    gpu.load_state_dict(cpu.state_dict())
+    gpu.to(dev())
+    x = torch.rand(4, 28, 28, 1)
+    y = F.one_hot(torch.randint(0, 5, (4,)), 5).float()
+    lc = (-(y * torch.log(cpu(x).clamp_min(1e-7))).sum(-1)).mean()
+    lc.backward()
+    lg = (-(y.to(dev()) * torch.log(gpu(x.to(dev())).clamp_min(1e-7))).sum(-1)).mean()
+    lg.backward()
+    assert abs(float(lc) - float(lg)) < 1e-4
+    for a, b in zip(cpu.parameters(), gpu.parameters()):
+        assert float((a.grad - b.grad.cpu()).abs().max()) < 1e-3 * max(1.0, float(a.grad.abs().max()))
+
+
+def _torch_gpt2_reference(model, idx, tgt):
+    """Plain PyTorch fp32 restatement of models/gpt2.py on the same weights."""
+    c = model.config
+    p = {n: t.detach().float() for n, t in model.named_parameters()}
+    B, T = idx.shape
+    x = p["wte"][idx] + p["wpe"][:T]
+    for i in range(c.n_layer):
+        pre = f"h.{i}."
+        h = F.layer_norm(x, (c.n_embd,), p[pre + "ln_1.gamma"], p[pre + "ln_1.beta"], 1e-5)
+        qkv = h @ p[pre + "c_attn.kernel"] + p[pre + "c_attn.bias"]
+        q, k, v = qkv.view(B, T, 3, c.n_head, c.n_embd // c.n_head).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, c.n_embd)
+        x = x + a @ p[pre + "c_proj.kernel"] + p[pre + "c_proj.bias"]
+        h = F.layer_norm(x, (c.n_embd,), p[pre + "ln_2.gamma"], p[pre + "ln_2.beta"], 1e-5)
+        h = F.gelu(h @ p[pre + "c_fc.kernel"] + p[pre + "c_fc.bias"], approximate="tanh")
+        x = x + h @ p[pre + "c_proj2.kernel"] + p[pre + "c_proj2.bias"]
+    x = F.layer_norm(x, (c.n_embd,), p["ln_f.gamma"], p["ln_f.beta"], 1e-5)
+    return F.cross_entropy((x @ p["wte"].t()).reshape(B * T, -1), tgt.reshape(-1))
+
+
+def test_gpt2_tiny_loss_and_grads_vs_torch():
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    torch.manual_seed(0)
+    cfg = GPT2Config.tiny()
+    model = GPT2(cfg).to(dev()).to(torch.bfloat16)
+    idx = torch.randint(0, cfg.vocab_size, (4, 64), device=dev())
+    tgt = torch.randint(0, cfg.vocab_size, (4, 64), device=dev())
+    loss = gpt2_loss(model, idx, tgt)
+    loss.backward()
+    ref_params = {n: t.detach().float().requires_grad_(True) for n, t in model.named_parameters()}
+
+    class Shim:
+        config = cfg
+
+        def named_parameters(self):
+            return ref_params.items()
+
+    ref = _torch_gpt2_reference(Shim(), idx, tgt)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 3e-2, (float(loss), float(ref))
+    worst = 0.0
+    for n, p in model.named_parameters():
+        g, r = p.grad.float(), ref_params[n].grad
+        worst = max(worst, float((g - r).abs().max() / r.abs().max().clamp_min(1e-6)))
+    assert worst < 8e-2, worst
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adam"])
+def test_engine_single_gpu_matches_torch_engine(opt):
+    """world = 1: the fused bucket kernel is the optimizer; compare with the PyTorch restatement ("nccl" back end)."""
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev())
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    losses = {}
+    for backend in ("p2p", "nccl"):
+        torch.manual_seed(0)
+        model = GPT2(cfg).to(dev())
+        eng = DataParallelEngine(model, gpt2_loss, {"optimizer": opt, "learningRate": 1e-3 if opt == "adam" else 0.05,
+                                                    "bucketBytes": 1 << 18, "backend": backend}, device=dev())
+        losses[backend] = [float(eng.step(x, y)) for _ in range(6)]
+    a, b = losses["p2p"], losses["nccl"]
+    assert a[-1] < a[0]
+    assert max(abs(u - v) for u, v in zip(a, b)) < 5e-2, (a, b)
+
+
+def test_engine_checkpoint_from_master_weights(tmp_path):
+    from distriflow_b200 import load_layers_model
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    torch.manual_seed(0)
+    net = mnist_mlp(softmax_output=False).to(dev())
+    ce = get_loss("softmaxCrossEntropy")
+    eng = DataParallelEngine(net, lambda m, x, y: ce(y, m(x)), {"optimizer": "sgd", "learningRate": 1e-3, "dtype": "fp32",
+                                                                  "gradDtype": "fp32"}, device=dev())
+    x = torch.rand(32, 28, 28, 1, device=dev())
+    y = torch.randint(0, 10, (32,), device=dev())
+    l0 = float(eng.step(x, y))
+    for _ in range(20):
+        l1 = float(eng.step(x, y))
+    assert l1 < l0
+    path = eng.save_checkpoint(str(tmp_path / "v1"))
+    back = load_layers_model(path)
+    for a, b in zip(eng.full_precision_weights(), back.parameters()):
+        assert torch.equal(a.cpu(), b.detach())
+
+
+def test_graft_smoke():
+    import __graft_entry__ as g
+    g.smoke()

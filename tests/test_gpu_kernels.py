@@ -1,0 +1,281 @@
+"""Numerics of every hand-written kernel against a plain PyTorch fp32 reference of the same op (B200 box)."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).abs().max() / b.abs().max().clamp(min=1e-6))
+
+
+# ----------------------------------------------------------------------------------------- tcgen05 GEMM
+def _gemm_case(M, N, K, a_mn, b_mn, out_dtype=torch.bfloat16, bias=False, act=None, block_n=None, splits=None, seed=0):
+    from distriflow_b200.ops.linear import _init_sigs, gemm
+    _init_sigs()
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    A = torch.randn((K, M) if a_mn else (M, K), device=dev(), generator=g).bfloat16()
+    B = torch.randn((K, N) if b_mn else (N, K), device=dev(), generator=g).bfloat16()
+    bvec = torch.randn(N, device=dev(), generator=g) if bias else None
+    out = gemm(A, B, a_mn=a_mn, b_mn=b_mn, M=M, N=N, K=K, bias=bvec, act=act, out_dtype=out_dtype, block_n=block_n, splits=splits)
+    Af = (A.t() if a_mn else A).float()
+    Bf = (B.t() if b_mn else B).float()
+    ref = Af @ Bf.t()
+    if bias:
+        ref = ref + bvec
+    if act == "relu":
+        ref = F.relu(ref)
+    elif act == "gelu":
+        ref = F.gelu(ref, approximate="tanh")
+    torch.cuda.synchronize()
+    return rel_err(out, ref)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("block_n", [128, 256])
+def test_gemm_tcgen05_layouts(a_mn, b_mn, block_n):
+    e = _gemm_case(256, 512, 256, a_mn, b_mn, block_n=block_n, splits=1)
+    assert e < 1e-2, f"rel err {e}"
+
+
+@pytest.mark.parametrize("shape", [(300, 264, 200), (128, 16, 64), (1000, 776, 1032), (4096, 768, 768), (2048, 3072, 768)])
+def test_gemm_tcgen05_tails(shape):
+    M, N, K = shape
+    for a_mn, b_mn in [(False, True), (False, False), (True, True)]:
+        if a_mn and M % 8:
+            continue
+        e = _gemm_case(M, N, K, a_mn, b_mn, splits=1)
+        assert e < 1e-2, f"{shape} a_mn={a_mn} b_mn={b_mn}: rel err {e}"
+
+
+def test_gemm_tcgen05_epilogues_and_fp32_out():
+    assert _gemm_case(512, 512, 256, False, True, bias=True, act="relu") < 1e-2
+    assert _gemm_case(512, 768, 256, False, True, bias=True, act="gelu") < 1e-2
+    assert _gemm_case(384, 256, 512, True, True, out_dtype=torch.float32) < 5e-3
+    assert _gemm_case(384, 256, 512, False, False, out_dtype=torch.float32, bias=True) < 5e-3
+
+
+def test_gemm_tcgen05_split_k():
+    # wgrad-like: small MN, long K; scratch workspace path
+    assert _gemm_case(768, 768, 8192, True, True, splits=4) < 1e-2
+    assert _gemm_case(256, 384, 4096, True, True, out_dtype=torch.float32, splits=8) < 5e-3
+    assert _gemm_case(768, 3072, 16384, True, True) < 1e-2          # heuristic picks the split
+
+
+def test_gemm_persistent_many_tiles_and_cta_cap():
+    from distriflow_b200.ops import linear as lin
+    assert _gemm_case(8192, 2304, 768, False, True) < 1e-2           # > 148 tiles: several per CTA, both TMEM stages
+    lin.set_max_ctas(100)
+    try:
+        assert _gemm_case(4096, 3072, 768, False, True) < 1e-2
+    finally:
+        lin.set_max_ctas(0)
+
+
+# ----------------------------------------------------------------------------------------- SIMT GEMM
+def test_gemm_simt_reference_shapes():
+    from distriflow_b200.ops.linear import _init_sigs, gemm
+    _init_sigs()
+    x = torch.randn(32, 784, device=dev())
+    w = torch.randn(784, 10, device=dev())
+    b = torch.randn(10, device=dev())
+    y = gemm(x, w, a_mn=False, b_mn=True, M=32, N=10, K=784, bias=b, act="relu")
+    assert rel_err(y, F.relu(x @ w + b)) < 1e-5
+    dy = torch.randn(32, 10, device=dev())
+    dx = gemm(dy, w, a_mn=False, b_mn=False, M=32, N=784, K=10)
+    assert rel_err(dx, dy @ w.t()) < 1e-5
+    dw = gemm(x, dy, a_mn=True, b_mn=True, M=784, N=10, K=32)
+    assert rel_err(dw, x.t() @ dy) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("act", [None, "relu", "gelu"])
+def test_linear_autograd(dtype, act):
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    K, N = (784, 10) if dtype == torch.float32 else (256, 384)
+    x = torch.randn(4, 24, K, device=dev(), dtype=dtype, requires_grad=True)
+    w = (torch.randn(K, N, device=dev()) * 0.05).to(dtype).requires_grad_(True)
+    b = torch.randn(N, device=dev()).to(dtype).requires_grad_(True)
+    y = ops.linear(x, w, b, act)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr, wr, br = (t.detach().float().requires_grad_(True) for t in (x, w, b))
+    yr = xr @ wr + br
+    if act == "relu":
+        yr = F.relu(yr)
+    elif act == "gelu":
+        yr = F.gelu(yr, approximate="tanh")
+    yr.backward(gy.float())
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert rel_err(y, yr) < tol
+    assert rel_err(x.grad, xr.grad) < tol and rel_err(w.grad, wr.grad) < tol and rel_err(b.grad, br.grad) < tol
+    assert w.grad.dtype == dtype and b.grad.dtype == dtype
+
+
+def test_linear_transposed_weight():
+    from distriflow_b200 import ops
+    torch.manual_seed(1)
+    x = torch.randn(512, 128, device=dev()).bfloat16().requires_grad_(True)
+    w = (torch.randn(640, 128, device=dev()) * 0.05).bfloat16().requires_grad_(True)     # [out, in]
+    y = ops.linear(x, w, None, None, transposed=True)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    yr = xr @ wr.t()
+    yr.backward(gy.float())
+    assert rel_err(y, yr) < 2e-2 and rel_err(x.grad, xr.grad) < 2e-2 and rel_err(w.grad, wr.grad) < 2e-2
+
+
+# ----------------------------------------------------------------------------------------- softmax-CE
+@pytest.mark.parametrize("dtype,C", [(torch.bfloat16, 50304), (torch.float32, 10), (torch.float32, 1003), (torch.bfloat16, 512)])
+def test_softmax_ce_index(dtype, C):
+    from distriflow_b200.ops.softmax_ce import softmax_cross_entropy
+    torch.manual_seed(0)
+    rows = 64
+    logits = (torch.randn(rows, C, device=dev()) * 3).to(dtype).requires_grad_(True)
+    labels = torch.randint(0, C, (rows,), device=dev())
+    loss = softmax_cross_entropy(logits, labels)
+    loss.backward()
+    lr = logits.detach().float().requires_grad_(True)
+    ref = F.cross_entropy(lr, labels)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 2e-3 * max(1.0, abs(float(ref)))
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(logits.grad, lr.grad) < tol + 5e-3
+
+
+def test_softmax_ce_inplace_unit_grad_and_int32():
+    from distriflow_b200.ops.softmax_ce import softmax_cross_entropy
+    torch.manual_seed(0)
+    base = (torch.randn(32, 2048, device=dev()) * 2).bfloat16()
+    labels = torch.randint(0, 2048, (32,), device=dev(), dtype=torch.int32)
+    lr = base.float().requires_grad_(True)
+    F.cross_entropy(lr, labels.long()).backward()
+    x = (base.clone() * 1.0).requires_grad_(True)       # non-leaf so the in-place overwrite is legal to inspect
+    x2 = x * 1.0
+    loss = softmax_cross_entropy(x2, labels, inplace=True, unit_grad=True)
+    loss.backward()
+    assert rel_err(x.grad, lr.grad) < 1.5e-2
+
+
+def test_softmax_ce_dense_and_reference_compat():
+    from distriflow_b200.losses import _RefCompatCE
+    from distriflow_b200.ops.softmax_ce import reference_compat_ce, softmax_cross_entropy
+    torch.manual_seed(0)
+    z = torch.randn(32, 10, device=dev(), requires_grad=True)
+    y = F.one_hot(torch.randint(0, 10, (32,), device=dev()), 10).float()
+    loss = softmax_cross_entropy(z, y)
+    loss.backward()
+    zr = z.detach().clone().requires_grad_(True)
+    ref = (-(y * F.log_softmax(zr, -1)).sum(-1)).mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 1e-5 and rel_err(z.grad, zr.grad) < 1e-5
+    for variant in ("custom", "true"):
+        p = torch.softmax(torch.randn(32, 10, device=dev()), -1).requires_grad_(True)
+        l1 = reference_compat_ce(y, p, variant)
+        l1.backward()
+        pc = p.detach().cpu().requires_grad_(True)
+        l2 = _RefCompatCE.apply(pc, y.cpu(), variant)
+        l2.backward()
+        assert abs(float(l1) - float(l2)) < 1e-5 and rel_err(p.grad.cpu(), pc.grad) < 1e-5
+
+
+# ----------------------------------------------------------------------------------------- conv / pool / helpers
+@pytest.mark.parametrize("cfg", [
+    dict(N=2, H=28, W=28, C=1, K=32, k=3, s=1, pad="valid"),          # reference CNN layer 1 (model.json)
+    dict(N=2, H=26, W=26, C=32, K=32, k=3, s=1, pad="valid"),         # reference CNN layer 2
+    dict(N=2, H=16, W=16, C=16, K=24, k=3, s=2, pad="same"),
+    dict(N=1, H=15, W=17, C=3, K=8, k=5, s=2, pad="same"),
+    dict(N=2, H=8, W=8, C=16, K=32, k=1, s=1, pad="valid"),
+])
+def test_conv2d_fp32_fwd_bwd(cfg):
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(cfg["N"], cfg["H"], cfg["W"], cfg["C"], device=dev(), requires_grad=True)
+    w = (torch.randn(cfg["k"], cfg["k"], cfg["C"], cfg["K"], device=dev()) * 0.2).requires_grad_(True)
+    b = torch.randn(cfg["K"], device=dev(), requires_grad=True)
+    y = ops.conv2d_nhwc(x, w, b, (cfg["s"], cfg["s"]), cfg["pad"], "relu")
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xc, wc, bc = (t.detach().cpu().requires_grad_(True) for t in (x, w, b))
+    yr = ops.conv2d_nhwc(xc, wc, bc, (cfg["s"], cfg["s"]), cfg["pad"], "relu")
+    yr.backward(gy.cpu())
+    assert y.shape == yr.shape
+    assert rel_err(y.cpu(), yr) < 1e-4
+    assert rel_err(x.grad.cpu(), xc.grad) < 1e-4 and rel_err(w.grad.cpu(), wc.grad) < 1e-3 and rel_err(b.grad.cpu(), bc.grad) < 1e-4
+
+
+def test_conv2d_bf16_simt_path():
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(2, 12, 12, 8, device=dev()).bfloat16().requires_grad_(True)
+    w = (torch.randn(3, 3, 8, 24, device=dev()) * 0.2).bfloat16().requires_grad_(True)
+    y = ops.conv2d_nhwc(x, w, None, (1, 1), "same", None)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xc, wc = x.detach().float().cpu().requires_grad_(True), w.detach().float().cpu().requires_grad_(True)
+    yr = ops.conv2d_nhwc(xc, wc, None, (1, 1), "same", None)
+    yr.backward(gy.float().cpu())
+    assert rel_err(y.cpu(), yr) < 2e-2 and rel_err(x.grad.cpu(), xc.grad) < 2e-2 and rel_err(w.grad.cpu(), wc.grad) < 2e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_maxpool(dtype):
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(2, 24, 24, 32, device=dev()).to(dtype).requires_grad_(True)
+    y = ops.maxpool2d_nhwc(x, (2, 2))
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xc = x.detach().float().cpu().requires_grad_(True)
+    yr = ops.maxpool2d_nhwc(xc, (2, 2))
+    yr.backward(gy.float().cpu())
+    assert torch.equal(y.float().cpu(), yr) and rel_err(x.grad.cpu(), xc.grad) < 1e-6
+    # overlapping 3x3/2 'same' windows (ResNet stem)
+    x2 = torch.randn(1, 9, 9, 8, device=dev()).to(dtype).requires_grad_(True)
+    y2 = ops.maxpool2d_nhwc(x2, (3, 3), (2, 2), "same")
+    y2.sum().backward()
+    x2c = x2.detach().float().cpu().requires_grad_(True)
+    y2r = ops.maxpool2d_nhwc(x2c, (3, 3), (2, 2), "same")
+    y2r.sum().backward()
+    assert torch.equal(y2.float().cpu(), y2r) and rel_err(x2.grad.cpu(), x2c.grad) < 1e-6
+
+
+def test_colsum_act_accuracy():
+    from distriflow_b200.ops import _lib
+    from distriflow_b200.ops._lib import check, dt, ptr, stream
+    from distriflow_b200.ops.linear import _init_sigs, act_op, colsum
+    _init_sigs()
+    x = torch.randn(1000, 776, device=dev()).bfloat16()
+    assert rel_err(colsum(x), x.float().sum(0)) < 1e-3
+    x32 = torch.randn(333, 10, device=dev())
+    assert rel_err(colsum(x32), x32.sum(0)) < 1e-5
+    a = torch.randn(4099, device=dev()).bfloat16()
+    b = torch.randn(4099, device=dev()).bfloat16()
+    assert rel_err(act_op(a, None, 0), F.gelu(a.float(), approximate="tanh")) < 1e-2
+    br = b.float().requires_grad_(True)
+    F.gelu(br, approximate="tanh").backward(a.float())
+    assert rel_err(act_op(a, b, 1), br.grad) < 1e-2
+    assert torch.equal(act_op(a, b, 2), torch.where(b > 0, a, torch.zeros_like(a)))
+    L = _lib.lib()
+    L.dfb_accuracy.restype = ctypes.c_int
+    L.dfb_accuracy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                               ctypes.c_long, ctypes.c_long, ctypes.c_int, ctypes.c_void_p]
+    pred = torch.randn(257, 10, device=dev())
+    lab = torch.randint(0, 10, (257,), device=dev())
+    slot = torch.zeros(2, device=dev())
+    check(L.dfb_accuracy(ptr(pred), ptr(lab), 0, ptr(slot), 257, 10, 10, 0, dt(pred), stream()), "acc")
+    assert int(slot[0]) == int((pred.argmax(-1) == lab).sum()) and int(slot[1]) == 257
+    onehot = F.one_hot(lab, 10).float()
+    slot.zero_()
+    check(L.dfb_accuracy(ptr(pred), ptr(onehot), 2, ptr(slot), 257, 10, 10, 10, dt(pred), stream()), "acc")
+    assert int(slot[0]) == int((pred.argmax(-1) == lab).sum())
