@@ -9,6 +9,8 @@ from __future__ import annotations
 
 import contextlib
 
+_STOCK_CTX = None
+
 import torch
 import torch.nn.functional as F
 
@@ -65,8 +67,9 @@ def make_ddp_step(model, loss_fn, optimizer: str, lr: float, world: int, device,
         opt = torch.optim.SGD(params, lr=lr, momentum=0.9)
     else:
         opt = torch.optim.SGD(params, lr=lr)
-    ctx = stock_ops()
-    ctx.__enter__()                 # stays on for the life of the process (baseline arm)
+    global _STOCK_CTX
+    _STOCK_CTX = stock_ops()        # kept referenced: a collected generator would run its `finally` and undo the patch
+    _STOCK_CTX.__enter__()          # stays on for the life of the process (baseline arm)
 
     def step(*batch):
         opt.zero_grad(set_to_none=True)

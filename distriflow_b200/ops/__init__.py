@@ -39,7 +39,7 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
            activation: Optional[str] = None, transposed: bool = False) -> torch.Tensor:
     """`act(x @ weight + bias)` with `weight` in tf.js layout `[in, out]` (`transposed=True`: `[out, in]`)."""
     if x.is_cuda:
-        from .linear import linear_cuda
+        from .dense import linear_cuda
         return linear_cuda(x, weight, bias, activation, transposed)
     w = weight.to(x.dtype)
     y = x @ (w.t() if transposed else w)

@@ -15,7 +15,7 @@ import torch
 
 from . import _lib
 from ._lib import c_int, c_void_p, check, dt, ptr, stream
-from .linear import ACT, colsum
+from .dense import ACT, colsum
 
 
 def _sigs():
@@ -98,7 +98,7 @@ class _Conv2dFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        from .linear import act_op
+        from .dense import act_op
         x, w, y = ctx.saved_tensors
         geom = ctx.geom
         (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom

@@ -186,6 +186,8 @@ class AsyncEngine:
             p._dfb_grad_ready = lambda: None
 
             def hook(param, sink=self.grad_flat[off:off + p.numel()]):
+                if param.grad is None:
+                    return
                 sink.copy_(param.grad.reshape(-1))
                 param.grad = None
 

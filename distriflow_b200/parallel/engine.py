@@ -150,6 +150,8 @@ class DataParallelEngine:
                 p._dfb_grad_ready = (lambda bb=b: self._param_ready(bb))
 
                 def hook(param, sink=sink, bb=b):              # parameters whose gradient comes from plain autograd
+                    if param.grad is None:                     # autograd fires the hook even for an undefined gradient:
+                        return                                 # that parameter went through the sink path already
                     sink.copy_(param.grad.reshape(-1))
                     param.grad = None
                     self._param_ready(bb)
@@ -174,7 +176,7 @@ class DataParallelEngine:
         """One synchronous data-parallel step: forward, backward (+ overlapped bucket collectives), new version."""
         self.zero_pending()
         if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"]:
-            from ..ops import linear as _lin
+            from ..ops import dense as _lin
             _lin.set_max_ctas(_lin.NUM_SMS - self.comm_ctas)   # leave SMs for the collective kernels during backward
         loss = self.loss_fn(self.model, *batch)
         loss.backward()
@@ -183,7 +185,7 @@ class DataParallelEngine:
                 self._launch_bucket(b)
         if self.device.type == "cuda":
             torch.cuda.current_stream().wait_stream(self.comm_stream)
-            from ..ops import linear as _lin
+            from ..ops import dense as _lin
             _lin.set_max_ctas(0)
         old = self.version
         self.version += 1

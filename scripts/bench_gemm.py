@@ -7,7 +7,7 @@ import os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
-from distriflow_b200.ops.linear import _init_sigs, gemm, pick_tile
+from distriflow_b200.ops.dense import _init_sigs, gemm, pick_tile
 
 
 def timeit(fn, n=10, warm=3):

@@ -57,7 +57,7 @@ def test_mnist_cnn_forward_backward_gpu_vs_cpu():
 def _torch_gpt2_reference(model, idx, tgt):
     """Plain PyTorch fp32 restatement of models/gpt2.py on the same weights."""
     c = model.config
-    p = {n: t.detach().float() for n, t in model.named_parameters()}
+    p = {n: t.float() for n, t in model.named_parameters()}
     B, T = idx.shape
     x = p["wte"][idx] + p["wpe"][:T]
     for i in range(c.n_layer):

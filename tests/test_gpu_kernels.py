@@ -19,7 +19,7 @@ def rel_err(a, b):
 
 # ----------------------------------------------------------------------------------------- tcgen05 GEMM
 def _gemm_case(M, N, K, a_mn, b_mn, out_dtype=torch.bfloat16, bias=False, act=None, block_n=None, splits=None, seed=0):
-    from distriflow_b200.ops.linear import _init_sigs, gemm
+    from distriflow_b200.ops.dense import _init_sigs, gemm
     _init_sigs()
     g = torch.Generator(device="cuda").manual_seed(seed)
     A = torch.randn((K, M) if a_mn else (M, K), device=dev(), generator=g).bfloat16()
@@ -71,7 +71,7 @@ def test_gemm_tcgen05_split_k():
 
 
 def test_gemm_persistent_many_tiles_and_cta_cap():
-    from distriflow_b200.ops import linear as lin
+    from distriflow_b200.ops import dense as lin
     assert _gemm_case(8192, 2304, 768, False, True) < 1e-2           # > 148 tiles: several per CTA, both TMEM stages
     lin.set_max_ctas(100)
     try:
@@ -82,7 +82,7 @@ def test_gemm_persistent_many_tiles_and_cta_cap():
 
 # ----------------------------------------------------------------------------------------- SIMT GEMM
 def test_gemm_simt_reference_shapes():
-    from distriflow_b200.ops.linear import _init_sigs, gemm
+    from distriflow_b200.ops.dense import _init_sigs, gemm
     _init_sigs()
     x = torch.randn(32, 784, device=dev())
     w = torch.randn(784, 10, device=dev())
@@ -253,7 +253,7 @@ def test_maxpool(dtype):
 def test_colsum_act_accuracy():
     from distriflow_b200.ops import _lib
     from distriflow_b200.ops._lib import check, dt, ptr, stream
-    from distriflow_b200.ops.linear import _init_sigs, act_op, colsum
+    from distriflow_b200.ops.dense import _init_sigs, act_op, colsum
     _init_sigs()
     x = torch.randn(1000, 776, device=dev()).bfloat16()
     assert rel_err(colsum(x), x.float().sum(0)) < 1e-3
