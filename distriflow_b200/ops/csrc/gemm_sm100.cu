@@ -465,3 +465,55 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
   return block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, p, max_ctas, stream)
                         : launch_gemm<128, float>(tmA, tmB, tmD, p, max_ctas, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Split-K GEMM for callers that must not allocate.
+//
+// Who this is for: code that runs where a device allocation is not an option — a step loop that has promised
+// never to block the device (cudaMalloc and cudaFree synchronise it), a plug-in living inside a host program
+// whose memory pool already owns the whole GPU and is not reachable from C (for instance a PyTorch process
+// whose caching allocator holds the memory while the caller is a plain C/C++ extension without libtorch), or a
+// job sized so close to the 180 GB limit that a late allocation could simply fail in the middle of training.
+// Such a caller cannot hand dfb_gemm_bf16 the fp32 workspace that its split-K path needs, so this entry point
+// brings the workspace with it: a fixed array in the library's own device data segment.
+//
+// Limit: kNoAllocScratchBytes (32 MiB) — dfb_gemm_workspace_bytes(M, N, splits) must not exceed it, otherwise
+// the call fails with a message that states both numbers.  The array exists once per GPU that loads this
+// library and stays until the process exits.
+//
+// Sharing rules: every call on a device uses the same array.  Nothing in it has to start at zero — each split
+// writes its whole [ceil128(M) x N] partial tile grid with plain stores before the reduce kernel reads it, so
+// whatever the previous call left behind is overwritten, never accumulated into.  Two calls whose kernels can
+// overlap on the GPU (different streams without an ordering between them) race on the array and corrupt each
+// other; keep calls on one stream or order them with events.
+//
+// Set-up: in host code the name g_noalloc_scratch is only a host-side handle for the device array, not an
+// address a kernel can use.  The first call on each device (with that device current) asks the runtime for the
+// real device address with cudaGetSymbolAddress and remembers it; later calls reuse it.  Make that first call
+// before starting any stream capture.
+constexpr size_t kNoAllocScratchBytes = size_t(32) << 20;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchBytes / sizeof(float)];
+static float* g_noalloc_scratch_addr[64];      // device address of the array, per device ordinal (0 = not resolved yet)
+
+DFB_API int dfb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
+                                         int K, int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype,
+                                         int act, int block_n, int splits, int max_ctas, cudaStream_t stream) {
+  DFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm (no-alloc): empty problem %d x %d x %d", M, N, K);
+  DFB_REQUIRE(splits >= 1, "gemm (no-alloc): splits must be >= 1");
+  const size_t need = dfb_gemm_workspace_bytes(M, N, splits);
+  DFB_REQUIRE(need <= kNoAllocScratchBytes,
+              "gemm (no-alloc): M=%d N=%d splits=%d needs %zu bytes of split-K scratch, the built-in array holds %zu; "
+              "lower `splits` or use dfb_gemm_bf16 with a caller-provided workspace",
+              M, N, splits, need, kNoAllocScratchBytes);
+  int dev = 0;
+  DFB_CUDA_CHECK(cudaGetDevice(&dev));
+  DFB_REQUIRE(dev >= 0 && dev < 64, "gemm (no-alloc): device ordinal %d out of range", dev);
+  if (g_noalloc_scratch_addr[dev] == nullptr) {       // once per device, with that device current
+    float* p = nullptr;
+    DFB_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    DFB_REQUIRE(p != nullptr, "gemm (no-alloc): cudaGetSymbolAddress returned a null address");
+    g_noalloc_scratch_addr[dev] = p;
+  }
+  return dfb_gemm_bf16(A, B, D, bias, bias_dtype, M, N, K, lda, ldb, ldd, a_mn_major, b_mn_major, out_dtype, act, block_n,
+                       splits, g_noalloc_scratch_addr[dev], kNoAllocScratchBytes, max_ctas, stream);
+}

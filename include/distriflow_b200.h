@@ -29,6 +29,18 @@ int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int b
                   int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits,
                   void* workspace, size_t workspace_bytes, int max_ctas, void* stream);
 
+/* Split-K GEMM that allocates nothing: same arguments as dfb_gemm_bf16 minus the workspace, which is a 32 MiB
+ * array inside the library (one per GPU, shared by all calls, kept until exit).  For callers that cannot
+ * allocate device memory themselves (no-sync step loops, C plug-ins inside a process whose pool owns the GPU).
+ * Fails with a clear message when dfb_gemm_workspace_bytes(M, N, splits) exceeds
+ * DFB_GEMM_NOALLOC_MAX_WORKSPACE_BYTES.  The first call on a device resolves the array's device address; make
+ * it before any stream capture.  Calls that overlap on the GPU race on the array.
+ * No counterpart in the reference (it has no native code and no split-K). */
+#define DFB_GEMM_NOALLOC_MAX_WORKSPACE_BYTES (32u << 20)
+int dfb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K,
+                                 int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act,
+                                 int block_n, int splits, int max_ctas, void* stream);
+
 /* ---- CUDA-core GEMM for fp32 / tiny-N / unaligned shapes (csrc/gemm_simt.cu) ---------------------------
  * D[m,n] = act(sum_k A[m*sa_m + k*sa_k] * B[n*sb_n + k*sb_k] + bias[n]).  The MNIST heads Dense(10), Dense(5)
  * of /root/reference/experiment/mnist/mnist_server.ts:16-22 and model.json run here. */
