@@ -55,9 +55,28 @@ static void load_encode() {
   if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) g_encode = reinterpret_cast<EncodeTiledFn>(fn);
 }
 
+// cuTensorMapEncodeTiled is a DRIVER call and needs a current context on the calling thread.  A fresh thread (the
+// autograd backward thread of device 0 is the usual case: torch skips cudaSetDevice when the target equals the
+// default device) has none until some runtime call binds one.  Bind the context of the device that owns `ptr`.
+static void ensure_thread_context(const void* ptr) {
+  static thread_local bool bound = false;
+  if (bound) return;
+  cudaPointerAttributes attr;
+  int dev = 0;
+  if (cudaPointerGetAttributes(&attr, ptr) == cudaSuccess && (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged))
+    dev = attr.device;
+  else {
+    cudaGetLastError();
+    cudaGetDevice(&dev);
+  }
+  cudaSetDevice(dev);
+  bound = true;
+}
+
 int encode_tmap(CUtensorMap* out, const void* base, int elem, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                 const uint32_t* box, const uint32_t* elem_strides, int swizzle_128b, int l2_promo_256) {
   std::call_once(g_encode_once, load_encode);
+  ensure_thread_context(base);
   if (!g_encode) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
     return 3;

@@ -32,8 +32,8 @@ def _sync_worker(rank, world, port, out):
                                                     "backend": backend}, rank=rank, world=world, device=dev)
         g = torch.Generator().manual_seed(100 + rank)            # different data per rank
         losses = []
+        idx = torch.randint(0, cfg.vocab_size, (4, 65), generator=g).to(dev)     # one fixed batch per rank: loss must fall
         for _ in range(6):
-            idx = torch.randint(0, cfg.vocab_size, (4, 65), generator=g).to(dev)
             losses.append(float(eng.step(idx[:, :-1].contiguous(), idx[:, 1:].contiguous())))
         torch.cuda.synchronize()
         w = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
