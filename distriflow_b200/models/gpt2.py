@@ -53,16 +53,12 @@ class Block(nn.Module):
                          (self.c_proj2, 0.02 / math.sqrt(2 * c.n_layer))):
             nn.init.normal_(lin.kernel, std=std)
 
-    def forward(self, x):
-        B, T, D = x.shape
-        h = self.ln_1(x)
-        qkv = self.c_attn(h)
-        q, k, v = qkv.view(B, T, 3, self.n_head, D // self.n_head).permute(2, 0, 3, 1, 4)
-        a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
-        a = a.transpose(1, 2).reshape(B, T, D)
-        x = x + self.c_proj(a)
-        x = x + self.c_proj2(self.c_fc(self.ln_2(x)))
-        return x
+    def forward(self, x, h):
+        """`x`: residual stream, `h` = ln_1(x) (computed by the caller, fused with the previous residual add).
+        Returns the attention branch output and leaves the adds to the fused add+LayerNorm kernels."""
+        a = ops.causal_self_attention(self.c_attn(h), self.n_head)
+        x, h2 = ops.add_layer_norm(x, self.c_proj(a), self.ln_2.gamma, self.ln_2.beta, self.ln_2.epsilon)
+        return x, self.c_proj2(self.c_fc(h2))
 
 
 class GPT2(nn.Module):
@@ -87,9 +83,12 @@ class GPT2(nn.Module):
         B, T = idx.shape
         pos = torch.arange(T, device=idx.device)
         x = F.embedding(idx, self.wte) + self.wpe[pos]
-        for blk in self.h:
-            x = blk(x)
-        x = self.ln_f(x)
+        h = self.h[0].ln_1(x)
+        for i, blk in enumerate(self.h):
+            x, m = blk(x, h)
+            nxt = self.h[i + 1].ln_1 if i + 1 < len(self.h) else self.ln_f
+            x, h = ops.add_layer_norm(x, m, nxt.gamma, nxt.beta, nxt.epsilon)      # residual add fused with the next LayerNorm
+        x = h
         logits = ops.linear(x, self.wte, None, None, transposed=True)
         if targets is None:
             return logits

@@ -16,8 +16,8 @@ from typing import Optional, Sequence, Tuple
 import torch
 import torch.nn.functional as F
 
-__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "softmax_cross_entropy", "native_available",
-           "same_padding"]
+__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "add_layer_norm", "causal_self_attention",
+           "softmax_cross_entropy", "native_available", "same_padding"]
 
 
 def native_available() -> bool:
@@ -95,6 +95,20 @@ def layer_norm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: fl
         from .norm import layer_norm_cuda
         return layer_norm_cuda(x, gamma, beta, eps)
     return F.layer_norm(x.float(), (x.shape[-1],), gamma.float(), beta.float(), eps).to(x.dtype)
+
+
+def add_layer_norm(x: torch.Tensor, r: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5):
+    """`(s, y)` with `s = x + r` (the residual stream) and `y = LayerNorm(s)`; one fused pass on CUDA."""
+    if x.is_cuda:
+        from .norm import add_layer_norm_cuda
+        return add_layer_norm_cuda(x, r, gamma, beta, eps)
+    s = x + r
+    return s, F.layer_norm(s.float(), (s.shape[-1],), gamma.float(), beta.float(), eps).to(s.dtype)
+
+
+def causal_self_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
+    from .attention import causal_self_attention as f
+    return f(qkv, n_head)
 
 
 def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor, ignore_index: Optional[int] = None,

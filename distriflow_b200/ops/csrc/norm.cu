@@ -1,0 +1,289 @@
+// Fused residual-add + LayerNorm (forward and backward) and a 128-byte-row permutation kernel for attention layouts.
+//
+// Not in the reference (its models have neither normalisation nor attention); they belong to the GPT-2 / ResNet
+// workloads named in BASELINE.json.  They exist because the step profile (profiles/step_profile_r1.md) showed the
+// PyTorch LayerNorm backward (GammaBetaBackward) and the cat/copy kernels around attention costing more than a
+// third of the GEMM time.  One warp per row, 16-byte loads, fp32 statistics.
+//   forward : s = x (+ r);  y = (s - mean) * rstd * gamma + beta;  mean/rstd saved
+//   backward: dx = (ds) + rstd * (g - mean_row(g) - xhat * mean_row(g * xhat)),  g = dy * gamma
+//             dgamma = sum_rows dy * xhat,  dbeta = sum_rows dy   (per-block partials, then a reduce kernel)
+#include "common.cuh"
+#include "device_utils.cuh"
+
+namespace dfb {
+
+constexpr int kLnMaxVec = 8;      // up to 8 x 16 B per lane: D <= 2048 for bf16, 1024 for fp32
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(128) add_ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ r, const T* __restrict__ gamma,
+                                                         const T* __restrict__ beta, T* __restrict__ s_out, T* __restrict__ y,
+                                                         float* __restrict__ mean, float* __restrict__ rstd, int rows, int D,
+                                                         float eps) {
+  using V = Vec16<T>;
+  constexpr int VN = V::kN;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const T* xr = x + (long)row * D;
+  float v[NV][VN];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) {
+      V a;
+      a.raw = *reinterpret_cast<const uint4*>(xr + c);
+      if (r != nullptr) {
+        V b;
+        b.raw = *reinterpret_cast<const uint4*>(r + (long)row * D + c);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) a.set(j, a.get(j) + b.get(j));     // rounded to T: the residual stream is stored in T
+        *reinterpret_cast<uint4*>(s_out + (long)row * D + c) = a.raw;
+      }
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        v[i][j] = a.get(j);
+        sum += v[i][j];
+      }
+    }
+  }
+  const float mu = warp_sum(sum) / (float)D;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) {
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        const float d = v[i][j] - mu;
+        sq += d * d;
+      }
+    }
+  }
+  const float rs = rsqrtf(warp_sum(sq) / (float)D + eps);
+  if (lane == 0) {
+    mean[row] = mu;
+    rstd[row] = rs;
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) {
+      V g, b, o;
+      g.raw = *reinterpret_cast<const uint4*>(gamma + c);
+      b.raw = *reinterpret_cast<const uint4*>(beta + c);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) o.set(j, (v[i][j] - mu) * rs * g.get(j) + b.get(j));
+      *reinterpret_cast<uint4*>(y + (long)row * D + c) = o.raw;
+    }
+  }
+}
+
+// Each block walks rows blockIdx.x*4 + warp, + gridDim.x*4, ... ; per-lane dgamma/dbeta partials live in registers and
+// are combined across the 4 warps through shared memory, then written to part[blockIdx.x][2][D].
+template <typename T, int NV>
+__global__ void __launch_bounds__(128) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
+                                                         const T* __restrict__ gamma, const float* __restrict__ mean,
+                                                         const float* __restrict__ rstd, T* __restrict__ dx,
+                                                         float* __restrict__ part, int rows, int D) {
+  using V = Vec16<T>;
+  constexpr int VN = V::kN;
+  extern __shared__ float sh[];              // [4 warps][2][D]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float dg[NV][VN], db[NV][VN], gam[NV][VN];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    V g;
+    if (c < D) g.raw = *reinterpret_cast<const uint4*>(gamma + c);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      dg[i][j] = 0.f;
+      db[i][j] = 0.f;
+      gam[i][j] = c < D ? g.get(j) : 0.f;
+    }
+  }
+  for (int row = blockIdx.x * 4 + warp; row < rows; row += gridDim.x * 4) {
+    const float mu = mean[row], rs = rstd[row];
+    float xh[NV][VN], gg[NV][VN];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+        V a, b;
+        a.raw = *reinterpret_cast<const uint4*>(s + (long)row * D + c);
+        b.raw = *reinterpret_cast<const uint4*>(dy + (long)row * D + c);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          const float xhat = (a.get(j) - mu) * rs, d = b.get(j);
+          xh[i][j] = xhat;
+          dg[i][j] += d * xhat;
+          db[i][j] += d;
+          const float g = d * gam[i][j];
+          gg[i][j] = g;
+          s1 += g;
+          s2 += g * xhat;
+        }
+      }
+    }
+    s1 = warp_sum(s1) / (float)D;
+    s2 = warp_sum(s2) / (float)D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+        V o, r;
+        if (ds != nullptr) r.raw = *reinterpret_cast<const uint4*>(ds + (long)row * D + c);
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          float val = rs * (gg[i][j] - s1 - xh[i][j] * s2);
+          if (ds != nullptr) val += r.get(j);
+          o.set(j, val);
+        }
+        *reinterpret_cast<uint4*>(dx + (long)row * D + c) = o.raw;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) {
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        sh[(warp * 2 + 0) * D + c + j] = dg[i][j];
+        sh[(warp * 2 + 1) * D + c + j] = db[i][j];
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * D; c += 128) {
+    const int which = c / D, col = c - which * D;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) t += sh[(w * 2 + which) * D + col];
+    part[((long)blockIdx.x * 2 + which) * D + col] = t;
+  }
+}
+
+// out[which][col] = sum_b part[b][which][col]  (fixed order: deterministic)
+template <typename T>
+__global__ void ln_param_grad_reduce_kernel(const float* __restrict__ part, T* __restrict__ dgamma, T* __restrict__ dbeta,
+                                            int nblocks, int D) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 2 * D) return;
+  const int which = c / D, col = c - which * D;
+  float t = 0.f;
+  for (int b = 0; b < nblocks; ++b) t += part[((long)b * 2 + which) * D + col];
+  (which ? dbeta : dgamma)[col] = from_f32<T>(t);
+}
+
+// Rows of `row_bytes` (multiple of 16) indexed by (i0,i1,i2,i3): src + i.s bytes -> dst + i.d bytes.  One 16-byte vector per thread per iteration; both sides see whole
+// 128-byte rows for the attention head layouts ([B,T,3,H,D] <-> [3,B,H,T,D], [B,H,T,D] <-> [B,T,H,D]).
+__global__ void __launch_bounds__(256) permute_rows_kernel(const char* __restrict__ src, char* __restrict__ dst, int n0, int n1, int n2,
+                                                           int n3, long s0, long s1, long s2, long s3, long d0, long d1, long d2,
+                                                           long d3, int row_bytes) {
+  const int vec_per_row = row_bytes >> 4;
+  const long total = (long)n0 * n1 * n2 * n3 * vec_per_row;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+    const int v = (int)(i % vec_per_row);
+    long t = i / vec_per_row;
+    const int i3 = (int)(t % n3); t /= n3;
+    const int i2 = (int)(t % n2); t /= n2;
+    const int i1 = (int)(t % n1);
+    const int i0 = (int)(t / n1);
+    const uint4 val = *reinterpret_cast<const uint4*>(src + i0 * s0 + i1 * s1 + i2 * s2 + i3 * s3 + (long)v * 16);
+    *reinterpret_cast<uint4*>(dst + i0 * d0 + i1 * d1 + i2 * d2 + i3 * d3 + (long)v * 16) = val;
+  }
+}
+
+template <typename T, int NV>
+static int launch_ln_fwd(const void* x, const void* r, const void* gamma, const void* beta, void* s_out, void* y, float* mean,
+                         float* rstd, int rows, int D, float eps, cudaStream_t st) {
+  add_ln_fwd_kernel<T, NV><<<ceil_div(rows, 4), 128, 0, st>>>((const T*)x, (const T*)r, (const T*)gamma, (const T*)beta, (T*)s_out,
+                                                           (T*)y, mean, rstd, rows, D, eps);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+template <typename T, int NV>
+static int launch_ln_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
+                         void* dx, float* part, int nblocks, int rows, int D, cudaStream_t st) {
+  auto kern = add_ln_bwd_kernel<T, NV>;
+  const int smem = 4 * 2 * D * (int)sizeof(float);
+  if (smem > 48 * 1024) DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  kern<<<nblocks, 128, smem, st>>>((const T*)dy, (const T*)ds, (const T*)s, (const T*)gamma, mean, rstd, (T*)dx, part, rows, D);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace dfb
+
+using namespace dfb;
+
+static int ln_nv(int D, int vn) { return ceil_div(D, 32 * vn); }
+
+// s_out = x + r (skipped when r is null: then s_out is unused), y = LayerNorm(s) * gamma + beta; mean/rstd fp32 [rows].
+// D must be a multiple of 8 (bf16) / 4 (fp32) and at most 2048 / 1024.
+DFB_API int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamma, const void* beta, void* s_out, void* y,
+                                  float* mean, float* rstd, int rows, int D, float eps, int dtype, cudaStream_t stream) {
+  DFB_REQUIRE(rows > 0 && D > 0, "layernorm: empty");
+  const int vn = dtype == DT_BF16 ? 8 : 4;
+  DFB_REQUIRE(dtype == DT_BF16 || dtype == DT_F32, "layernorm: dtype");
+  DFB_REQUIRE(D % vn == 0 && ln_nv(D, vn) <= kLnMaxVec, "layernorm: D=%d unsupported (multiple of %d, <= %d)", D, vn, 32 * vn * kLnMaxVec);
+  const int nv = ln_nv(D, vn);
+#define DFB_LN_FWD(NV)                                                                                                     \
+  if (nv <= NV)                                                                                                            \
+    return dtype == DT_BF16 ? launch_ln_fwd<__nv_bfloat16, NV>(x, r, gamma, beta, s_out, y, mean, rstd, rows, D, eps, stream) \
+                            : launch_ln_fwd<float, NV>(x, r, gamma, beta, s_out, y, mean, rstd, rows, D, eps, stream);
+  DFB_LN_FWD(1) DFB_LN_FWD(2) DFB_LN_FWD(3) DFB_LN_FWD(4) DFB_LN_FWD(8)
+#undef DFB_LN_FWD
+  return 2;
+}
+
+DFB_API int dfb_layernorm_bwd_blocks(int rows) {
+  int b = num_sms() * 4;
+  int need = ceil_div(rows, 4);
+  return b < need ? b : need;
+}
+
+// dx = ds + LayerNorm-backward(dy); dgamma/dbeta in the parameter dtype.  `part` is fp32 scratch of
+// dfb_layernorm_bwd_blocks(rows) * 2 * D floats supplied by the caller.
+DFB_API int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean,
+                                  const float* rstd, void* dx, void* dgamma, void* dbeta, float* part, int rows, int D, int dtype,
+                                  cudaStream_t stream) {
+  DFB_REQUIRE(rows > 0 && D > 0, "layernorm_bwd: empty");
+  const int vn = dtype == DT_BF16 ? 8 : 4;
+  DFB_REQUIRE(dtype == DT_BF16 || dtype == DT_F32, "layernorm_bwd: dtype");
+  DFB_REQUIRE(D % vn == 0 && ln_nv(D, vn) <= kLnMaxVec, "layernorm_bwd: D=%d unsupported", D);
+  const int nv = ln_nv(D, vn);
+  const int nblocks = dfb_layernorm_bwd_blocks(rows);
+  int rc = 2;
+#define DFB_LN_BWD(NV)                                                                                                          \
+  if (rc == 2 && nv <= NV)                                                                                                      \
+    rc = dtype == DT_BF16 ? launch_ln_bwd<__nv_bfloat16, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, stream)    \
+                          : launch_ln_bwd<float, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, stream);
+  DFB_LN_BWD(1) DFB_LN_BWD(2) DFB_LN_BWD(3) DFB_LN_BWD(4) DFB_LN_BWD(8)
+#undef DFB_LN_BWD
+  if (rc) return rc;
+  if (dtype == DT_BF16)
+    ln_param_grad_reduce_kernel<__nv_bfloat16><<<ceil_div(2 * D, 128), 128, 0, stream>>>(part, (__nv_bfloat16*)dgamma,
+                                                                                         (__nv_bfloat16*)dbeta, nblocks, D);
+  else
+    ln_param_grad_reduce_kernel<float><<<ceil_div(2 * D, 128), 128, 0, stream>>>(part, (float*)dgamma, (float*)dbeta, nblocks, D);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API int dfb_permute_rows(const void* src, void* dst, int n0, int n1, int n2, int n3, long s0, long s1, long s2, long s3,
+                             long d0, long d1, long d2, long d3, int row_bytes, cudaStream_t stream) {
+  DFB_REQUIRE(row_bytes > 0 && (row_bytes % 16) == 0, "permute_rows: row_bytes must be a multiple of 16");
+  DFB_REQUIRE(((s0 | s1 | s2 | s3 | d0 | d1 | d2 | d3) % 16) == 0, "permute_rows: strides must be multiples of 16 bytes");
+  const long total = (long)n0 * n1 * n2 * n3 * (row_bytes / 16);
+  DFB_REQUIRE(total > 0, "permute_rows: empty");
+  long blocks = (total + 255) / 256;
+  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
+  permute_rows_kernel<<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, n0, n1, n2, n3, s0, s1, s2, s3, d0, d1, d2,
+                                                       d3, row_bytes);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -279,3 +279,53 @@ def test_colsum_act_accuracy():
     slot.zero_()
     check(L.dfb_accuracy(ptr(pred), ptr(onehot), 2, ptr(slot), 257, 10, 10, 10, dt(pred), stream()), "acc")
     assert int(slot[0]) == int((pred.argmax(-1) == lab).sum())
+
+
+# ----------------------------------------------------------------------------------------- LayerNorm / attention layout
+@pytest.mark.parametrize("dtype,D", [(torch.bfloat16, 768), (torch.float32, 128), (torch.bfloat16, 2048), (torch.float32, 36)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_add_layer_norm(dtype, D, with_res):
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    rows = 333
+    x = torch.randn(3, rows // 3, D, device=dev()).to(dtype).requires_grad_(True)
+    r = torch.randn(3, rows // 3, D, device=dev()).to(dtype).requires_grad_(True) if with_res else None
+    g = (1 + 0.1 * torch.randn(D, device=dev())).to(dtype).requires_grad_(True)
+    b = (0.1 * torch.randn(D, device=dev())).to(dtype).requires_grad_(True)
+    if with_res:
+        s, y = ops.add_layer_norm(x, r, g, b, 1e-5)
+        gs, gy = torch.randn_like(s), torch.randn_like(y)
+        torch.autograd.backward([s, y], [gs, gy])
+    else:
+        y = ops.layer_norm(x, g, b, 1e-5)
+        gy = torch.randn_like(y)
+        y.backward(gy)
+    xr, gr, br = (t.detach().float().requires_grad_(True) for t in (x, g, b))
+    if with_res:
+        rr = r.detach().float().requires_grad_(True)
+        sr = (xr + rr).to(dtype).float() if dtype == torch.bfloat16 else xr + rr
+        sr = xr + rr + (sr - (xr + rr)).detach()          # same rounding of the stored residual stream, gradient of a plain add
+        yr = F.layer_norm(sr, (D,), gr, br, 1e-5)
+        torch.autograd.backward([sr, yr], [gs.float(), gy.float()])
+        assert rel_err(s, sr) < 1e-2 and rel_err(r.grad, rr.grad) < 2e-2
+    else:
+        yr = F.layer_norm(xr, (D,), gr, br, 1e-5)
+        yr.backward(gy.float())
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert rel_err(y, yr) < tol and rel_err(x.grad, xr.grad) < tol
+    assert rel_err(g.grad, gr.grad) < tol and rel_err(b.grad, br.grad) < tol
+
+
+def test_attention_layout_kernels_match_torch():
+    from distriflow_b200.ops.attention import causal_self_attention
+    torch.manual_seed(0)
+    B, T, H, D = 2, 128, 4, 64
+    qkv = torch.randn(B, T, 3 * H * D, device=dev()).bfloat16().requires_grad_(True)
+    out = causal_self_attention(qkv, H)
+    go = torch.randn_like(out)
+    out.backward(go)
+    ref_in = qkv.detach().clone().requires_grad_(True)
+    q, k, v = ref_in.view(B, T, 3, H, D).permute(2, 0, 3, 1, 4)
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, H * D)
+    ref.backward(go)
+    assert rel_err(out, ref) < 2e-2 and rel_err(qkv.grad, ref_in.grad) < 2e-2
