@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--optimizer", default="adam")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--comm-ctas", type=int, default=64)
+    ap.add_argument("--reserve-sms", type=int, default=0)
     return ap.parse_args()
 
 
@@ -160,7 +162,8 @@ def main():
         else:
             from distriflow_b200.parallel.engine import DataParallelEngine
             engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
-                                                         "bucketBytes": int(args.bucket_mb * (1 << 20))},
+                                                         "bucketBytes": int(args.bucket_mb * (1 << 20)),
+                                                         "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms},
                                         rank=rank, world=world, device=device)
         step = engine.step
     else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)

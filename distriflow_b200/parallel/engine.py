@@ -68,7 +68,8 @@ class DataParallelEngine:
         self.lr = float(self.cfg["learningRate"])
         self.version = 0                    # number of optimizer steps applied (model version index)
         self.maximumStaleness = int(self.cfg["maximumStaleness"])
-        self.comm_ctas = 32
+        self.comm_ctas = int(self.cfg["commCtas"])
+        self.reserve_sms = int(self.cfg["reserveSMs"])
         self._epoch = 0
         self._launches = 0                  # own-kernel launches issued by the engine (comm/optimizer kernels)
         self.versionCallbacks: List[Callable[[int, int], None]] = []
@@ -175,9 +176,9 @@ class DataParallelEngine:
     def step(self, *batch: Any) -> torch.Tensor:
         """One synchronous data-parallel step: forward, backward (+ overlapped bucket collectives), new version."""
         self.zero_pending()
-        if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"]:
+        if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"] and self.reserve_sms:
             from ..ops import dense as _lin
-            _lin.set_max_ctas(_lin.NUM_SMS - self.comm_ctas)   # leave SMs for the collective kernels during backward
+            _lin.set_max_ctas(_lin.NUM_SMS - self.reserve_sms)  # optionally leave SMs free for the collective kernels
         loss = self.loss_fn(self.model, *batch)
         loss.backward()
         for b in self.buckets:                                 # anything not launched from a hook (unused params, overlap off)
