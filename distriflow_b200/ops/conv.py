@@ -27,9 +27,10 @@ def _sigs():
         L.dfb_maxpool_nhwc.argtypes = [c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_maxpool_nhwc_bwd.restype = c_int
         L.dfb_maxpool_nhwc_bwd.argtypes = [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
-        if hasattr(L, "dfb_conv2d_tc"):
-            L.dfb_conv2d_tc.restype = c_int
-            L.dfb_conv2d_tc.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p, ctypes.c_size_t, c_void_p]
+        L.dfb_conv2d_tc.restype = c_int
+        L.dfb_conv2d_tc.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p, ctypes.c_size_t, c_void_p]
+        L.dfb_conv2d_tc_supported.restype = c_int
+        L.dfb_conv2d_tc_supported.argtypes = [c_int] * 12
         L._dfb_conv_sigs = True
     return L
 
@@ -49,9 +50,14 @@ def _geometry(H: int, W: int, kh: int, kw: int, strides: Tuple[int, int], paddin
     return OH, OW, pt, pl
 
 
-def _tc_eligible(x: torch.Tensor, C: int, K: int) -> bool:
-    L = _lib.lib()
-    return hasattr(L, "dfb_conv2d_tc") and x.dtype == torch.bfloat16 and C % 16 == 0 and K % 16 == 0
+def _tc_eligible(mode: int, x: torch.Tensor, geom) -> bool:
+    if x.dtype != torch.bfloat16 or FORCE_SIMT:
+        return False
+    (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
+    return bool(_sigs().dfb_conv2d_tc_supported(mode, N, H, W, C, OH, OW, K, kh, kw, sh, sw))
+
+
+FORCE_SIMT = False      # tests flip this to compare the two implementations
 
 
 def _conv_call(mode: int, a, b, out, bias, geom, act, ksplit=1):
@@ -66,12 +72,10 @@ def _conv_call(mode: int, a, b, out, bias, geom, act, ksplit=1):
 def _conv_tc(mode: int, a, b, out, bias, geom, act):
     L = _sigs()
     (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
-    ws_bytes = int(L.dfb_conv2d_tc_workspace_bytes(mode, N, H, W, C, OH, OW, K, kh, kw)) if hasattr(L, "dfb_conv2d_tc_workspace_bytes") else 0
-    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=a.device) if ws_bytes else None
-    rc = L.dfb_conv2d_tc(mode, ptr(a), ptr(b), ptr(out), ptr(bias), dt(bias) if bias is not None else 0,
-                         N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl, dt(a), 1 if out.dtype == torch.float32 else 0,
-                         ACT[act], 0, ptr(ws), ctypes.c_size_t(ws_bytes), stream())
-    return rc
+    check(L.dfb_conv2d_tc(mode, ptr(a), ptr(b), ptr(out), ptr(bias), dt(bias) if bias is not None else 0,
+                          N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl, dt(a), 1 if out.dtype == torch.float32 else 0,
+                          ACT[act], 0, None, ctypes.c_size_t(0), stream()), "dfb_conv2d_tc")
+    return out
 
 
 class _Conv2dFn(torch.autograd.Function):
@@ -86,10 +90,9 @@ class _Conv2dFn(torch.autograd.Function):
         w = kernel if kernel.dtype == x.dtype else kernel.to(x.dtype)
         w = w.contiguous()
         y = torch.empty((N, OH, OW, K), device=x.device, dtype=x.dtype)
-        done = False
-        if _tc_eligible(x, C, K):
-            done = _conv_tc(0, x, w, y, bias, geom, activation) == 0
-        if not done:
+        if _tc_eligible(0, x, geom):
+            _conv_tc(0, x, w, y, bias, geom, activation)
+        else:
             _conv_call(0, x, w, y, bias, geom, activation)
         ctx.geom, ctx.activation = geom, activation
         ctx.kernel_ref, ctx.bias_ref = kernel, bias
@@ -111,20 +114,18 @@ class _Conv2dFn(torch.autograd.Function):
         kernel, bias = ctx.kernel_ref, ctx.bias_ref
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            done = False
-            if _tc_eligible(x, C, K):
-                done = _conv_tc(1, dy, w, dx, None, geom, None) == 0
-            if not done:
+            if _tc_eligible(1, x, geom):
+                _conv_tc(1, dy, w, dx, None, geom, None)
+            else:
                 _conv_call(1, dy, w, dx, None, geom, None)
         if ctx.needs_input_grad[1]:
             pixels = N * OH * OW
             tiles = (-(-(kh * kw * C) // 64)) * (-(-K // 64))
             ksplit = max(1, min(64, (148 * 4) // max(tiles, 1), pixels // 256))
             dw32 = torch.empty((kh, kw, C, K), device=x.device, dtype=torch.float32)
-            done = False
-            if _tc_eligible(x, C, K):
-                done = _conv_tc(2, x, dy, dw32, None, geom, None) == 0
-            if not done:
+            if _tc_eligible(2, x, geom):
+                _conv_tc(2, x, dy, dw32, None, geom, None)
+            else:
                 _conv_call(2, x, dy, dw32, None, geom, None, ksplit)
             sink = getattr(kernel, "_dfb_grad_sink", None)
             if sink is not None:

@@ -54,6 +54,7 @@ int dfb_gemm_simt(const void* A, const void* B, void* D, const void* bias, int b
 int dfb_conv2d_simt(int mode, const void* a, const void* b, void* out, const void* bias, int bias_dtype, int N, int H, int W,
                     int C, int OH, int OW, int K, int kh, int kw, int sh, int sw, int pt, int pl, int dtype, int out_is_f32,
                     int act, int ksplit, void* stream);
+int dfb_conv2d_tc_supported(int mode, int N, int H, int W, int C, int OH, int OW, int K, int kh, int kw, int sh, int sw);
 size_t dfb_conv2d_tc_workspace_bytes(int mode, int N, int H, int W, int C, int OH, int OW, int K, int kh, int kw);
 int dfb_conv2d_tc(int mode, const void* a, const void* b, void* out, const void* bias, int bias_dtype, int N, int H, int W,
                   int C, int OH, int OW, int K, int kh, int kw, int sh, int sw, int pt, int pl, int dtype, int out_is_f32,

@@ -329,3 +329,57 @@ def test_attention_layout_kernels_match_torch():
     ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, H * D)
     ref.backward(go)
     assert rel_err(out, ref) < 2e-2 and rel_err(qkv.grad, ref_in.grad) < 2e-2
+
+
+# ----------------------------------------------------------------------------------------- tcgen05 implicit-GEMM conv
+@pytest.mark.parametrize("cfg", [
+    dict(N=4, H=16, W=16, C=64, K=64, k=3, s=1, pad="same"),           # ResNet-20 last stage / ResNet-50 stage 1 3x3
+    dict(N=2, H=28, W=28, C=128, K=128, k=3, s=1, pad="same"),         # partial pixel tiles (tw=28, th=4 -> 112 rows)
+    dict(N=3, H=14, W=14, C=256, K=256, k=3, s=1, pad="same"),
+    dict(N=4, H=7, W=7, C=512, K=512, k=3, s=1, pad="same"),           # two images per tile
+    dict(N=2, H=56, W=56, C=64, K=256, k=1, s=1, pad="same"),          # 1x1 expand
+    dict(N=2, H=56, W=56, C=256, K=64, k=1, s=1, pad="same"),          # 1x1 reduce
+    dict(N=2, H=28, W=28, C=128, K=128, k=3, s=2, pad="same"),         # strided 3x3 (element strides in the tensor map)
+    dict(N=2, H=28, W=28, C=256, K=512, k=1, s=2, pad="same"),         # strided 1x1 projection shortcut
+    dict(N=2, H=12, W=12, C=64, K=128, k=3, s=1, pad="valid"),
+])
+def test_conv2d_tcgen05_vs_fp32_reference(cfg):
+    from distriflow_b200 import ops
+    from distriflow_b200.ops import conv as convmod
+    torch.manual_seed(0)
+    x = torch.randn(cfg["N"], cfg["H"], cfg["W"], cfg["C"], device=dev()).bfloat16().requires_grad_(True)
+    w = (torch.randn(cfg["k"], cfg["k"], cfg["C"], cfg["K"], device=dev()) * (1.0 / (cfg["k"] * cfg["C"] ** 0.5))).bfloat16().requires_grad_(True)
+    b = torch.randn(cfg["K"], device=dev()).bfloat16().requires_grad_(True)
+    geom_ok = convmod._sigs().dfb_conv2d_tc_supported(0, cfg["N"], cfg["H"], cfg["W"], cfg["C"], -(-cfg["H"] // cfg["s"]),
+                                                      -(-cfg["W"] // cfg["s"]), cfg["K"], cfg["k"], cfg["k"], cfg["s"], cfg["s"])
+    assert geom_ok or cfg["pad"] == "valid"
+    y = ops.conv2d_nhwc(x, w, b, (cfg["s"], cfg["s"]), cfg["pad"], "relu")
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr, wr, br = (t.detach().float().cpu().requires_grad_(True) for t in (x, w, b))
+    yr = ops.conv2d_nhwc(xr, wr, br, (cfg["s"], cfg["s"]), cfg["pad"], "relu")
+    yr.backward(gy.float().cpu())
+    assert y.shape == yr.shape
+    assert rel_err(y.cpu(), yr) < 2e-2, "forward"
+    assert rel_err(x.grad.cpu(), xr.grad) < 2e-2, "dgrad"
+    assert rel_err(w.grad.cpu(), wr.grad) < 2e-2, "wgrad"
+    assert rel_err(b.grad.cpu(), br.grad) < 2e-2
+
+
+def test_resnet20_and_resnet50_block_step_on_gpu():
+    from distriflow_b200.models.resnet import Bottleneck, resnet20, resnet_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    torch.manual_seed(0)
+    m = resnet20().to(dev())
+    eng = DataParallelEngine(m, resnet_loss, {"optimizer": "momentum", "learningRate": 0.05}, device=dev())
+    x = torch.randn(32, 32, 32, 3, device=dev())
+    y = torch.randint(0, 10, (32,), device=dev())
+    l0 = float(eng.step(x, y))
+    for _ in range(10):
+        l1 = float(eng.step(x, y))
+    assert l1 == l1 and l1 < l0, (l0, l1)
+    blk = Bottleneck(256, 64, 1, "b").to(dev()).to(torch.bfloat16)        # ResNet-50 stage-1 block: all convs on tcgen05
+    xb = torch.randn(4, 56, 56, 256, device=dev()).bfloat16().requires_grad_(True)
+    out = blk(xb)
+    out.float().square().mean().backward()
+    assert torch.isfinite(out.float()).all() and torch.isfinite(xb.grad.float()).all()
