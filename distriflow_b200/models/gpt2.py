@@ -75,6 +75,10 @@ class GPT2(nn.Module):
         self.input_shape = [c.n_positions]
         self.output_shape = [c.n_positions, c.padded_vocab]
 
+    def first_dense_kernel(self):
+        """The first GEMM of the forward pass (block 0 QKV projection): its all-gather is fused into that GEMM."""
+        return self.h[0].c_attn.kernel
+
     def num_params(self) -> int:
         c = self.config
         return sum(p.numel() for p in self.parameters()) - (c.padded_vocab - c.vocab_size) * c.n_embd

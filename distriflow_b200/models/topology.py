@@ -48,6 +48,14 @@ class SequentialModel(nn.Module):
         self.train(was)
         return list(y.shape[1:])
 
+    def first_dense_kernel(self):
+        for layer in self.layers:
+            if isinstance(layer, L.Dense):
+                return layer.kernel
+            if isinstance(layer, L.Conv2D):
+                return None
+        return None
+
     # weight naming follows tfjs: "<layer_name>/kernel|bias|gamma|beta|moving_mean|moving_variance"
     def named_weights(self) -> List[Tuple[str, torch.Tensor]]:
         out = []

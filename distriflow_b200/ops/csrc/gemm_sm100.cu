@@ -47,6 +47,13 @@ struct GemmParams {
   int splits;           // split-K factor (1 = none)
   int kb_per_split;     // k-blocks per split
   int split_rows;       // row offset between splits in the fp32 workspace (multiple of 128)
+  // fused all-gather of the B operand (kGather kernels only): B = W[K,N] MN-major, sharded over ranks along K
+  const long long* pieces;    // [num_pieces][4] = {src (peer) address, dst (local) address, bytes, k-block}
+  const int* piece_chunk0;    // [num_pieces + 1] prefix sums of 512-byte chunks
+  const unsigned* expected;   // [k-blocks] remote bytes each k-block waits for
+  unsigned* ready;            // [k-blocks] bytes landed so far (zeroed before the launch)
+  int num_pieces;
+  int rot_kb;                 // k-loop starts at this k-block (first locally owned one) and wraps around
 };
 
 __device__ __forceinline__ float gelu_tanh(float x) {
@@ -57,8 +64,8 @@ __device__ __forceinline__ float gelu_tanh(float x) {
   return 0.5f * x * (1.0f + t);
 }
 
-template <int BLOCK_N, typename OutT>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int BLOCK_N, typename OutT, bool kGather = false>
+__global__ void __launch_bounds__(kThreads + (kGather ? 64 : 0), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
   using Cfg = GemmCfg<BLOCK_N>;
@@ -130,7 +137,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m0 = m_blk * kBlockM, n0 = n_blk * BLOCK_N;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, kb_total);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int it = 0; it < kb1 - kb0; ++it) {
+          int kb = kb0 + it;
+          if constexpr (kGather) {
+            kb = kb0 + (it + p.rot_kb) % (kb1 - kb0);
+            const unsigned need = p.expected[kb];
+            if (need) {                           // wait until the gather warps (of any CTA) have landed this k-block of W
+              unsigned have;
+              do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(have) : "l"(p.ready + kb) : "memory");
+              } while (have < need);
+              fence_proxy_async_all();            // generic-proxy stores -> visible to the TMA (async proxy) read below
+            }
+          }
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           uint8_t* sa = smem_a + stage * kATileBytes;
@@ -176,7 +195,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int it = 0; it < kb1 - kb0; ++it) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint64_t a_desc = make_smem_desc_sw128(smem_u32(smem_a + stage * kATileBytes), a_lbo, 1024);
@@ -184,7 +203,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             umma_f16(tmem_d, a_desc + (uint64_t)(k * a_kstep), b_desc + (uint64_t)(k * b_kstep), idesc,
-                     (kb > kb0 || k > 0) ? 1u : 0u);
+                     (it > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);            // frees the smem slot once these MMAs have read it
           if (++stage == kStages) {
@@ -197,6 +216,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           acc = 0;
           acc_phase ^= 1;
         }
+      }
+    }
+  } else if (kGather && warp_idx >= 6) {
+    // ===================================================================== gather warps: pull remote shards of W into the local buffer
+    // Work is claimed dynamically (atomic ticket) so that progress never depends on a CTA that is not resident yet.
+    const int total = p.piece_chunk0[p.num_pieces];
+    unsigned* ticket = p.ready + ceil_div(p.K, kBlockK);
+    while (true) {
+      int c = 0;
+      if (lane == 0) c = (int)atomicAdd(ticket, 1u);
+      c = __shfl_sync(0xffffffff, c, 0);
+      if (c >= total) break;
+      int piece = 0;
+      while (c >= p.piece_chunk0[piece + 1]) ++piece;
+      const long long* pc = p.pieces + 4 * piece;
+      const long base = (long)(c - p.piece_chunk0[piece]) * 512;
+      const long off = base + lane * 16;
+      const long bytes = pc[2];
+      if (off < bytes) {
+        uint4 v;
+        asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(pc[0] + off) : "memory");
+        *reinterpret_cast<uint4*>(pc[1] + off) = v;
+      }
+      __threadfence();
+      __syncwarp();
+      if (lane == 0) {
+        const long left = bytes - base;
+        const unsigned n = (unsigned)(left < 512 ? left : 512);
+        asm volatile("red.release.gpu.global.add.u32 [%0], %1;\n" ::"l"(p.ready + (int)pc[3]), "r"(n) : "memory");
       }
     }
   } else {
@@ -346,11 +395,11 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, OutT* __restr
   }
 }
 
-template <int BLOCK_N, typename OutT>
+template <int BLOCK_N, typename OutT, bool kGather = false>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const GemmParams& p,
                        int max_ctas, cudaStream_t stream) {
   using Cfg = GemmCfg<BLOCK_N>;
-  auto kern = gemm_tcgen05_kernel<BLOCK_N, OutT>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, OutT, kGather>;
   static bool configured = false;      // per instantiation; attribute is per device function (all devices of one kind)
   if (!configured) {
     DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -359,7 +408,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
   const int tiles = ceil_div(p.M, kBlockM) * ceil_div(p.N, BLOCK_N) * p.splits;
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-  kern<<<grid, kThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, tmD, p);
+  kern<<<grid, kThreads + (kGather ? 64 : 0), Cfg::kSmemBytes, stream>>>(tmA, tmB, tmD, p);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -416,6 +465,7 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
   splits = ceil_div(kb_total, kb_per);
 
   GemmParams p;
+  memset(&p, 0, sizeof(p));
   p.bias = bias; p.bias_dtype = bias_dtype; p.M = M; p.N = N; p.K = K; p.a_mn = a_mn_major ? 1 : 0; p.b_mn = b_mn_major ? 1 : 0;
   p.act = act; p.splits = splits; p.kb_per_split = kb_per; p.split_rows = 0;
 
@@ -464,6 +514,40 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
                           : launch_gemm<128, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream);
   return block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, p, max_ctas, stream)
                         : launch_gemm<128, float>(tmA, tmB, tmD, p, max_ctas, stream);
+}
+
+// All-gather fused into the GEMM that first consumes the gathered weights (BASELINE north star, SURVEY K8+K1):
+//   D[M,N] = act(A[M,K] * W[K,N] + bias), W row-major (MN-major B) and sharded over the ranks in contiguous byte ranges.
+// `pieces` (device, int64 [num_pieces][4] = {peer source address, local destination address, bytes, k-block}) lists
+// the remote ranges of W, cut at k-block (64-row) boundaries; `piece_chunk0` (device, int32 [num_pieces+1]) are prefix sums
+// of their 512-byte chunk counts; `expected` (device, uint32 [k-blocks]) the remote bytes per k-block; `ready` (device,
+// uint32 [k-blocks + 1]) is zeroed here.  Two extra warps per CTA copy the remote shards into the local W buffer over
+// NVLink while the k-loop starts on the locally owned rows (`rot_kb`); the TMA producer waits on `ready[kb]` per k-block.
+// The owners' slices must be final (the closing barrier of the bucket kernel guarantees it).
+DFB_API int dfb_ag_gemm_bf16(const void* A, const void* W_local, void* D, const void* bias, int bias_dtype, int M, int N, int K,
+                             int lda, int ldb, int ldd, int out_dtype, int act, int block_n, const long long* pieces,
+                             const int* piece_chunk0, int num_pieces, const unsigned* expected, unsigned* ready, int rot_kb,
+                             cudaStream_t stream) {
+  DFB_REQUIRE(M > 0 && N > 0 && K > 0, "ag_gemm: empty problem");
+  DFB_REQUIRE(block_n == 128 || block_n == 256, "ag_gemm: block_n must be 128 or 256");
+  DFB_REQUIRE(out_dtype == DT_BF16, "ag_gemm: bf16 output only");
+  DFB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldd % 8) == 0, "ag_gemm: pitches must be multiples of 8 elements");
+  const int kb_total = ceil_div(K, kBlockK);
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.bias = bias; p.bias_dtype = bias_dtype; p.M = M; p.N = N; p.K = K; p.a_mn = 0; p.b_mn = 1; p.act = act; p.splits = 1;
+  p.kb_per_split = kb_total; p.pieces = pieces; p.piece_chunk0 = piece_chunk0; p.expected = expected; p.ready = ready;
+  p.num_pieces = num_pieces; p.rot_kb = ((rot_kb % kb_total) + kb_total) % kb_total;
+  CUtensorMap tmA, tmB, tmD;
+  if (make_operand_map(&tmA, A, M, K, lda, 0, kBlockM)) return 4;
+  if (make_operand_map(&tmB, W_local, N, K, ldb, 1, block_n)) return 4;
+  uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+  uint64_t str[1] = {(uint64_t)ldd * 2};
+  uint32_t box[2] = {64, 128};
+  if (encode_tmap(&tmD, D, 0, 2, dims, str, box, nullptr, 1)) return 4;
+  DFB_CUDA_CHECK(cudaMemsetAsync(ready, 0, (size_t)(kb_total + 1) * sizeof(unsigned), stream));
+  return block_n == 256 ? launch_gemm<256, __nv_bfloat16, true>(tmA, tmB, tmD, p, 0, stream)
+                        : launch_gemm<128, __nv_bfloat16, true>(tmA, tmB, tmD, p, 0, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -78,6 +78,21 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int, N:
     return out
 
 
+def ag_gemm(x2: torch.Tensor, w: torch.Tensor, plan, bias: Optional[torch.Tensor] = None, act: Optional[str] = None) -> torch.Tensor:
+    """Forward GEMM `act(x2 @ w + bias)` that also gathers the remote shards of `w` (see parallel/ag_fusion.py)."""
+    L = _lib.lib()
+    M, K = x2.shape
+    N = w.shape[1]
+    out = torch.empty((M, N), device=x2.device, dtype=x2.dtype)
+    bn, _ = pick_tile(M, N, K)
+    if bias is not None and bias.dtype not in (torch.float32, torch.bfloat16):
+        bias = bias.float()
+    check(L.dfb_ag_gemm_bf16(ptr(x2), ptr(w), ptr(out), ptr(bias), c_int(dt(bias) if bias is not None else 0), M, N, K,
+                             x2.stride(0), w.stride(0), out.stride(0), dt(out), ACT[act], bn, ptr(plan.pieces), ptr(plan.chunk0),
+                             plan.num_pieces, ptr(plan.expected), ptr(plan.ready), plan.rot_kb, stream()), "dfb_ag_gemm_bf16")
+    return out
+
+
 def colsum(x2d: torch.Tensor) -> torch.Tensor:
     L = _lib.lib()
     M, N = x2d.shape
@@ -113,6 +128,9 @@ def _init_sigs() -> None:
     L.dfb_gemm_simt.restype = c_int
     L.dfb_gemm_simt.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int] + [ctypes.c_long] * 5 + \
         [c_int] * 5 + [c_void_p]
+    L.dfb_ag_gemm_bf16.restype = c_int
+    L.dfb_ag_gemm_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 10 + [c_void_p, c_void_p, c_int, c_void_p,
+                                                                                          c_void_p, c_int, c_void_p]
     L.dfb_colsum.restype = c_int
     L.dfb_colsum.argtypes = [c_void_p, c_void_p, c_int, c_int, ctypes.c_long, c_int, c_void_p]
     L.dfb_act.restype = c_int
@@ -136,7 +154,18 @@ class _LinearFn(torch.autograd.Function):
         w = weight if weight.dtype == x2.dtype else weight.to(x2.dtype)
         M = x2.shape[0]
         saved_act = None
-        if activation == "gelu":
+        plan = getattr(weight, "_dfb_ag", None)
+        if plan is not None and plan.num_pieces > 0 and not transposed and w is weight and _tc_ok(x2, w) and N >= 16:
+            # the all-gather of this kernel is fused into its first consumer: this GEMM pulls the remote shards itself
+            if activation == "gelu":
+                pre = ag_gemm(x2, w, plan, bias)
+                y = act_op(pre, None, 0)
+                saved_act = pre
+            else:
+                y = ag_gemm(x2, w, plan, bias, activation)
+                if activation == "relu":
+                    saved_act = y
+        elif activation == "gelu":
             pre = gemm(x2, w, a_mn=False, b_mn=not transposed, M=M, N=N, K=K, bias=bias)
             y = act_op(pre, None, 0)
             saved_act = pre

@@ -114,6 +114,7 @@ struct SyncArgs {
   int rank, R;
   uint32_t epoch;        // barrier generation, strictly increasing per launch; 0 = no cross-rank barriers (emulation)
   int push;              // 1 = push refreshed weights to every rank, 0 = only write the local copy
+  long nopush_lo, nopush_hi;   // bucket-relative element range that is NOT pushed (its all-gather is fused into the consumer GEMM)
   OptParams opt;
 };
 
@@ -201,9 +202,10 @@ __global__ void __launch_bounds__(512) sync_rs_opt_ag_kernel(const SyncArgs a) {
       for (int h = 0; h < PV; ++h)
 #pragma unroll
         for (int j = 0; j < VP::kN; ++j) o[h].set(j, w[h * VP::kN + j]);
+      const bool pushed = a.push && !(e >= a.nopush_lo && e < a.nopush_hi);
 #pragma unroll
       for (int q = 0; q < kMaxRanks; ++q) {
-        if (q < R && (a.push || q == a.rank)) {
+        if (q < R && (pushed || q == a.rank)) {
           TP* dst = reinterpret_cast<TP*>(a.params.p[q]) + e;
 #pragma unroll
           for (int h = 0; h < PV; ++h) st_peer_v4(dst + h * VP::kN, o[h].raw);
@@ -570,7 +572,7 @@ static void fill_peers(PeerPtrs& d, void* const* src, int R) {
 DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
                                void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
                                int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
-                               float weight_decay, int step, int ctas, cudaStream_t stream) {
+                               float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, cudaStream_t stream) {
   DFB_REQUIRE(R >= 1 && R <= kMaxRanks && rank >= 0 && rank < R, "sync: bad rank %d / world %d", rank, R);
   DFB_REQUIRE(shard > 0 && (shard % 8) == 0, "sync: shard must be a positive multiple of 8 elements");
   DFB_REQUIRE(shard * R >= n, "sync: shard * R must cover the bucket");
@@ -581,7 +583,7 @@ DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* co
   if (sig) fill_peers(a.sig, sig, R); else memset(&a.sig, 0, sizeof(a.sig));
   DFB_REQUIRE(epoch == 0 || sig != nullptr, "sync: barriers need signal pads");
   a.master = master; a.m = m; a.v = v; a.reduced_out = reduced_out; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
-  a.epoch = epoch; a.push = push;
+  a.epoch = epoch; a.push = push; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi;
   a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
   a.opt.weight_decay = weight_decay;
   a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));

@@ -47,6 +47,7 @@ class Bucket:
         self.m: Optional[torch.Tensor] = None
         self.v: Optional[torch.Tensor] = None
         self.pending = 0
+        self.nopush = (0, 0)      # element range whose all-gather is fused into its consumer GEMM
 
 
 def _round_up(x: int, m: int) -> int:
@@ -75,6 +76,11 @@ class DataParallelEngine:
         self.versionCallbacks: List[Callable[[int, int], None]] = []
         self._build_buckets(heap)
         self._install_hooks()
+        if self.cfg["fuseAllGather"]:
+            first = getattr(model, "first_dense_kernel", None)
+            w = first() if callable(first) else None
+            if w is not None:
+                self.fuse_allgather(w)
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.device)
 
@@ -159,6 +165,21 @@ class DataParallelEngine:
 
                 p.register_post_accumulate_grad_hook(hook)
 
+    def fuse_allgather(self, weight: nn.Parameter) -> bool:
+        """Fuse the all-gather of `weight` (a Dense kernel `[in, out]`, bf16) into the GEMM that consumes it first."""
+        if self.backend != "p2p" or self.world == 1 or weight.dim() != 2 or self.param_dtype != torch.bfloat16:
+            return False
+        b = self._bucket_of.get(id(weight))
+        if b is None or b.nopush != (0, 0):
+            return False
+        from .ag_fusion import build_plan
+        off = b.offsets[[id(p) for p in b.params].index(id(weight))]
+        K, N = weight.shape
+        bases = [self.heap.peer_bases[q] + b.param_off for q in range(self.world)]
+        weight._dfb_ag = build_plan(K, N, 2, off, b.shard, self.rank, self.world, bases, self.device)
+        b.nopush = (off, off + weight.numel())
+        return True
+
     # ------------------------------------------------------------------------------------ step
     def on_new_version(self, cb: Callable[[int, int], None]) -> None:
         self.versionCallbacks.append(cb)
@@ -217,7 +238,8 @@ class DataParallelEngine:
                                        ptr(b.master), ptr(b.m), ptr(b.v), None, b.numel, b.shard, self.rank, self.world,
                                        epoch, 1, dt(b.grad_buf), dt(b.param_buf), _OPT[c["optimizer"]], self.lr,
                                        c["momentum"], c["beta1"], c["beta2"], c["eps"], c["weightDecay"], self.version + 1,
-                                       self.comm_ctas if self.world > 1 else 148 * 2, _lib.stream()), "dfb_sync_rs_opt_ag")
+                                       self.comm_ctas if self.world > 1 else 148 * 2, b.nopush[0], b.nopush[1], _lib.stream()),
+                  "dfb_sync_rs_opt_ag")
         self._launches += 1
 
     def _launch_bucket_torch(self, b: Bucket) -> None:
@@ -297,7 +319,7 @@ def _comm_sigs():
         L.dfb_sync_rs_opt_ag.restype = c_int
         L.dfb_sync_rs_opt_ag.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int,
                                          c_int, ctypes.c_uint, c_int, c_int, c_int, c_int, c_float, c_float, c_float, c_float,
-                                         c_float, c_float, c_int, c_int, c_void_p]
+                                         c_float, c_float, c_int, c_int, ctypes.c_long, ctypes.c_long, c_void_p]
         L.dfb_allgather_push.restype = c_int
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int

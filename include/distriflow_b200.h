@@ -29,6 +29,13 @@ int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int b
                   int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits,
                   void* workspace, size_t workspace_bytes, int max_ctas, void* stream);
 
+/* All-gather fused into the first consuming GEMM: D = act(A * W + bias) with W[K,N] sharded over ranks; two extra warps
+ * per CTA pull the remote shards over NVLink into the local W buffer while the k-loop starts on local rows.
+ * Replaces the weight broadcast of /root/reference/src/server/federated_server.ts:80 for that layer (SURVEY K8+K1). */
+int dfb_ag_gemm_bf16(const void* A, const void* W_local, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda,
+                     int ldb, int ldd, int out_dtype, int act, int block_n, const long long* pieces, const int* piece_chunk0,
+                     int num_pieces, const unsigned* expected, unsigned* ready, int rot_kb, void* stream);
+
 /* Split-K GEMM that allocates nothing: same arguments as dfb_gemm_bf16 minus the workspace, which is a 32 MiB
  * array inside the library (one per GPU, shared by all calls, kept until exit).  For callers that cannot
  * allocate device memory themselves (no-sync step loops, C plug-ins inside a process whose pool owns the GPU).
@@ -93,7 +100,7 @@ int dfb_enable_peer_access(int peer_device);
 int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
                        void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
                        int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
-                       float weight_decay, int step, int ctas, void* stream);
+                       float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, void* stream);
 int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
                        int ctas, void* stream);
 int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
@@ -103,7 +110,7 @@ int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void*
                    int grad_dtype, int ctas, void* stream);
 int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
                     unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum, float beta1,
-                    float beta2, float eps, float weight_decay, int step, int ctas, void* stream);
+                    float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, void* stream);
 int dfb_async_pull(void* const* params, void* const* sig, void* dst, unsigned* seen_version, long n_bytes, long shard_bytes,
                    int rank, int R, int ctas, void* stream);
 int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, void* stream);

@@ -66,7 +66,7 @@ def test_sync_rs_opt_ag_emulated(R, kind, gdt, pdt):
             check(L.dfb_sync_rs_opt_ag(h.ptrs(offs["g"]), h.ptrs(offs["p"]), None, ptr(masters[r]), ptr(ms[r]), ptr(vs[r]), None,
                                        n, shard, r, R, 0, 1, dt(heaps[0].view(offs["g"], (1,), gdt)),
                                        dt(heaps[0].view(offs["p"], (1,), pdt)), OPT[kind], 0.01, 0.9, 0.9, 0.999, 1e-8, 0.0, step,
-                                       8, stream()), "sync")
+                                       8, 0, 0, stream()), "sync")
         torch.cuda.synchronize()
         wr, mr, vr = _ref_opt(kind, wr, gmean, mr, vr, 0.01, step)
         full_master = torch.cat(masters)
@@ -92,7 +92,7 @@ def test_reduced_out_and_no_push():
     red = torch.empty(shard, device=dev(), dtype=torch.bfloat16)
     master = torch.zeros(shard, device=dev())
     check(L.dfb_sync_rs_opt_ag(heaps[1].ptrs(offs["g"]), heaps[1].ptrs(offs["p"]), None, ptr(master), None, None, ptr(red), n, shard,
-                               1, R, 0, 0, 1, 1, OPT["none"], 0.0, 0.0, 0.9, 0.999, 1e-8, 0.0, 1, 4, stream()), "sync")
+                               1, R, 0, 0, 1, 1, OPT["none"], 0.0, 0.0, 0.9, 0.999, 1e-8, 0.0, 1, 4, 0, 0, stream()), "sync")
     torch.cuda.synchronize()
     ref = sum(g.float() for g in gs)[shard:2 * shard] / R
     assert torch.allclose(red.float(), ref, rtol=1e-2, atol=1e-2)
@@ -201,3 +201,42 @@ def test_gather_batch_from_ticket():
     t = wq.take()                                      # batch 2
     out = wq.gather(data, 4)
     assert t.batch == 2 and torch.equal(out, data[8:12])
+
+
+@pytest.mark.parametrize("R", [2, 8])
+def test_allgather_fused_gemm_emulated(R):
+    """Each emulated rank holds only its own slice of W; the fused GEMM must pull the rest and produce x @ W."""
+    from distriflow_b200.ops.dense import _init_sigs, ag_gemm
+    from distriflow_b200.parallel.ag_fusion import build_plan
+    from distriflow_b200.parallel.symm import SymmetricHeap
+    _init_sigs()
+    torch.manual_seed(R)
+    M, K, N = 1024, 768, 2304
+    w_off = 64 * 5                                    # W does not start at the bucket start
+    numel = K * N
+    total = ((w_off + numel + 64 * 3 + R * 64 - 1) // (R * 64)) * (R * 64)
+    shard = total // R
+    heaps = SymmetricHeap.emulated(R, total * 2 + 65536)
+    offs = [h.alloc(total * 2) for h in heaps][0]
+    W = (torch.randn(K, N, device=dev()) * 0.05).bfloat16()
+    x = torch.randn(M, K, device=dev()).bfloat16()
+    bias = torch.randn(N, device=dev())
+    flat = torch.zeros(total, device=dev(), dtype=torch.bfloat16)
+    flat[w_off:w_off + numel] = W.reshape(-1)
+    for r, h in enumerate(heaps):                     # every rank: own slice correct, everything else poisoned
+        buf = h.view(offs, (total,), torch.bfloat16)
+        buf.fill_(float("nan"))
+        buf[r * shard:(r + 1) * shard] = flat[r * shard:(r + 1) * shard]
+    ref = torch.relu(x.float() @ W.float() + bias)
+    for r, h in enumerate(heaps):
+        bases = [hh.base + offs for hh in heaps]
+        plan = build_plan(K, N, 2, w_off, shard, r, R, bases, dev())
+        w_local = h.view(offs, (total,), torch.bfloat16)[w_off:w_off + numel].view(K, N)
+        assert plan.num_pieces > 0 and plan.remote_bytes > 0
+        y = ag_gemm(x, w_local, plan, bias, "relu")
+        torch.cuda.synchronize()
+        assert torch.equal(w_local, W), "gathered weights differ"
+        err = float((y.float() - ref).abs().max() / ref.abs().max())
+        assert err < 1e-2, err
+    for h in heaps:
+        h.close()

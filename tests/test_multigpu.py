@@ -36,6 +36,14 @@ def _sync_worker(rank, world, port, out):
         for _ in range(6):
             losses.append(float(eng.step(idx[:, :-1].contiguous(), idx[:, 1:].contiguous())))
         torch.cuda.synchronize()
+        if backend == "p2p":
+            with torch.no_grad():                      # one more forward: the fused all-gather GEMM refreshes its kernel
+                gpt2_loss(model, idx[:, :-1].contiguous(), idx[:, 1:].contiguous())
+            torch.cuda.synchronize()
+            masters = eng.full_precision_weights()
+            live = [p for p in model.parameters() if p.requires_grad]
+            res["working_equals_master"] = all(torch.equal(p.data, m.to(p.dtype)) for p, m in zip(live, masters))
+            res["fused"] = getattr(model.first_dense_kernel(), "_dfb_ag", None) is not None
         w = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
         res[backend] = (losses, w.cpu())
         ws = [torch.empty_like(w) for _ in range(world)]
@@ -59,7 +67,8 @@ def test_sync_engine_p2p_matches_nccl(world, tmp_path):
     ln, wn = res["nccl"]
     assert lp[-1] < lp[0]
     assert max(abs(a - b) for a, b in zip(lp, ln)) < 5e-2, (lp, ln)
-    assert float((wp - wn).abs().max()) < 5e-3
+    assert float((wp - wn).abs().max()) < 2e-2          # bf16 gradients: fp32 pull-reduce vs NCCL's bf16 ring
+    assert res["fused"] and res["working_equals_master"], "a rank's working weights differ from the gathered masters"
 
 
 def _async_worker(rank, world, port, out):
