@@ -98,14 +98,15 @@ class AsyncShardState:
         check(self.L.dfb_async_pull(h.ptrs(lo.p_off), h.ptrs(0), ptr(lo.params), ptr(lo.seen), self.n * self.psz,
                                     self.shard * self.psz, r, self.world, self.ctas, _lib.stream()), "dfb_async_pull")
 
-    def push(self, rank: Optional[int], grad: torch.Tensor, scale: float = 1.0) -> None:
+    def push(self, rank: Optional[int], grad: torch.Tensor, scale: float = 1.0, ticket: Optional[torch.Tensor] = None) -> None:
         r = self._one(rank)
         lo = self.loc[r]
         h = lo.heap
         assert grad.numel() == self.n and grad.is_contiguous(), (grad.numel(), self.n)
         check(self.L.dfb_async_push(ptr(grad), h.ptrs(lo.a0_off), h.ptrs(lo.a1_off), h.ptrs(0), ptr(lo.seen), ptr(lo.push_state),
                                     self.n, self.shard, r, self.world, self.max_staleness, scale,
-                                    1 if self.policy == "scale" else 0, dt(grad), self.ctas, _lib.stream()), "dfb_async_push")
+                                    1 if self.policy == "scale" else 0, dt(grad), self.ctas, ptr(ticket), _lib.stream()),
+              "dfb_async_push")
 
     def apply(self, rank: Optional[int] = None) -> None:
         r = self._one(rank)
@@ -205,6 +206,45 @@ class AsyncEngine:
         self.state.apply()
         self.version += 1
         return loss.detach()
+
+    def run_dataset(self, wq, x_all: torch.Tensor, y_all: torch.Tensor, batch_size: int, max_steps: int = 1 << 30,
+                    on_step: Optional[Callable[[int, torch.Tensor], None]] = None) -> int:
+        """Train until the device work queue is exhausted.  `x_all` / `y_all` are device-resident; every step takes a
+        ticket on the device, gathers its rows by that ticket, trains on it and marks it complete — the host never
+        sees a batch index on the critical path.  It looks at a copy of the ticket a few steps late only to learn that
+        the queue is done; the steps issued after that are no-ops on the device (ticket = 0xffffffff)."""
+        xb = torch.empty((batch_size, *x_all.shape[1:]), dtype=x_all.dtype, device=x_all.device)
+        yb = torch.empty((batch_size, *y_all.shape[1:]), dtype=y_all.dtype, device=y_all.device)
+        lag = []          # (event, pinned copy of the ticket)
+        n = 0
+        while n < max_steps:
+            t = wq.take_async()
+            wq.gather(x_all, batch_size, xb)
+            wq.gather(y_all, batch_size, yb)
+            self.state.pull()
+            loss = self.loss_fn(self.model, xb, yb)
+            loss.backward()
+            self.state.push(None, self.grad_flat, ticket=t)
+            self.state.apply()
+            wq.complete()
+            host = torch.empty(2, dtype=torch.int32, pin_memory=True)
+            host.copy_(t, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            lag.append((ev, host))
+            n += 1
+            self.version += 1
+            if on_step is not None:
+                on_step(n, loss.detach())
+            done = False
+            while lag and (lag[0][0].query() or len(lag) > 4):
+                ev0, h0 = lag.pop(0)
+                ev0.synchronize()
+                if (int(h0[0]) & 0xFFFFFFFF) == 0xFFFFFFFF:
+                    done = True
+            if done:
+                break
+        return n
 
     def drain(self) -> None:
         """Apply whatever is still in flight (call on every rank after the last step, then barrier)."""

@@ -285,12 +285,17 @@ struct AsyncPushArgs {
   int max_staleness;
   float scale;           // multiplies the gradient (1.0, or 1/(1+staleness) is applied per owner when policy = scale)
   int policy_scale;
+  const uint32_t* ticket;  // optional work-queue ticket of this step: 0xffffffff (dataset exhausted) turns the push into a no-op
 };
 
 // Phase 1 (one block): per owner, read its version, apply the staleness guard, register as in-flight pusher.
 __global__ void async_push_begin_kernel(const AsyncPushArgs a) {
   const int o = threadIdx.x;
   if (o >= a.R) return;
+  if (a.ticket != nullptr && a.ticket[0] == 0xffffffffu) {      // no batch was dispatched for this step: nothing to push
+    a.push_state[o] = 0xffffffffu;
+    return;
+  }
   uint32_t* ctl = reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase;
   const uint32_t ver = ld_acquire_sys(ctl + A_VERSION);
   const int staleness = (int)(ver - a.seen_version[o]);
@@ -639,7 +644,8 @@ DFB_API int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, 
 
 DFB_API int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void* const* sig,
                            const unsigned* seen_version, unsigned* push_state, long n, long shard, int rank, int R,
-                           int max_staleness, float scale, int policy_scale, int grad_dtype, int ctas, cudaStream_t stream) {
+                           int max_staleness, float scale, int policy_scale, int grad_dtype, int ctas, const unsigned* ticket,
+                           cudaStream_t stream) {
   DFB_REQUIRE(R >= 1 && R <= kMaxRanks && (shard % 8) == 0, "async_push: bad arguments");
   AsyncPushArgs a;
   a.grad = grad;
@@ -647,7 +653,7 @@ DFB_API int dfb_async_push(const void* grad, void* const* acc0, void* const* acc
   fill_peers(a.acc1, acc1, R);
   fill_peers(a.sig, sig, R);
   a.seen_version = seen_version; a.push_state = push_state; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
-  a.max_staleness = max_staleness; a.scale = scale; a.policy_scale = policy_scale;
+  a.max_staleness = max_staleness; a.scale = scale; a.policy_scale = policy_scale; a.ticket = ticket;
   async_push_begin_kernel<<<1, 32, 0, stream>>>(a);
   int grid = ctas > 0 ? ctas : 32;
   if (grad_dtype == DT_BF16) async_push_data_kernel<__nv_bfloat16><<<grid, 512, 0, stream>>>(a);

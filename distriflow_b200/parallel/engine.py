@@ -326,7 +326,7 @@ def _comm_sigs():
         L.dfb_rank_barrier.argtypes = [P, c_int, c_int, ctypes.c_uint, c_void_p]
         L.dfb_async_push.restype = c_int
         L.dfb_async_push.argtypes = [c_void_p, P, P, P, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int, c_int,
-                                     c_float, c_int, c_int, c_int, c_void_p]
+                                     c_float, c_int, c_int, c_int, c_void_p, c_void_p]
         L.dfb_async_apply.restype = c_int
         L.dfb_async_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       ctypes.c_long, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int,

@@ -107,7 +107,7 @@ int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* st
 /* async path (asynchronousSGD_server.ts:65-108): push with staleness guard, in-place apply, pull */
 int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void* const* sig, const unsigned* seen_version,
                    unsigned* push_state, long n, long shard, int rank, int R, int max_staleness, float scale, int policy_scale,
-                   int grad_dtype, int ctas, void* stream);
+                   int grad_dtype, int ctas, const unsigned* ticket, void* stream);
 int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
                     unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum, float beta1,
                     float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, void* stream);

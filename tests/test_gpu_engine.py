@@ -146,3 +146,40 @@ def test_engine_checkpoint_from_master_weights(tmp_path):
 def test_graft_smoke():
     import __graft_entry__ as g
     g.smoke()
+
+
+def test_async_engine_with_device_work_queue_single_gpu():
+    """world = 1: ticket -> gather -> pull -> fit -> push -> apply -> complete; every batch exactly once per epoch."""
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.oracle import synthetic_mnist
+    from distriflow_b200.parallel.async_engine import AsyncEngine
+    from distriflow_b200.parallel.workqueue import DeviceWorkQueue
+    torch.manual_seed(0)
+    x, y = synthetic_mnist(256, seed=2)
+    xd, yd = torch.from_numpy(x).to(dev()), torch.from_numpy(y).to(dev())
+    net = mnist_mlp(softmax_output=False).to(dev())
+    ce = get_loss("softmaxCrossEntropy")
+    eng = AsyncEngine(net, lambda m, a, b: ce(b, m(a)), {"optimizer": "sgd", "learningRate": 1e-4, "dtype": "fp32", "gradDtype": "fp32",
+                                                         "maximumStaleness": 4}, device=dev())
+    wq = DeviceWorkQueue(eng.state.heaps[0], 8, 2)
+    losses = []
+    n = eng.run_dataset(wq, xd, yd, 32, on_step=lambda i, l: losses.append(float(l)))
+    eng.drain()
+    c = eng.counters()
+    assert c["applied"] == 16 and c["dropped"] == 0 and c["version"] == 16, c      # 8 batches x 2 epochs, nothing lost
+    assert 16 <= n <= 16 + 6                                                         # a few no-op steps after the queue drained
+    assert losses[15] < losses[0]
+    assert wq.take().done
+
+
+def test_metric_ring():
+    from distriflow_b200.utils.metrics import DeviceMetricRing
+    ring = DeviceMetricRing(slots=4, device=dev())
+    pred = torch.randn(64, 10, device=dev())
+    lab = torch.randint(0, 10, (64,), device=dev())
+    for i in range(6):
+        ring.record(pred, lab, loss=torch.tensor(float(i), device=dev()))
+    got = ring.poll(block=True)
+    assert len(got) == 6 and got[-1]["loss"] == 5.0
+    assert abs(got[0]["accuracy"] - float((pred.argmax(-1) == lab).float().mean())) < 1e-6
