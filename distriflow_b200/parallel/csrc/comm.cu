@@ -509,17 +509,18 @@ __global__ void wq_complete_kernel(uint32_t* wq, const uint32_t* ticket) {
 }
 
 // Gather the rows of batch `ticket[0]` from a device-resident dataset: dst[r, :] = src[(b*bs + r) % rows, :].
+template <typename U>
 __global__ void __launch_bounds__(256) gather_batch_kernel(const char* __restrict__ src, char* __restrict__ dst,
                                                            const uint32_t* __restrict__ ticket, long row_bytes, int batch_size,
                                                            long rows) {
   const uint32_t b = ticket[0];
   if (b == 0xffffffffu) return;
-  const long vec_per_row = row_bytes / 16;
+  const long vec_per_row = row_bytes / (long)sizeof(U);
   const long total = vec_per_row * batch_size;
   for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
     const long r = i / vec_per_row, c = i - r * vec_per_row;
     const long sr = ((long)b * batch_size + r) % rows;
-    reinterpret_cast<uint4*>(dst + r * row_bytes)[c] = reinterpret_cast<const uint4*>(src + sr * row_bytes)[c];
+    reinterpret_cast<U*>(dst + r * row_bytes)[c] = reinterpret_cast<const U*>(src + sr * row_bytes)[c];
   }
 }
 
@@ -729,12 +730,14 @@ DFB_API int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, cudaStr
 DFB_API int dfb_wq_pad_words(unsigned batches) { return kWqBase + W_BITMAP + (int)((batches + 31) / 32); }
 DFB_API int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                              cudaStream_t stream) {
-  DFB_REQUIRE((row_bytes % 16) == 0, "gather_batch: row size must be a multiple of 16 bytes");
-  long total = row_bytes / 16 * batch_size;
+  DFB_REQUIRE((row_bytes % 4) == 0, "gather_batch: row size must be a multiple of 4 bytes");
+  const bool wide = (row_bytes % 16) == 0 && ((uintptr_t)src % 16) == 0 && ((uintptr_t)dst % 16) == 0;
+  long total = row_bytes / (wide ? 16 : 4) * batch_size;
   long blocks = (total + 255) / 256;
   if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   if (blocks < 1) blocks = 1;
-  gather_batch_kernel<<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, ticket, row_bytes, batch_size, rows);
+  if (wide) gather_batch_kernel<uint4><<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, ticket, row_bytes, batch_size, rows);
+  else gather_batch_kernel<uint32_t><<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, ticket, row_bytes, batch_size, rows);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
