@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--optimizer", default="adam")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--comm-ctas", type=int, default=64)
+    ap.add_argument("--comm-ctas", type=int, default=148)
     ap.add_argument("--reserve-sms", type=int, default=0)
     return ap.parse_args()
 

@@ -78,7 +78,7 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "overlap": True,              # launch bucket reduce on a side stream during backward
     "backend": "p2p",             # "p2p" (own kernels) | "nccl" (baseline) | "gloo" (CPU plumbing)
     "fuseAllGather": True,        # all-gather fused into the first consuming GEMM
-    "commCtas": 64,               # CTAs of the fused collective kernel (512 threads, <= 64 regs: co-resides with a GEMM CTA)
+    "commCtas": 148,              # CTAs of the fused collective kernel (256 threads x <= 128 regs: co-resides with a GEMM CTA)
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
 }
 

@@ -119,96 +119,112 @@ struct SyncArgs {
 };
 
 template <typename TG, typename TP, int R_T>
-__global__ void __launch_bounds__(512) sync_rs_opt_ag_kernel(const SyncArgs a) {
+__global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {   // 256 x <=128 regs: shares an SM with a GEMM CTA
   const int R = R_T > 0 ? R_T : a.R;
   if (a.epoch) rank_barrier(a.sig, a.rank, R, kSigIn, a.epoch, blockIdx.x == 0);   // everybody's gradients are final
   using VG = Vec16<TG>;
-  constexpr int VN = 8;                       // elements per thread-iteration (16 B of bf16, or 2 x 16 B of fp32)
-  constexpr int GV = VN / VG::kN;             // 16-byte loads per peer per iteration
+  constexpr int VN = 8;                       // elements per vector (16 B of bf16, or 2 x 16 B of fp32)
+  constexpr int GV = VN / VG::kN;             // 16-byte loads per peer per vector
+  // vectors per thread-iteration: keep ~8 peer loads of 16 B in flight per thread whatever the world size, so that the
+  // NVLink latency (~2 us) is covered at R = 2 as well as at R = 8
+  constexpr int U = (R_T == 2 && GV == 1) ? 4 : ((R_T == 4 && GV == 1) || (R_T == 2)) ? 2 : 1;
   const long lo = (long)a.rank * a.shard;
   const long hi = min(a.n, lo + a.shard);
   const long nvec = hi > lo ? (hi - lo + VN - 1) / VN : 0;
   const float inv_r = 1.f / (float)R;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
-    const long e = lo + i * VN;               // first element (bucket-relative)
-    VG g[kMaxRanks][GV];
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+    VG g[U][kMaxRanks][GV];
 #pragma unroll
-    for (int q = 0; q < kMaxRanks; ++q) {
-      if (q < R) {
-        const TG* src = reinterpret_cast<const TG*>(a.grads.p[q]) + e;
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * stride;
+      if (i < nvec) {
+        const long e = lo + i * VN;
 #pragma unroll
-        for (int h = 0; h < GV; ++h) g[q][h].raw = ld_peer_v4(src + h * VG::kN);
+        for (int q = 0; q < kMaxRanks; ++q) {
+          if (q < R) {
+            const TG* src = reinterpret_cast<const TG*>(a.grads.p[q]) + e;
+#pragma unroll
+            for (int h = 0; h < GV; ++h) g[u][q][h].raw = ld_peer_v4(src + h * VG::kN);
+          }
+        }
       }
     }
-    float acc[VN];
 #pragma unroll
-    for (int j = 0; j < VN; ++j) acc[j] = 0.f;
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * stride;
+      if (i >= nvec) continue;
+      const long e = lo + i * VN;               // first element (bucket-relative)
+      float acc[VN];
 #pragma unroll
-    for (int q = 0; q < kMaxRanks; ++q) {     // fixed order -> bitwise reproducible, identical on every rank
-      if (q < R) {
+      for (int j = 0; j < VN; ++j) acc[j] = 0.f;
 #pragma unroll
-        for (int h = 0; h < GV; ++h)
+      for (int q = 0; q < kMaxRanks; ++q) {     // fixed order -> bitwise reproducible, identical on every rank
+        if (q < R) {
 #pragma unroll
-          for (int j = 0; j < VG::kN; ++j) acc[h * VG::kN + j] += g[q][h].get(j);
+          for (int h = 0; h < GV; ++h)
+#pragma unroll
+            for (int j = 0; j < VG::kN; ++j) acc[h * VG::kN + j] += g[u][q][h].get(j);
+        }
       }
-    }
-    const long s = i * VN;                    // shard-relative
-    float w[VN];
-    {
-      const float4 w0 = *reinterpret_cast<const float4*>(a.master + s);
-      const float4 w1 = *reinterpret_cast<const float4*>(a.master + s + 4);
-      w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
-    }
-    float mm[VN], vv[VN];
-    if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
-      const float4 m0 = *reinterpret_cast<const float4*>(a.m + s), m1 = *reinterpret_cast<const float4*>(a.m + s + 4);
-      mm[0] = m0.x; mm[1] = m0.y; mm[2] = m0.z; mm[3] = m0.w; mm[4] = m1.x; mm[5] = m1.y; mm[6] = m1.z; mm[7] = m1.w;
-    }
-    if (a.opt.kind == OPT_ADAM) {
-      const float4 v0 = *reinterpret_cast<const float4*>(a.v + s), v1 = *reinterpret_cast<const float4*>(a.v + s + 4);
-      vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
-    }
-#pragma unroll
-    for (int j = 0; j < VN; ++j) {
-      acc[j] *= inv_r;
-      w[j] = opt_step(w[j], acc[j], &mm[j], &vv[j], a.opt);
-    }
-    if (a.opt.kind != OPT_NONE) {
-      *reinterpret_cast<float4*>(a.master + s) = make_float4(w[0], w[1], w[2], w[3]);
-      *reinterpret_cast<float4*>(a.master + s + 4) = make_float4(w[4], w[5], w[6], w[7]);
+      const long s = i * VN;                    // shard-relative
+      float w[VN];
+      {
+        const float4 w0 = *reinterpret_cast<const float4*>(a.master + s);
+        const float4 w1 = *reinterpret_cast<const float4*>(a.master + s + 4);
+        w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+      }
+      float mm[VN], vv[VN];
       if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
-        *reinterpret_cast<float4*>(a.m + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-        *reinterpret_cast<float4*>(a.m + s + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        const float4 m0 = *reinterpret_cast<const float4*>(a.m + s), m1 = *reinterpret_cast<const float4*>(a.m + s + 4);
+        mm[0] = m0.x; mm[1] = m0.y; mm[2] = m0.z; mm[3] = m0.w; mm[4] = m1.x; mm[5] = m1.y; mm[6] = m1.z; mm[7] = m1.w;
       }
       if (a.opt.kind == OPT_ADAM) {
-        *reinterpret_cast<float4*>(a.v + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-        *reinterpret_cast<float4*>(a.v + s + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+        const float4 v0 = *reinterpret_cast<const float4*>(a.v + s), v1 = *reinterpret_cast<const float4*>(a.v + s + 4);
+        vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
       }
-    }
-    if (a.reduced_out != nullptr) {
-      VG o[GV];
 #pragma unroll
-      for (int h = 0; h < GV; ++h) {
-#pragma unroll
-        for (int j = 0; j < VG::kN; ++j) o[h].set(j, acc[h * VG::kN + j]);
-        reinterpret_cast<uint4*>(reinterpret_cast<TG*>(a.reduced_out) + s)[h] = o[h].raw;
+      for (int j = 0; j < VN; ++j) {
+        acc[j] *= inv_r;
+        w[j] = opt_step(w[j], acc[j], &mm[j], &vv[j], a.opt);
       }
-    }
-    if (a.opt.kind != OPT_NONE) {
-      using VP = Vec16<TP>;
-      constexpr int PV = VN / VP::kN;
-      VP o[PV];
+      if (a.opt.kind != OPT_NONE) {
+        *reinterpret_cast<float4*>(a.master + s) = make_float4(w[0], w[1], w[2], w[3]);
+        *reinterpret_cast<float4*>(a.master + s + 4) = make_float4(w[4], w[5], w[6], w[7]);
+        if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
+          *reinterpret_cast<float4*>(a.m + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+          *reinterpret_cast<float4*>(a.m + s + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        }
+        if (a.opt.kind == OPT_ADAM) {
+          *reinterpret_cast<float4*>(a.v + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+          *reinterpret_cast<float4*>(a.v + s + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+        }
+      }
+      if (a.reduced_out != nullptr) {
+        VG o[GV];
 #pragma unroll
-      for (int h = 0; h < PV; ++h)
+        for (int h = 0; h < GV; ++h) {
 #pragma unroll
-        for (int j = 0; j < VP::kN; ++j) o[h].set(j, w[h * VP::kN + j]);
-      const bool pushed = a.push && !(e >= a.nopush_lo && e < a.nopush_hi);
+          for (int j = 0; j < VG::kN; ++j) o[h].set(j, acc[h * VG::kN + j]);
+          reinterpret_cast<uint4*>(reinterpret_cast<TG*>(a.reduced_out) + s)[h] = o[h].raw;
+        }
+      }
+      if (a.opt.kind != OPT_NONE) {
+        using VP = Vec16<TP>;
+        constexpr int PV = VN / VP::kN;
+        VP o[PV];
 #pragma unroll
-      for (int q = 0; q < kMaxRanks; ++q) {
-        if (q < R && (pushed || q == a.rank)) {
-          TP* dst = reinterpret_cast<TP*>(a.params.p[q]) + e;
+        for (int h = 0; h < PV; ++h)
 #pragma unroll
-          for (int h = 0; h < PV; ++h) st_peer_v4(dst + h * VP::kN, o[h].raw);
+          for (int j = 0; j < VP::kN; ++j) o[h].set(j, w[h * VP::kN + j]);
+        const bool pushed = a.push && !(e >= a.nopush_lo && e < a.nopush_hi);
+#pragma unroll
+        for (int q = 0; q < kMaxRanks; ++q) {
+          if (q < R && (pushed || q == a.rank)) {
+            TP* dst = reinterpret_cast<TP*>(a.params.p[q]) + e;
+#pragma unroll
+            for (int h = 0; h < PV; ++h) st_peer_v4(dst + h * VP::kN, o[h].raw);
+          }
         }
       }
     }
@@ -598,16 +614,16 @@ DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* co
   DFB_REQUIRE(opt_kind != OPT_ADAM || v != nullptr, "sync: Adam second moment missing");
   const long lo = (long)rank * shard, hi = lo + shard < n ? lo + shard : n;
   long nvec = hi > lo ? (hi - lo + 7) / 8 : 0;
-  int grid = ctas > 0 ? ctas : 32;
-  long need = (nvec + 511) / 512;
+  int grid = ctas > 0 ? ctas : 64;
+  long need = (nvec + 255) / 256;
   if (need < 1) need = 1;
   if (grid > need) grid = (int)need;
 #define DFB_SYNC_LAUNCH(TG, TP)                                                     \
   do {                                                                               \
-    if (R == 8) sync_rs_opt_ag_kernel<TG, TP, 8><<<grid, 512, 0, stream>>>(a);       \
-    else if (R == 4) sync_rs_opt_ag_kernel<TG, TP, 4><<<grid, 512, 0, stream>>>(a);  \
-    else if (R == 2) sync_rs_opt_ag_kernel<TG, TP, 2><<<grid, 512, 0, stream>>>(a);  \
-    else sync_rs_opt_ag_kernel<TG, TP, 0><<<grid, 512, 0, stream>>>(a);              \
+    if (R == 8) sync_rs_opt_ag_kernel<TG, TP, 8><<<grid, 256, 0, stream>>>(a);       \
+    else if (R == 4) sync_rs_opt_ag_kernel<TG, TP, 4><<<grid, 256, 0, stream>>>(a);  \
+    else if (R == 2) sync_rs_opt_ag_kernel<TG, TP, 2><<<grid, 256, 0, stream>>>(a);  \
+    else sync_rs_opt_ag_kernel<TG, TP, 0><<<grid, 256, 0, stream>>>(a);              \
   } while (0)
   if (grad_dtype == DT_BF16 && param_dtype == DT_BF16) DFB_SYNC_LAUNCH(__nv_bfloat16, __nv_bfloat16);
   else if (grad_dtype == DT_F32 && param_dtype == DT_F32) DFB_SYNC_LAUNCH(float, float);

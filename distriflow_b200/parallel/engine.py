@@ -238,7 +238,7 @@ class DataParallelEngine:
                                        ptr(b.master), ptr(b.m), ptr(b.v), None, b.numel, b.shard, self.rank, self.world,
                                        epoch, 1, dt(b.grad_buf), dt(b.param_buf), _OPT[c["optimizer"]], self.lr,
                                        c["momentum"], c["beta1"], c["beta2"], c["eps"], c["weightDecay"], self.version + 1,
-                                       self.comm_ctas if self.world > 1 else 148 * 2, b.nopush[0], b.nopush[1], _lib.stream()),
+                                       self.comm_ctas if self.world > 1 else 148 * 4, b.nopush[0], b.nopush[1], _lib.stream()),
                   "dfb_sync_rs_opt_ag")
         self._launches += 1
 
