@@ -45,7 +45,7 @@ class _MergeHeads(torch.autograd.Function):
         B, H, T, D = a.shape
         a = a.contiguous()
         out = torch.empty((B, T, H * D), dtype=a.dtype, device=a.device)
-        permute_rows(a, out, (B, T, H), (H * T * D, D, T * D), (T * H * D, H * D, D), D)
+        permute_rows(a, out, (B, H, T), (H * T * D, T * D, D), (T * H * D, D, H * D), D)
         ctx.dims = (B, H, T, D)
         return out
 

@@ -81,47 +81,53 @@ __global__ void __launch_bounds__(128) add_ln_fwd_kernel(const T* __restrict__ x
 
 // Each block walks rows blockIdx.x*4 + warp, + gridDim.x*4, ... ; per-lane dgamma/dbeta partials live in registers and
 // are combined across the 4 warps through shared memory, then written to part[blockIdx.x][2][D].
+// All three row operands (dy, s, ds) are fetched up front as packed 16-byte vectors (9 loads in flight per lane at
+// D = 768) and unpacked twice, which keeps the register count low enough for 4 blocks per SM.
 template <typename T, int NV>
-__global__ void __launch_bounds__(128) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
-                                                         const T* __restrict__ gamma, const float* __restrict__ mean,
-                                                         const float* __restrict__ rstd, T* __restrict__ dx,
-                                                         float* __restrict__ part, int rows, int D) {
+__global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
+                                                            const T* __restrict__ gamma, const float* __restrict__ mean,
+                                                            const float* __restrict__ rstd, T* __restrict__ dx,
+                                                            float* __restrict__ part, int rows, int D) {
   using V = Vec16<T>;
   constexpr int VN = V::kN;
   extern __shared__ float sh[];              // [4 warps][2][D]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float dg[NV][VN], db[NV][VN], gam[NV][VN];
+  float dg[NV][VN], db[NV][VN];
+  V gam[NV];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = (i * 32 + lane) * VN;
-    V g;
-    if (c < D) g.raw = *reinterpret_cast<const uint4*>(gamma + c);
+    if (c < D) gam[i].raw = *reinterpret_cast<const uint4*>(gamma + c);
+    else gam[i].raw = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int j = 0; j < VN; ++j) {
       dg[i][j] = 0.f;
       db[i][j] = 0.f;
-      gam[i][j] = c < D ? g.get(j) : 0.f;
     }
   }
   for (int row = blockIdx.x * 4 + warp; row < rows; row += gridDim.x * 4) {
+    V a[NV], b[NV], r[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+        a[i].raw = *reinterpret_cast<const uint4*>(s + (long)row * D + c);
+        b[i].raw = *reinterpret_cast<const uint4*>(dy + (long)row * D + c);
+        if (ds != nullptr) r[i].raw = *reinterpret_cast<const uint4*>(ds + (long)row * D + c);
+      }
+    }
     const float mu = mean[row], rs = rstd[row];
-    float xh[NV][VN], gg[NV][VN];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * VN;
       if (c < D) {
-        V a, b;
-        a.raw = *reinterpret_cast<const uint4*>(s + (long)row * D + c);
-        b.raw = *reinterpret_cast<const uint4*>(dy + (long)row * D + c);
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          const float xhat = (a.get(j) - mu) * rs, d = b.get(j);
-          xh[i][j] = xhat;
+          const float xhat = (a[i].get(j) - mu) * rs, d = b[i].get(j);
           dg[i][j] += d * xhat;
           db[i][j] += d;
-          const float g = d * gam[i][j];
-          gg[i][j] = g;
+          const float g = d * gam[i].get(j);
           s1 += g;
           s2 += g * xhat;
         }
@@ -133,12 +139,12 @@ __global__ void __launch_bounds__(128) add_ln_bwd_kernel(const T* __restrict__ d
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * VN;
       if (c < D) {
-        V o, r;
-        if (ds != nullptr) r.raw = *reinterpret_cast<const uint4*>(ds + (long)row * D + c);
+        V o;
 #pragma unroll
         for (int j = 0; j < VN; ++j) {
-          float val = rs * (gg[i][j] - s1 - xh[i][j] * s2);
-          if (ds != nullptr) val += r.get(j);
+          const float xhat = (a[i].get(j) - mu) * rs;
+          float val = rs * (b[i].get(j) * gam[i].get(j) - s1 - xhat * s2);
+          if (ds != nullptr) val += r[i].get(j);
           o.set(j, val);
         }
         *reinterpret_cast<uint4*>(dx + (long)row * D + c) = o.raw;
@@ -166,34 +172,46 @@ __global__ void __launch_bounds__(128) add_ln_bwd_kernel(const T* __restrict__ d
   }
 }
 
-// out[which][col] = sum_b part[b][which][col]  (fixed order: deterministic)
+// out[which][col] = sum_b part[b][which][col]: 32 columns x 32 partial-groups per block, fixed order (deterministic).
 template <typename T>
-__global__ void ln_param_grad_reduce_kernel(const float* __restrict__ part, T* __restrict__ dgamma, T* __restrict__ dbeta,
-                                            int nblocks, int D) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 2 * D) return;
-  const int which = c / D, col = c - which * D;
+__global__ void __launch_bounds__(1024) ln_param_grad_reduce_kernel(const float* __restrict__ part, T* __restrict__ dgamma,
+                                                                    T* __restrict__ dbeta, int nblocks, int D) {
+  __shared__ float sh[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float t = 0.f;
-  for (int b = 0; b < nblocks; ++b) t += part[((long)b * 2 + which) * D + col];
-  (which ? dbeta : dgamma)[col] = from_f32<T>(t);
+  if (c < 2 * D)
+    for (int b = ty; b < nblocks; b += 32) t += part[(long)b * 2 * D + c];
+  sh[ty][tx] = t;
+  __syncthreads();
+  if (ty == 0 && c < 2 * D) {
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) tot += sh[k][tx];
+    const int which = c / D, col = c - which * D;
+    (which ? dbeta : dgamma)[col] = from_f32<T>(tot);
+  }
 }
 
-// Rows of `row_bytes` (multiple of 16) indexed by (i0,i1,i2,i3): src + i.s bytes -> dst + i.d bytes.  One 16-byte vector per thread per iteration; both sides see whole
+// Rows of `row_bytes` (multiple of 16) indexed by (i0,i1,i2,i3): src + i.s bytes -> dst + i.d bytes.  The grid covers
+// (i1, i0); the threads of a block sweep (i2, i3, 16-byte vector) with a single division per vector.  Both sides see whole
 // 128-byte rows for the attention head layouts ([B,T,3,H,D] <-> [3,B,H,T,D], [B,H,T,D] <-> [B,T,H,D]).
 __global__ void __launch_bounds__(256) permute_rows_kernel(const char* __restrict__ src, char* __restrict__ dst, int n0, int n1, int n2,
                                                            int n3, long s0, long s1, long s2, long s3, long d0, long d1, long d2,
                                                            long d3, int row_bytes) {
   const int vec_per_row = row_bytes >> 4;
-  const long total = (long)n0 * n1 * n2 * n3 * vec_per_row;
-  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
-    const int v = (int)(i % vec_per_row);
-    long t = i / vec_per_row;
-    const int i3 = (int)(t % n3); t /= n3;
-    const int i2 = (int)(t % n2); t /= n2;
-    const int i1 = (int)(t % n1);
-    const int i0 = (int)(t / n1);
-    const uint4 val = *reinterpret_cast<const uint4*>(src + i0 * s0 + i1 * s1 + i2 * s2 + i3 * s3 + (long)v * 16);
-    *reinterpret_cast<uint4*>(dst + i0 * d0 + i1 * d1 + i2 * d2 + i3 * d3 + (long)v * 16) = val;
+  const int inner = n3 * vec_per_row;
+  const int total = n2 * inner;
+  for (int i1 = blockIdx.x; i1 < n1; i1 += gridDim.x) {
+    const int i0 = blockIdx.y;
+    const char* sp = src + i0 * s0 + i1 * s1;
+    char* dp = dst + i0 * d0 + i1 * d1;
+    for (int i = threadIdx.x; i < total; i += 256) {
+      const int i2 = i / inner, rem = i - i2 * inner;
+      const int i3 = rem / vec_per_row, v = rem - i3 * vec_per_row;
+      const uint4 val = *reinterpret_cast<const uint4*>(sp + i2 * s2 + i3 * s3 + (long)v * 16);
+      *reinterpret_cast<uint4*>(dp + i2 * d2 + i3 * d3 + (long)v * 16) = val;
+    }
   }
 }
 
@@ -266,10 +284,10 @@ DFB_API int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s,
 #undef DFB_LN_BWD
   if (rc) return rc;
   if (dtype == DT_BF16)
-    ln_param_grad_reduce_kernel<__nv_bfloat16><<<ceil_div(2 * D, 128), 128, 0, stream>>>(part, (__nv_bfloat16*)dgamma,
+    ln_param_grad_reduce_kernel<__nv_bfloat16><<<ceil_div(2 * D, 32), 1024, 0, stream>>>(part, (__nv_bfloat16*)dgamma,
                                                                                          (__nv_bfloat16*)dbeta, nblocks, D);
   else
-    ln_param_grad_reduce_kernel<float><<<ceil_div(2 * D, 128), 128, 0, stream>>>(part, (float*)dgamma, (float*)dbeta, nblocks, D);
+    ln_param_grad_reduce_kernel<float><<<ceil_div(2 * D, 32), 1024, 0, stream>>>(part, (float*)dgamma, (float*)dbeta, nblocks, D);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -279,10 +297,9 @@ DFB_API int dfb_permute_rows(const void* src, void* dst, int n0, int n1, int n2,
   DFB_REQUIRE(row_bytes > 0 && (row_bytes % 16) == 0, "permute_rows: row_bytes must be a multiple of 16");
   DFB_REQUIRE(((s0 | s1 | s2 | s3 | d0 | d1 | d2 | d3) % 16) == 0, "permute_rows: strides must be multiples of 16 bytes");
   const long total = (long)n0 * n1 * n2 * n3 * (row_bytes / 16);
-  DFB_REQUIRE(total > 0, "permute_rows: empty");
-  long blocks = (total + 255) / 256;
-  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
-  permute_rows_kernel<<<(int)blocks, 256, 0, stream>>>((const char*)src, (char*)dst, n0, n1, n2, n3, s0, s1, s2, s3, d0, d1, d2,
+  DFB_REQUIRE(total > 0 && n0 <= 65535, "permute_rows: empty or n0 too large");
+  dim3 blocks(n1 < 65535 ? n1 : 65535, n0);
+  permute_rows_kernel<<<blocks, 256, 0, stream>>>((const char*)src, (char*)dst, n0, n1, n2, n3, s0, s1, s2, s3, d0, d1, d2,
                                                        d3, row_bytes);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
