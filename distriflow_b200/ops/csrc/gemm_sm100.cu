@@ -363,6 +363,306 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 }
 
+// ======================================================================================================
+// 2-CTA variant: a cluster of two CTAs (one SM pair) computes a 256 x 256 tile with tcgen05.mma.cta_group::2.
+// Each CTA stages its own 128 rows of A and its own 128-column half of B (32 KiB per k-block instead of 48 KiB),
+// the leader CTA's elected thread issues the MMAs for both, and each CTA's TMEM receives its 128 accumulator rows.
+// Per-SM shared-memory fill drops from 96 to 64 bytes per MMA cycle, which is what limited the 1-CTA kernel
+// (profiles/ncu_kernels_r1.csv: tensor pipe 68-71 % active on the K = 768 products).
+//   full[stage]   lives in the leader; both CTAs' TMA loads complete on it (peer-bit-masked barrier address)
+//   empty[stage]  one per CTA; the leader's tcgen05.commit multicasts the arrival to both
+//   tmem_full     one per CTA, multicast commit;  tmem_empty lives in the leader, 8 arrivals (4 epilogue warps x 2 CTAs)
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+constexpr int k2Stages = 6;
+constexpr int k2StageBytes = kATileBytes + 128 * kBlockK * 2;         // 16 KiB A + 16 KiB B half
+constexpr int k2SmemBytes = k2Stages * k2StageBytes + 2 * kStageOutBytes + 256 + 1024;
+constexpr int k2TmemCols = 512;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap, uint64_t* bar, int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {       // arrives on `bar` in BOTH CTAs of the pair
+  const uint16_t mask = 3;
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t target_cta) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(smem_u32(bar)), "r"(target_cta));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(remote) : "memory");
+}
+
+template <typename OutT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+  constexpr int BLOCK_N = 256;
+  constexpr int kChunkN = 128 / (int)sizeof(OutT);
+  constexpr int kChunks = BLOCK_N / kChunkN;
+  constexpr int kBHalf = 128 * kBlockK * 2;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + k2Stages * kATileBytes;
+  uint8_t* smem_out = smem + k2Stages * k2StageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + 2 * kStageOutBytes);
+  uint64_t* empty_bar = full_bar + k2Stages;
+  uint64_t* tmem_full = empty_bar + k2Stages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = (cta == 0);
+
+  const int m_blocks = ceil_div(p.M, 256);
+  const int n_blocks = ceil_div(p.N, BLOCK_N);
+  const int kb_total = ceil_div(p.K, kBlockK);
+  const int tiles_mn = m_blocks * n_blocks;
+  const int num_tiles = tiles_mn * p.splits;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp_idx == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmD);
+    for (int i = 0; i < k2Stages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);
+    }
+    fence_mbar_init();
+  }
+  if (warp_idx == 1) {
+    uint32_t ncols = k2TmemCols;
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(tmem_ptr)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  auto decode_tile = [&](int tile, int& m_blk, int& n_blk, int& split) {
+    split = tile / tiles_mn;
+    int t = tile - split * tiles_mn;
+    const int group = 4 * n_blocks;               // groups of 4 x 256 rows sweep n: concurrently running pairs share tiles in L2
+    int g = t / group;
+    int first_m = g * 4;
+    int gsz = min(4, m_blocks - first_m);
+    int r = t - g * group;
+    m_blk = first_m + r % gsz;
+    n_blk = r / gsz;
+  };
+
+  if (warp_idx == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int m_blk, n_blk, split;
+        decode_tile(tile, m_blk, n_blk, split);
+        const int m0 = m_blk * 256 + (int)cta * 128, n0 = n_blk * BLOCK_N + (int)cta * 128;
+        const int kb0 = split * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * k2StageBytes);      // bytes of both CTAs land on the leader's barrier
+          uint8_t* sa = smem_a + stage * kATileBytes;
+          uint8_t* sb = smem_b + stage * kBHalf;
+          const int k0 = kb * kBlockK;
+          if (p.a_mn) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) tma_load_2d_2sm(sa + i * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * i, k0);
+          } else {
+            tma_load_2d_2sm(sa, &tmA, &full_bar[stage], k0, m0);
+          }
+          if (p.b_mn) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) tma_load_2d_2sm(sb + i * kAtomBytes, &tmB, &full_bar[stage], n0 + 64 * i, k0);
+          } else {
+            tma_load_2d_2sm(sb, &tmB, &full_bar[stage], k0, n0);
+          }
+          if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp_idx == 1) {
+    if (leader && elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(256, BLOCK_N, (uint32_t)p.a_mn, (uint32_t)p.b_mn);
+      const uint32_t a_lbo = p.a_mn ? kAtomBytes : 0, b_lbo = p.b_mn ? kAtomBytes : 0;
+      const uint32_t a_kstep = p.a_mn ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+      const uint32_t b_kstep = p.b_mn ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int m_blk, n_blk, split;
+        decode_tile(tile, m_blk, n_blk, split);
+        const int kb0 = split * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, kb_total);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        for (int it = 0; it < kb1 - kb0; ++it) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t a_desc = make_smem_desc_sw128(smem_u32(smem_a + stage * kATileBytes), a_lbo, 1024);
+          const uint64_t b_desc = make_smem_desc_sw128(smem_u32(smem_b + stage * kBHalf), b_lbo, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_f16_2sm(tmem_d, a_desc + (uint64_t)(k * a_kstep), b_desc + (uint64_t)(k * b_kstep), idesc, (it > 0 || k > 0) ? 1u : 0u);
+          umma_commit_2sm(&empty_bar[stage]);
+          if (++stage == k2Stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&tmem_full[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    const int quarter = warp_idx & 3, row = quarter * 32 + lane;
+    const bool issuer = (threadIdx.x == 64);
+    int acc = 0;
+    uint32_t acc_phase = 0, out_iter = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      int m_blk, n_blk, split;
+      decode_tile(tile, m_blk, n_blk, split);
+      const int m0 = m_blk * 256 + (int)cta * 128, n0 = n_blk * BLOCK_N;
+      const int out_row0 = m0 + split * p.split_rows;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < kChunks; ++c) {
+        float v[kChunkN];
+        {
+          uint32_t r0[32];
+          tmem_ld_32x32(taddr + c * kChunkN, r0);
+          if constexpr (kChunkN == 64) {
+            uint32_t r1[32];
+            tmem_ld_32x32(taddr + c * kChunkN + 32, r1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[32 + j] = __uint_as_float(r1[j]);
+          } else {
+            tmem_ld_wait();
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r0[j]);
+        }
+        if (c == kChunks - 1) {                        // accumulator drained: tell the leader's MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+        }
+        uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
+        if (issuer) tma_store_wait_read<1>();
+        named_bar_sync(1, kEpiThreads);
+        if (p.bias != nullptr) {
+          const int nb = n0 + c * kChunkN;
+          if (p.bias_dtype == DT_F32) {
+            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+#pragma unroll
+            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __ldg(bp + j) : 0.f;
+          } else {
+            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+#pragma unroll
+            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __bfloat162float(bp[j]) : 0.f;
+          }
+        }
+        if (p.act == ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < kChunkN; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (p.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < kChunkN; ++j) v[j] = gelu_tanh(v[j]);
+        }
+        uint8_t* row_ptr = stage_out + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          uint4 q;
+          if constexpr (sizeof(OutT) == 2) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j + 0], v[8 * j + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+            q.x = *reinterpret_cast<uint32_t*>(&h0);
+            q.y = *reinterpret_cast<uint32_t*>(&h1);
+            q.z = *reinterpret_cast<uint32_t*>(&h2);
+            q.w = *reinterpret_cast<uint32_t*>(&h3);
+          } else {
+            q.x = __float_as_uint(v[4 * j + 0]);
+            q.y = __float_as_uint(v[4 * j + 1]);
+            q.z = __float_as_uint(v[4 * j + 2]);
+            q.w = __float_as_uint(v[4 * j + 3]);
+          }
+          *reinterpret_cast<uint4*>(row_ptr + ((j ^ (row & 7)) << 4)) = q;
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, kEpiThreads);
+        if (issuer) {
+          tma_store_2d(&tmD, stage_out, n0 + c * kChunkN, out_row0);
+          tma_store_commit();
+        }
+        ++out_iter;
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (issuer) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();                 // nobody leaves (or frees TMEM) while the partner may still read its smem / signal its barriers
+  if (warp_idx == 1) {
+    tc_fence_after();
+    uint32_t ncols = k2TmemCols;
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(ncols) : "memory");
+  }
+}
+
+template <typename OutT>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const GemmParams& p, int max_ctas,
+                        cudaStream_t stream) {
+  auto kern = gemm2_tcgen05_kernel<OutT>;
+  static bool configured = false;
+  if (!configured) {
+    DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, k2SmemBytes));
+    configured = true;
+  }
+  const int tiles = ceil_div(p.M, 256) * ceil_div(p.N, 256) * p.splits;
+  int pairs = num_sms() / 2;
+  if (max_ctas > 0 && pairs > max_ctas / 2) pairs = max_ctas / 2;
+  if (pairs > tiles) pairs = tiles;
+  if (pairs < 1) pairs = 1;
+  kern<<<2 * pairs, kThreads, k2SmemBytes, stream>>>(tmA, tmB, tmD, p);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 // out[m, n] = act(sum_s ws[s*split_rows + m, n] + bias[n]); ws fp32 with row pitch ldw.
 template <typename OutT>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, OutT* __restrict__ out, const void* __restrict__ bias,
@@ -433,7 +733,7 @@ using namespace dfb;
 // Bytes of fp32 scratch dfb_gemm_bf16 needs for a given problem and split factor (0 when splits <= 1).
 DFB_API size_t dfb_gemm_workspace_bytes(int M, int N, int splits) {
   if (splits <= 1) return 0;
-  size_t mpad = (size_t)ceil_div(M, kBlockM) * kBlockM;
+  size_t mpad = (size_t)ceil_div(M, 256) * 256;          // 256: the 2-CTA kernel works on 256-row tiles
   return (size_t)splits * mpad * (size_t)N * sizeof(float);
 }
 
@@ -453,7 +753,9 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
                           int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n,
                           int splits, void* workspace, size_t workspace_bytes, int max_ctas, cudaStream_t stream) {
   DFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d x %d x %d", M, N, K);
-  DFB_REQUIRE(block_n == 128 || block_n == 256, "gemm: block_n must be 128 or 256");
+  DFB_REQUIRE(block_n == 128 || block_n == 256 || block_n == 512, "gemm: block_n must be 128, 256 or 512 (= 2-CTA 256x256)");
+  const bool two_cta = (block_n == 512);
+  if (two_cta) block_n = 256;
   DFB_REQUIRE(out_dtype == DT_BF16 || out_dtype == DT_F32, "gemm: out dtype");
   DFB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16-byte pitch)");
   DFB_REQUIRE((ldd * (out_dtype == DT_BF16 ? 2 : 4)) % 16 == 0, "gemm: output pitch must be a multiple of 16 bytes");
@@ -471,14 +773,14 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
 
   CUtensorMap tmA, tmB, tmD;
   if (make_operand_map(&tmA, A, M, K, lda, p.a_mn, kBlockM)) return 4;
-  if (make_operand_map(&tmB, B, N, K, ldb, p.b_mn, block_n)) return 4;
+  if (make_operand_map(&tmB, B, N, K, ldb, p.b_mn, two_cta ? 128 : block_n)) return 4;
 
   if (splits > 1) {
     DFB_REQUIRE((N % 4) == 0, "gemm split-K: N must be a multiple of 4");
     const size_t need = dfb_gemm_workspace_bytes(M, N, splits);
     DFB_REQUIRE(workspace != nullptr && workspace_bytes >= need, "gemm split-K: workspace of %zu bytes required, got %zu",
                 need, workspace_bytes);
-    const int mpad = ceil_div(M, kBlockM) * kBlockM;
+    const int mpad = ceil_div(M, 256) * 256;
     p.split_rows = mpad;
     GemmParams pk = p;
     pk.bias = nullptr; pk.act = ACT_NONE;
@@ -486,8 +788,9 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
     uint64_t str[1] = {(uint64_t)N * 4};
     uint32_t box[2] = {32, 128};
     if (encode_tmap(&tmD, workspace, 1, 2, dims, str, box, nullptr, 1)) return 4;
-    int rc = block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, pk, max_ctas, stream)
-                            : launch_gemm<128, float>(tmA, tmB, tmD, pk, max_ctas, stream);
+    int rc = two_cta ? launch_gemm2<float>(tmA, tmB, tmD, pk, max_ctas, stream)
+             : block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, pk, max_ctas, stream)
+                              : launch_gemm<128, float>(tmA, tmB, tmD, pk, max_ctas, stream);
     if (rc) return rc;
     const long total = (long)M * (N / 4);
     int blocks = (int)((total + 255) / 256);
@@ -509,6 +812,9 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
     uint32_t box[2] = {(uint32_t)(128 / esz), 128};
     if (encode_tmap(&tmD, D, out_dtype == DT_BF16 ? 0 : 1, 2, dims, str, box, nullptr, 1)) return 4;
   }
+  if (two_cta)
+    return out_dtype == DT_BF16 ? launch_gemm2<__nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream)
+                                : launch_gemm2<float>(tmA, tmB, tmD, p, max_ctas, stream);
   if (out_dtype == DT_BF16)
     return block_n == 256 ? launch_gemm<256, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream)
                           : launch_gemm<128, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream);

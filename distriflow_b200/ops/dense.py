@@ -33,7 +33,21 @@ def _tc_ok(*mats: torch.Tensor) -> bool:
     return True
 
 
+TWO_CTA = True           # use the cta_group::2 kernel (256x256 tiles on SM pairs) where it fills the machine
+
+
 def pick_tile(M: int, N: int, K: int) -> Tuple[int, int]:
+    """(block_n, splits).  block_n = 512 selects the 2-CTA kernel (256 x 256 tile per SM pair)."""
+    pairs = NUM_SMS // 2
+    kb = -(-K // 64)
+    if TWO_CTA and M >= 256 and N >= 256 and _MAX_CTAS == 0:
+        t2 = -(-M // 256) * -(-N // 256)
+        if t2 >= pairs:
+            return 512, 1
+        if kb >= 32 and N % 4 == 0:          # short MN, long K (weight gradients): split K over the pairs
+            sp = max(1, min(pairs // t2, kb // 8, 16))
+            if t2 * sp * 10 >= pairs * 6:
+                return 512, sp
     mb = -(-M // 128)
     t256 = mb * -(-N // 256)
     bn = 256 if (t256 >= NUM_SMS and N >= 256) else 128
@@ -84,7 +98,7 @@ def ag_gemm(x2: torch.Tensor, w: torch.Tensor, plan, bias: Optional[torch.Tensor
     M, K = x2.shape
     N = w.shape[1]
     out = torch.empty((M, N), device=x2.device, dtype=x2.dtype)
-    bn, _ = pick_tile(M, N, K)
+    bn = 256 if (-(-M // 128) * -(-N // 256) >= NUM_SMS and N >= 256) else 128
     if bias is not None and bias.dtype not in (torch.float32, torch.bfloat16):
         bias = bias.float()
     check(L.dfb_ag_gemm_bf16(ptr(x2), ptr(w), ptr(out), ptr(bias), c_int(dt(bias) if bias is not None else 0), M, N, K,

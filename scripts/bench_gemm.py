@@ -23,6 +23,10 @@ def timeit(fn, n=10, warm=3):
     return e0.elapsed_time(e1) / n
 
 
+FORCE_BN = int(os.environ.get("DFB_BENCH_BN", "0")) or None
+FORCE_SPLITS = int(os.environ.get("DFB_BENCH_SPLITS", "0")) or None
+
+
 def main():
     _init_sigs()
     dev = torch.device("cuda")
@@ -43,15 +47,15 @@ def main():
         flops = 2.0 * tokens * K * N
         for kind in ("fwd", "dgrad", "wgrad"):
             if kind == "fwd":
-                ours = lambda: gemm(nxt(xs), w, a_mn=False, b_mn=True, M=tokens, N=N, K=K)
+                ours = lambda: gemm(nxt(xs), w, a_mn=False, b_mn=True, M=tokens, N=N, K=K, block_n=FORCE_BN)
                 ref = lambda: torch.matmul(nxt(xs), w)
                 tile = pick_tile(tokens, N, K)
             elif kind == "dgrad":
-                ours = lambda: gemm(nxt(dys), w, a_mn=False, b_mn=False, M=tokens, N=K, K=N)
+                ours = lambda: gemm(nxt(dys), w, a_mn=False, b_mn=False, M=tokens, N=K, K=N, block_n=FORCE_BN)
                 ref = lambda: torch.matmul(nxt(dys), w.t())
                 tile = pick_tile(tokens, K, N)
             else:
-                ours = lambda: gemm(nxt(xs), nxt(dys), a_mn=True, b_mn=True, M=K, N=N, K=tokens)
+                ours = lambda: gemm(nxt(xs), nxt(dys), a_mn=True, b_mn=True, M=K, N=N, K=tokens, block_n=FORCE_BN, splits=FORCE_SPLITS)
                 ref = lambda: torch.matmul(nxt(xs).t(), nxt(dys))
                 tile = pick_tile(K, N, tokens)
             t_o, t_r = timeit(ours), timeit(ref)

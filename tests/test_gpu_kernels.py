@@ -40,10 +40,23 @@ def _gemm_case(M, N, K, a_mn, b_mn, out_dtype=torch.bfloat16, bias=False, act=No
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
-@pytest.mark.parametrize("block_n", [128, 256])
+@pytest.mark.parametrize("block_n", [128, 256, 512])
 def test_gemm_tcgen05_layouts(a_mn, b_mn, block_n):
-    e = _gemm_case(256, 512, 256, a_mn, b_mn, block_n=block_n, splits=1)
+    e = _gemm_case(256, 512, 256, a_mn, b_mn, block_n=block_n, splits=1)       # 512 = 2-CTA (cta_group::2) 256x256 tiles
     assert e < 1e-2, f"rel err {e}"
+
+
+@pytest.mark.parametrize("shape", [(300, 264, 200), (1000, 776, 1032), (8192, 2304, 768), (768, 3072, 4096)])
+def test_gemm_two_cta_tails_epilogues_splitk(shape):
+    M, N, K = shape
+    for a_mn, b_mn in [(False, True), (False, False), (True, True)]:
+        if a_mn and M % 8:
+            continue
+        assert _gemm_case(M, N, K, a_mn, b_mn, block_n=512, splits=1) < 1e-2, (shape, a_mn, b_mn)
+    assert _gemm_case(M, N, K, False, True, block_n=512, splits=1, bias=True, act="gelu") < 1e-2
+    assert _gemm_case(M, N, K, False, False, block_n=512, splits=1, bias=True, out_dtype=torch.float32) < 5e-3
+    if K >= 1024:
+        assert _gemm_case(M, N, K, True, True, block_n=512, splits=4) < 1e-2
 
 
 @pytest.mark.parametrize("shape", [(300, 264, 200), (128, 16, 64), (1000, 776, 1032), (4096, 768, 768), (2048, 3072, 768)])
