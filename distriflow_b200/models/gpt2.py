@@ -58,7 +58,7 @@ class Block(nn.Module):
         Returns the attention branch output and leaves the adds to the fused add+LayerNorm kernels."""
         a = ops.causal_self_attention(self.c_attn(h), self.n_head)
         x, h2 = ops.add_layer_norm(x, self.c_proj(a), self.ln_2.gamma, self.ln_2.beta, self.ln_2.epsilon)
-        return x, self.c_proj2(self.c_fc(h2))
+        return x, ops.mlp(h2, self.c_fc.kernel, self.c_fc.bias, self.c_proj2.kernel, self.c_proj2.bias)
 
 
 class GPT2(nn.Module):

@@ -16,7 +16,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 import torch.nn.functional as F
 
-__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "add_layer_norm", "causal_self_attention",
+__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "add_layer_norm", "causal_self_attention", "mlp",
            "softmax_cross_entropy", "native_available", "same_padding"]
 
 
@@ -46,6 +46,15 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     if bias is not None:
         y = y + bias.to(y.dtype)
     return _act_cpu(y, activation)
+
+
+def mlp(x: torch.Tensor, w1: torch.Tensor, b1: Optional[torch.Tensor], w2: torch.Tensor, b2: Optional[torch.Tensor]) -> torch.Tensor:
+    """Transformer feed-forward block `gelu(x @ w1 + b1) @ w2 + b2` (tanh GELU) with the activation fused into the GEMM
+    epilogues on CUDA (forward: dual output; backward: gelu' applied in the dgrad epilogue)."""
+    if x.is_cuda:
+        from .dense import mlp_cuda
+        return mlp_cuda(x, w1, b1, w2, b2)
+    return linear(linear(x, w1, b1, "gelu"), w2, b2)
 
 
 def same_padding(size: int, k: int, s: int) -> Tuple[int, int]:

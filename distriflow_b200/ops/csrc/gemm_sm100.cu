@@ -54,7 +54,77 @@ struct GemmParams {
   unsigned* ready;            // [k-blocks] bytes landed so far (zeroed before the launch)
   int num_pieces;
   int rot_kb;                 // k-loop starts at this k-block (first locally owned one) and wraps around
+  // auxiliary bf16 matrix [M, N] (pitch aux_ld) touched by the epilogue of bf16-output kernels:
+  //   aux_mode 1: aux = accumulator + bias BEFORE the activation (the pre-activation a GELU backward needs)
+  //   aux_mode 2: output = accumulator * gelu'(aux)              (GELU backward fused into the next layer's dgrad)
+  void* aux;
+  long aux_ld;
+  int aux_mode;
 };
+
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * x * x);
+}
+
+// Epilogue hook on one 64-column chunk of one accumulator row (bf16-output kernels only).
+__device__ __forceinline__ void epilogue_aux(float (&v)[64], const GemmParams& a, int gm, int nb, int M, int N) {
+  if (a.aux_mode == 0 || gm >= M) return;
+  __nv_bfloat16* rowp = reinterpret_cast<__nv_bfloat16*>(a.aux) + (long)gm * a.aux_ld + nb;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (nb + 8 * j + 8 > N) break;
+    if (a.aux_mode == 1) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j + 0], v[8 * j + 1]);
+      __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
+      __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+      uint4 q = {*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1), *reinterpret_cast<uint32_t*>(&h2),
+                 *reinterpret_cast<uint32_t*>(&h3)};
+      *reinterpret_cast<uint4*>(rowp + 8 * j) = q;
+    } else {
+      const uint4 q = *reinterpret_cast<const uint4*>(rowp + 8 * j);
+      const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&q);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[8 * j + i] *= gelu_tanh_grad(__bfloat162float(h[i]));
+    }
+  }
+}
+
+// bias for one chunk of columns [nb, nb + CH): every lane reads the same addresses (L1 broadcast), 16 bytes at a time
+template <int CH>
+__device__ __forceinline__ void add_bias_chunk(float (&v)[CH], const void* bias, int bias_dtype, int nb, int N) {
+  if (bias_dtype == DT_F32) {
+    const float* bp = reinterpret_cast<const float*>(bias) + nb;
+    if (nb + CH <= N && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
+#pragma unroll
+      for (int j = 0; j < CH / 4; ++j) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + j);
+        v[4 * j] += b4.x; v[4 * j + 1] += b4.y; v[4 * j + 2] += b4.z; v[4 * j + 3] += b4.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CH; ++j) v[j] += (nb + j < N) ? __ldg(bp + j) : 0.f;
+    }
+  } else {
+    const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(bias) + nb;
+    if (nb + CH <= N && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
+#pragma unroll
+      for (int j = 0; j < CH / 8; ++j) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(bp) + j);
+        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&q);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[8 * j + i] += __bfloat162float(h[i]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CH; ++j) v[j] += (nb + j < N) ? __bfloat162float(bp[j]) : 0.f;
+    }
+  }
+}
 
 __device__ __forceinline__ float gelu_tanh(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
@@ -291,26 +361,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
         if (issuer) tma_store_wait_read<1>();          // the store that last used this buffer has drained
         named_bar_sync(1, kEpiThreads);
-        if (p.bias != nullptr) {      // same addresses for every lane: L1 broadcast loads
-          const int nb = n0 + c * kChunkN;
-          if (p.bias_dtype == DT_F32) {
-            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
-            if (nb + kChunkN <= p.N && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
-#pragma unroll
-              for (int j = 0; j < kChunkN / 4; ++j) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + j);
-                v[4 * j] += b4.x; v[4 * j + 1] += b4.y; v[4 * j + 2] += b4.z; v[4 * j + 3] += b4.w;
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __ldg(bp + j) : 0.f;
-            }
-          } else {
-            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
-#pragma unroll
-            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __bfloat162float(bp[j]) : 0.f;
-          }
-        }
+        if (p.bias != nullptr) add_bias_chunk<kChunkN>(v, p.bias, p.bias_dtype, n0 + c * kChunkN, p.N);
+        if constexpr (kChunkN == 64) epilogue_aux(v, p, m0 + row, n0 + c * kChunkN, p.M, p.N);
         if (p.act == ACT_RELU) {
 #pragma unroll
           for (int j = 0; j < kChunkN; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -582,18 +634,8 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
         if (issuer) tma_store_wait_read<1>();
         named_bar_sync(1, kEpiThreads);
-        if (p.bias != nullptr) {
-          const int nb = n0 + c * kChunkN;
-          if (p.bias_dtype == DT_F32) {
-            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
-#pragma unroll
-            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __ldg(bp + j) : 0.f;
-          } else {
-            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
-#pragma unroll
-            for (int j = 0; j < kChunkN; ++j) v[j] += (nb + j < p.N) ? __bfloat162float(bp[j]) : 0.f;
-          }
-        }
+        if (p.bias != nullptr) add_bias_chunk<kChunkN>(v, p.bias, p.bias_dtype, n0 + c * kChunkN, p.N);
+        if constexpr (kChunkN == 64) epilogue_aux(v, p, m0 + row, n0 + c * kChunkN, p.M, p.N);
         if (p.act == ACT_RELU) {
 #pragma unroll
           for (int j = 0; j < kChunkN; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -749,10 +791,13 @@ DFB_API int dfb_gemm_pick_splits(int M, int N, int K, int block_n, int sms) {
 }
 
 // See include/distriflow_b200.h.  `workspace` (fp32 scratch) is required iff splits > 1.
-DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K,
-                          int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n,
-                          int splits, void* workspace, size_t workspace_bytes, int max_ctas, cudaStream_t stream) {
+static int gemm_impl(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda, int ldb,
+                     int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits, void* workspace,
+                     size_t workspace_bytes, int max_ctas, void* aux, long aux_ld, int aux_mode, cudaStream_t stream) {
   DFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d x %d x %d", M, N, K);
+  DFB_REQUIRE(aux_mode == 0 || (aux != nullptr && out_dtype == DT_BF16 && (aux_ld % 8) == 0 && (N % 8) == 0 &&
+                                ((uintptr_t)aux % 16) == 0),
+              "gemm: the aux epilogue needs bf16 output, N and aux pitch multiples of 8, 16-byte aligned aux");
   DFB_REQUIRE(block_n == 128 || block_n == 256 || block_n == 512, "gemm: block_n must be 128, 256 or 512 (= 2-CTA 256x256)");
   const bool two_cta = (block_n == 512);
   if (two_cta) block_n = 256;
@@ -770,6 +815,8 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
   memset(&p, 0, sizeof(p));
   p.bias = bias; p.bias_dtype = bias_dtype; p.M = M; p.N = N; p.K = K; p.a_mn = a_mn_major ? 1 : 0; p.b_mn = b_mn_major ? 1 : 0;
   p.act = act; p.splits = splits; p.kb_per_split = kb_per; p.split_rows = 0;
+  p.aux = aux; p.aux_ld = aux_ld; p.aux_mode = aux_mode;
+  DFB_REQUIRE(aux_mode == 0 || splits == 1, "gemm: the aux epilogue cannot be combined with split-K");
 
   CUtensorMap tmA, tmB, tmD;
   if (make_operand_map(&tmA, A, M, K, lda, p.a_mn, kBlockM)) return 4;
@@ -820,6 +867,24 @@ DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bia
                           : launch_gemm<128, __nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream);
   return block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, p, max_ctas, stream)
                         : launch_gemm<128, float>(tmA, tmB, tmD, p, max_ctas, stream);
+}
+
+// See include/distriflow_b200.h.  `workspace` (fp32 scratch) is required iff splits > 1.
+DFB_API int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K,
+                          int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n,
+                          int splits, void* workspace, size_t workspace_bytes, int max_ctas, cudaStream_t stream) {
+  return gemm_impl(A, B, D, bias, bias_dtype, M, N, K, lda, ldb, ldd, a_mn_major, b_mn_major, out_dtype, act, block_n, splits,
+                   workspace, workspace_bytes, max_ctas, nullptr, 0, 0, stream);
+}
+
+// Same GEMM with an auxiliary bf16 matrix in the epilogue: aux_mode 1 stores the pre-activation (accumulator + bias) to
+// `aux` while D receives act(...); aux_mode 2 multiplies the accumulator by gelu'(aux) (GELU backward fused into the dgrad
+// of the following layer).  No split-K.
+DFB_API int dfb_gemm_bf16_aux(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K,
+                              int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int act, int block_n, void* aux,
+                              long aux_ld, int aux_mode, int max_ctas, cudaStream_t stream) {
+  return gemm_impl(A, B, D, bias, bias_dtype, M, N, K, lda, ldb, ldd, a_mn_major, b_mn_major, DT_BF16, act, block_n, 1, nullptr,
+                   0, max_ctas, aux, aux_ld, aux_mode, stream);
 }
 
 // All-gather fused into the GEMM that first consumes the gathered weights (BASELINE north star, SURVEY K8+K1):

@@ -107,6 +107,22 @@ def ag_gemm(x2: torch.Tensor, w: torch.Tensor, plan, bias: Optional[torch.Tensor
     return out
 
 
+def gemm_aux(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int, N: int, K: int, aux: torch.Tensor, aux_mode: int,
+             bias: Optional[torch.Tensor] = None, act: Optional[str] = None) -> torch.Tensor:
+    """tcgen05 GEMM whose epilogue also writes the pre-activation to `aux` (mode 1) or multiplies by gelu'(aux) (mode 2)."""
+    L = _lib.lib()
+    out = torch.empty((M, N), device=a.device, dtype=torch.bfloat16)
+    bn, sp = pick_tile(M, N, K)
+    if sp != 1:
+        bn = 256 if (-(-M // 128) * -(-N // 256) >= NUM_SMS and N >= 256) else 128
+    if bias is not None and bias.dtype not in (torch.float32, torch.bfloat16):
+        bias = bias.float()
+    check(L.dfb_gemm_bf16_aux(ptr(a), ptr(b), ptr(out), ptr(bias), c_int(dt(bias) if bias is not None else 0), M, N, K,
+                              a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn), ACT[act], bn, ptr(aux),
+                              ctypes.c_long(aux.stride(0)), aux_mode, _MAX_CTAS, stream()), "dfb_gemm_bf16_aux")
+    return out
+
+
 def colsum(x2d: torch.Tensor) -> torch.Tensor:
     L = _lib.lib()
     M, N = x2d.shape
@@ -145,6 +161,9 @@ def _init_sigs() -> None:
     L.dfb_ag_gemm_bf16.restype = c_int
     L.dfb_ag_gemm_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 10 + [c_void_p, c_void_p, c_int, c_void_p,
                                                                                           c_void_p, c_int, c_void_p]
+    L.dfb_gemm_bf16_aux.restype = c_int
+    L.dfb_gemm_bf16_aux.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 11 + [c_void_p, ctypes.c_long, c_int, c_int,
+                                                                                           c_void_p]
     L.dfb_colsum.restype = c_int
     L.dfb_colsum.argtypes = [c_void_p, c_void_p, c_int, c_int, ctypes.c_long, c_int, c_void_p]
     L.dfb_act.restype = c_int
@@ -246,3 +265,75 @@ def linear_cuda(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tens
     if activation not in ACT:
         raise ValueError(f"unsupported fused activation {activation}")
     return _LinearFn.apply(x, weight, bias, activation, transposed)
+
+
+def _deliver(param, grad: torch.Tensor, shape=None):
+    """Write a parameter gradient into the engine's bucket sink if there is one (returns None then), else return it."""
+    sink = getattr(param, "_dfb_grad_sink", None)
+    if sink is not None:
+        sink.copy_(grad.reshape(-1))
+        param._dfb_grad_ready()
+        return None
+    return grad.to(param.dtype)
+
+
+class _MlpFn(torch.autograd.Function):
+    """y = gelu(x @ w1 + b1) @ w2 + b2 with the GELU living in GEMM epilogues: forward fc1 writes the pre-activation and the
+    GELU output in one pass; backward, fc2's data-gradient GEMM multiplies by gelu'(pre) in its epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2):
+        _init_sigs()
+        K, H = w1.shape
+        N = w2.shape[1]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        pre = torch.empty((M, H), device=x.device, dtype=torch.bfloat16)
+        h = gemm_aux(x2, w1, a_mn=False, b_mn=True, M=M, N=H, K=K, aux=pre, aux_mode=1, bias=b1, act="gelu")
+        y = gemm(h, w2, a_mn=False, b_mn=True, M=M, N=N, K=H, bias=b2)
+        ctx.save_for_backward(x2, pre, h, w1, w2)
+        ctx.refs = (w1, b1, w2, b2)
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, pre, h, w1d, w2d = ctx.saved_tensors
+        w1, b1, w2, b2 = ctx.refs
+        M, K = x2.shape
+        H, N = w2d.shape
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        # fc2: dW2 = h^T dy, db2 = colsum(dy), dpre = (dy W2^T) * gelu'(pre)   <- GELU backward in the dgrad epilogue
+        dw2 = _wgrad(h, dy2, w2, H, N, M)
+        db2 = _deliver(b2, colsum(dy2)) if b2 is not None else None
+        dpre = gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2)
+        # fc1
+        dw1 = _wgrad(x2, dpre, w1, K, H, M)
+        db1 = _deliver(b1, colsum(dpre)) if b1 is not None else None
+        dx = gemm(dpre, w1d, a_mn=False, b_mn=False, M=M, N=K, K=H).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        return dx, dw1, db1, dw2, db2
+
+
+def _wgrad(x2, dy2, weight, K, N, M):
+    sink = getattr(weight, "_dfb_grad_sink", None)
+    if sink is not None:
+        gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out=sink.view(K, N))
+        weight._dfb_grad_ready()
+        return None
+    return gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out_dtype=weight.dtype)
+
+
+FUSE_GELU = False        # measured on B200 (scripts/bench_aux.py): the aux epilogues make the GEMM epilogue-bound
+                         # (fwd 274 us vs 226 us, bwd 315 us vs 204 us at 32768x768x3072), so the separate kernels stay
+
+
+def mlp_cuda(x, w1, b1, w2, b2):
+    ok = FUSE_GELU and x.dtype == torch.bfloat16 and all(t.dtype == torch.bfloat16 for t in (w1, w2)) and w1.shape[1] % 8 == 0 \
+        and w1.shape[0] % 8 == 0 and w2.shape[1] % 8 == 0 and w1.is_contiguous() and w2.is_contiguous()
+    if not ok:
+        return linear_cuda(linear_cuda(x, w1, b1, "gelu"), w2, b2, None)
+    return _MlpFn.apply(x, w1, b1, w2, b2)

@@ -29,6 +29,12 @@ int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int b
                   int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits,
                   void* workspace, size_t workspace_bytes, int max_ctas, void* stream);
 
+/* GEMM with an auxiliary bf16 matrix in the epilogue: aux_mode 1 also stores the pre-activation, aux_mode 2 multiplies by
+ * gelu'(aux) (fused GELU backward).  Replaces the activation ops around Dense layers of the tf.js graph. */
+int dfb_gemm_bf16_aux(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda,
+                      int ldb, int ldd, int a_mn_major, int b_mn_major, int act, int block_n, void* aux, long aux_ld,
+                      int aux_mode, int max_ctas, void* stream);
+
 /* All-gather fused into the first consuming GEMM: D = act(A * W + bias) with W[K,N] sharded over ranks; two extra warps
  * per CTA pull the remote shards over NVLink into the local W buffer while the k-loop starts on local rows.
  * Replaces the weight broadcast of /root/reference/src/server/federated_server.ts:80 for that layer (SURVEY K8+K1). */

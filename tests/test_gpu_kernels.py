@@ -396,3 +396,28 @@ def test_resnet20_and_resnet50_block_step_on_gpu():
     out = blk(xb)
     out.float().square().mean().backward()
     assert torch.isfinite(out.float()).all() and torch.isfinite(xb.grad.float()).all()
+
+
+def test_fused_mlp_gelu_in_epilogues():
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    D, H = 256, 1024
+    x = torch.randn(3, 200, D, device=dev()).bfloat16().requires_grad_(True)
+    w1 = (torch.randn(D, H, device=dev()) * 0.05).bfloat16().requires_grad_(True)
+    b1 = (torch.randn(H, device=dev()) * 0.1).bfloat16().requires_grad_(True)
+    w2 = (torch.randn(H, D, device=dev()) * 0.05).bfloat16().requires_grad_(True)
+    b2 = (torch.randn(D, device=dev()) * 0.1).bfloat16().requires_grad_(True)
+    from distriflow_b200.ops import dense
+    dense.FUSE_GELU = True
+    try:
+        y = ops.mlp(x, w1, b1, w2, b2)
+        gy = torch.randn_like(y)
+        y.backward(gy)
+    finally:
+        dense.FUSE_GELU = False
+    ref = [t.detach().float().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    yr = F.gelu(ref[0] @ ref[1] + ref[2], approximate="tanh") @ ref[3] + ref[4]
+    yr.backward(gy.float())
+    assert rel_err(y, yr) < 2e-2
+    for got, r in zip((x, w1, b1, w2, b2), ref):
+        assert rel_err(got.grad, r.grad) < 3e-2
