@@ -29,6 +29,8 @@ def _sigs():
         L.dfb_maxpool_nhwc_bwd.argtypes = [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_conv2d_tc.restype = c_int
         L.dfb_conv2d_tc.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p, ctypes.c_size_t, c_void_p]
+        L.dfb_im2col_nhwc.restype = c_int
+        L.dfb_im2col_nhwc.argtypes = [c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_conv2d_tc_supported.restype = c_int
         L.dfb_conv2d_tc_supported.argtypes = [c_int] * 12
         L._dfb_conv_sigs = True
@@ -76,6 +78,74 @@ def _conv_tc(mode: int, a, b, out, bias, geom, act):
                           N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl, dt(a), 1 if out.dtype == torch.float32 else 0,
                           ACT[act], 0, None, ctypes.c_size_t(0), stream()), "dfb_conv2d_tc")
     return out
+
+
+def _im2col(x, geom, kpad):
+    L = _sigs()
+    (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = geom
+    out = torch.empty((N * OH * OW, kpad), device=x.device, dtype=torch.bfloat16)
+    check(L.dfb_im2col_nhwc(ptr(x), ptr(out), N, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, kpad, stream()), "dfb_im2col_nhwc")
+    return out
+
+
+class _ThinConvFn(torch.autograd.Function):
+    """Convolution with very few input channels (ResNet stems, C_in = 3): bf16 patch matrix + the tcgen05 Dense GEMM for the
+    forward and the filter gradient; the patch matrix is rebuilt in backward instead of being kept."""
+
+    @staticmethod
+    def forward(ctx, x, kernel, bias, strides, padding, activation):
+        from .dense import _init_sigs, gemm
+        _init_sigs()
+        x = x.contiguous()
+        N, H, W, C = x.shape
+        kh, kw, _, K = kernel.shape
+        OH, OW, pt, pl = _geometry(H, W, kh, kw, strides, padding)
+        geom = (N, H, W, C, OH, OW, K, kh, kw, strides[0], strides[1], pt, pl)
+        kreal = kh * kw * C
+        kpad = -(-kreal // 64) * 64
+        wmat = torch.zeros((kpad, K), device=x.device, dtype=torch.bfloat16)
+        wmat[:kreal] = kernel.reshape(kreal, K).to(torch.bfloat16)
+        patches = _im2col(x, geom, kpad)
+        y = gemm(patches, wmat, a_mn=False, b_mn=True, M=N * OH * OW, N=K, K=kpad, bias=bias, act=activation)
+        ctx.geom, ctx.activation, ctx.kpad = geom, activation, kpad
+        ctx.kernel_ref, ctx.bias_ref = kernel, bias
+        ctx.save_for_backward(x, wmat, y if activation == "relu" else None)
+        return y.view(N, OH, OW, K)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .dense import act_op, gemm
+        x, wmat, y = ctx.saved_tensors
+        (N, H, W, C, OH, OW, K, kh, kw, sh, sw, pt, pl) = ctx.geom
+        kreal = kh * kw * C
+        dy2 = dy.reshape(-1, K).contiguous()
+        if ctx.activation == "relu":
+            dy2 = act_op(dy2, y, 2)
+        kernel, bias = ctx.kernel_ref, ctx.bias_ref
+        dx = dw = db = None
+        if ctx.needs_input_grad[1]:
+            patches = _im2col(x, ctx.geom, ctx.kpad)
+            dwm = gemm(patches, dy2, a_mn=True, b_mn=True, M=ctx.kpad, N=K, K=N * OH * OW, out_dtype=torch.float32)
+            dw_full = dwm[:kreal].reshape(kh, kw, C, K)
+            sink = getattr(kernel, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.view(kh, kw, C, K).copy_(dw_full)
+                kernel._dfb_grad_ready()
+            else:
+                dw = dw_full.to(kernel.dtype)
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _conv_call(1, dy2.view(N, OH, OW, K), ctx.kernel_ref.to(x.dtype).contiguous(), dx, None, ctx.geom, None)
+        if bias is not None and ctx.needs_input_grad[2]:
+            db = colsum(dy2)
+            sink = getattr(bias, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.copy_(db)
+                bias._dfb_grad_ready()
+                db = None
+            else:
+                db = db.to(bias.dtype)
+        return dx, dw, db, None, None, None
 
 
 class _Conv2dFn(torch.autograd.Function):
@@ -146,6 +216,9 @@ class _Conv2dFn(torch.autograd.Function):
 
 
 def conv2d_cuda(x, kernel, bias, strides, padding, activation):
+    C, K = kernel.shape[2], kernel.shape[3]
+    if x.dtype == torch.bfloat16 and C < 16 and K % 8 == 0 and not FORCE_SIMT and x.shape[0] * x.shape[1] * x.shape[2] >= 4096:
+        return _ThinConvFn.apply(x, kernel, bias, tuple(strides), padding, activation)
     return _Conv2dFn.apply(x, kernel, bias, tuple(strides), padding, activation)
 
 

@@ -7,7 +7,8 @@
 // coordinates are zero-filled by the TMA unit, which is exactly the convolution padding; the traversal stride of the
 // tensor map (`elementStrides`) is the convolution stride.
 //   FWD    Y[p, co]         = sum_{tap, ci} X[p (+) tap, ci] * W[tap, ci, co]     A K-major,  B MN-major (W rows = tap*C+ci)
-//   DGRAD  dX[q, ci]        = sum_{tap, co} dY[q (-) tap, co] * W[tap, ci, co]    A K-major,  B K-major   (stride 1)
+//   DGRAD  dX[q, ci]        = sum_{tap, co} dY[q (-) tap, co] * W[tap, ci, co]    A K-major,  B K-major; strided convs: one
+//          launch per parity class of the input pixel, written to a strided sub-grid of dX
 //   WGRAD  dW[tap, ci, co] += sum_{p} X[p (+) tap, ci] * dY[p, co]                A, B MN-major, K = pixels, split over
 //          pixel tiles and combined with TMA reduce-add (cp.reduce.async.bulk.tensor .add.f32) into a zeroed fp32 dW.
 // Replaces the tf.js conv2d forward/backward of the Conv2D layers in /root/reference/experiment/mnist/model.json for
@@ -46,6 +47,7 @@ struct CvParams {
   int stride_h, stride_w;  // FWD/WGRAD: convolution stride (start = o*stride + off + tap); DGRAD: 1
   int off_h, off_w;        // FWD/WGRAD: -pad_top/-pad_left;  DGRAD: +pad
   int tap_sign;            // +1 FWD/WGRAD, -1 DGRAD
+  int tap_dh[9], tap_dw[9], tap_w[9];   // DGRAD: per contributing tap, the dY offset of output pixel (a, b) and the filter tap index
   int a_bytes;             // bytes one A box delivers (FWD/DGRAD: rows*128; WGRAD: per 64-channel atom)
   int b_bytes;             // WGRAD: bytes per B atom box
   int splits, kb_per_split;// WGRAD: split of the pixel-tile loop
@@ -166,13 +168,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_expect_tx(&full_bar[stage], p.a_bytes + Cfg::kBTile);
             uint8_t* sa = smem_a + stage * kCvATile;
             uint8_t* sb = smem_b + stage * Cfg::kBTile;
-            tma_load_4d(sa, &tmA, &full_bar[stage], c0, p.off_w + p.tap_sign * s, h0 * p.stride_h + p.off_h + p.tap_sign * r, img0);
+            if (MODE == CV_DGRAD) tma_load_4d(sa, &tmA, &full_bar[stage], c0, p.tap_dw[tap], h0 + p.tap_dh[tap], img0);
+            else tma_load_4d(sa, &tmA, &full_bar[stage], c0, p.off_w + s, h0 * p.stride_h + p.off_h + r, img0);
             if (MODE == CV_FWD) {       // W rows = tap*C_in + ci (K), columns = co (N): MN-major, 64x64 atoms
 #pragma unroll
               for (int i = 0; i < BLOCK_N / 64; ++i)
                 tma_load_2d(sb + i * kCvAtom, &tmB, &full_bar[stage], n0 + 64 * i, tap * p.Ck + c0);
             } else {                    // DGRAD: rows = tap*C_in + ci (N), columns = co (K): K-major
-              tma_load_2d(sb, &tmB, &full_bar[stage], c0, tap * p.Cn + n0);
+              tma_load_2d(sb, &tmB, &full_bar[stage], c0, p.tap_w[tap] * p.Cn + n0);
             }
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
@@ -351,6 +354,15 @@ static int nhwc_map(CUtensorMap* tm, const void* base, int N, int H, int W, int 
   return encode_tmap(tm, base, 0, 4, dims, str, box, es, 1);
 }
 
+// [N, H', W', C] view with explicit pixel strides (bytes) — the parity sub-grids of a strided data gradient
+static int nhwc_map_strided(CUtensorMap* tm, const void* base, int N, int H, int W, int C, long sw_bytes, long sh_bytes, long sn_bytes,
+                            int bc, int bw, int bh, int bn) {
+  uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  uint64_t str[3] = {(uint64_t)sw_bytes, (uint64_t)sh_bytes, (uint64_t)sn_bytes};
+  uint32_t box[4] = {(uint32_t)bc, (uint32_t)bw, (uint32_t)bh, (uint32_t)bn};
+  return encode_tmap(tm, base, 0, 4, dims, str, box, nullptr, 1);
+}
+
 }  // namespace dfb
 
 using namespace dfb;
@@ -358,8 +370,8 @@ using namespace dfb;
 // 1 if the tcgen05 path takes this problem (otherwise callers use dfb_conv2d_simt).
 DFB_API int dfb_conv2d_tc_supported(int mode, int N, int H, int W, int C, int OH, int OW, int K, int kh, int kw, int sh, int sw) {
   if (C % 64 != 0 || K % 64 != 0) return 0;
-  if (mode == CV_DGRAD && (sh != 1 || sw != 1)) return 0;
-  if (mode == CV_DGRAD) { if (W > 128) return 0; } else if (OW > (mode == CV_WGRAD ? 64 : 128)) return 0;
+  if (mode == CV_DGRAD && (kh * kw > 9 || sh > 2 || sw > 2)) return 0;
+  if (mode == CV_DGRAD) { if (ceil_div(W, sw) > 128) return 0; } else if (OW > (mode == CV_WGRAD ? 64 : 128)) return 0;
   if ((OW - 1) * sw + 1 > 256 || (OH - 1) * sh + 1 > 100000) return 0;
   return 1;
 }
@@ -401,21 +413,49 @@ DFB_API int dfb_conv2d_tc(int mode, const void* a, const void* b, void* out, con
     return launch_conv_tc<CV_FWD, 64>(tmA, tmB, tmD, p, tiles, stream);
   }
   if (mode == CV_DGRAD) {
-    pick_pixel_tile(128, N, H, W, p.tn, p.th, p.tw);
-    p.tiles_h = ceil_div(H, p.th); p.tiles_n = ceil_div(N, p.tn);
-    p.Ck = K; p.Cn = C; p.stride_h = 1; p.stride_w = 1; p.off_h = pt; p.off_w = pl; p.tap_sign = -1;
-    p.a_bytes = p.tn * p.th * p.tw * 128;
-    if (nhwc_map(&tmA, a, N, OH, OW, K, 64, p.tw, p.th, p.tn, 1, 1)) return 4;
-    const int bn = C % 256 == 0 && p.tiles_h * p.tiles_n * (C / 256) >= num_sms() ? 256 : (C % 128 == 0 ? 128 : 64);
+    // dX[n, ih, iw, :] = sum over taps (r, s) with (ih + pt - r) % sh == 0 and (iw + pl - s) % sw == 0 of
+    // dY[n, (ih+pt-r)/sh, (iw+pl-s)/sw, :] * W[r, s]^T.  Pixels of one parity class (ih % sh, iw % sw) share the same
+    // tap subset, so each class is a stride-1 gather over dY written to a strided sub-grid of dX (strides in the map).
+    p.Ck = K; p.Cn = C; p.stride_h = 1; p.stride_w = 1; p.tap_sign = -1;
+    const int bn = C % 256 == 0 && ceil_div(N * H * W, 128 * sh * sw) * (C / 256) >= num_sms() ? 256 : (C % 128 == 0 ? 128 : 64);
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)kh * kw * C};
     uint64_t str[1] = {(uint64_t)K * 2};
     uint32_t box[2] = {64, (uint32_t)bn};
     if (encode_tmap(&tmB, b, 0, 2, dims, str, box, nullptr, 1)) return 4;
-    if (nhwc_map(&tmD, out, N, H, W, C, 64, p.tw, p.th, p.tn, 1, 1)) return 4;
-    const int tiles = p.tiles_h * p.tiles_n * ceil_div(C, bn);
-    if (bn == 256) return launch_conv_tc<CV_DGRAD, 256>(tmA, tmB, tmD, p, tiles, stream);
-    if (bn == 128) return launch_conv_tc<CV_DGRAD, 128>(tmA, tmB, tmD, p, tiles, stream);
-    return launch_conv_tc<CV_DGRAD, 64>(tmA, tmB, tmD, p, tiles, stream);
+    if (sh > 1 || sw > 1) DFB_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)N * H * W * C * 2, stream));   // classes without taps stay zero
+    for (int ph = 0; ph < sh; ++ph) {
+      for (int pw = 0; pw < sw; ++pw) {
+        const int Hc = (H - ph + sh - 1) / sh, Wc = (W - pw + sw - 1) / sw;
+        if (Hc <= 0 || Wc <= 0) continue;
+        int nt = 0;
+        for (int r = 0; r < kh; ++r) {
+          if ((ph + pt - r) % sh != 0) continue;
+          for (int s2 = 0; s2 < kw; ++s2) {
+            if ((pw + pl - s2) % sw != 0) continue;
+            p.tap_dh[nt] = (ph + pt - r) / sh;       // exact: the numerator is a multiple of sh (C++ division of an exact multiple)
+            p.tap_dw[nt] = (pw + pl - s2) / sw;
+            p.tap_w[nt] = r * kw + s2;
+            ++nt;
+          }
+        }
+        if (nt == 0) continue;
+        p.taps = nt;
+        pick_pixel_tile(128, N, Hc, Wc, p.tn, p.th, p.tw);
+        p.tiles_h = ceil_div(Hc, p.th); p.tiles_n = ceil_div(N, p.tn);
+        p.a_bytes = p.tn * p.th * p.tw * 128;
+        if (nhwc_map(&tmA, a, N, OH, OW, K, 64, p.tw, p.th, p.tn, 1, 1)) return 4;
+        const char* dbase = reinterpret_cast<const char*>(out) + ((size_t)ph * W + pw) * C * 2;
+        if (nhwc_map_strided(&tmD, dbase, N, Hc, Wc, C, (long)sw * C * 2, (long)sh * W * C * 2, (long)H * W * C * 2, 64, p.tw, p.th,
+                             p.tn))
+          return 4;
+        const int tiles = p.tiles_h * p.tiles_n * ceil_div(C, bn);
+        int rc = bn == 256 ? launch_conv_tc<CV_DGRAD, 256>(tmA, tmB, tmD, p, tiles, stream)
+                 : bn == 128 ? launch_conv_tc<CV_DGRAD, 128>(tmA, tmB, tmD, p, tiles, stream)
+                             : launch_conv_tc<CV_DGRAD, 64>(tmA, tmB, tmD, p, tiles, stream);
+        if (rc) return rc;
+      }
+    }
+    return 0;
   }
   // WGRAD
   pick_pixel_tile(64, N, OH, OW, p.tn, p.th, p.tw);

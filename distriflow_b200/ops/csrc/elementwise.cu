@@ -289,3 +289,50 @@ DFB_API int dfb_accuracy(const void* pred, const void* labels, int label_kind, f
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------- im2col for thin-channel convolutions (ResNet stem: C_in = 3)
+// patches[p, k] = X[n, oh*sh-pt+r, ow*sw-pl+s, ci] with k = (r*kw+s)*C+ci, zero for padding and for k >= kh*kw*C (row pitch
+// Kpad, a multiple of 8).  With C_in < 64 the implicit-GEMM TMA path has no 128-byte channel rows to fetch, so the patch
+// matrix is materialised once (bf16) and the tcgen05 Dense GEMM does forward and filter gradient on it.
+namespace dfb {
+__global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int H,
+                                                     int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
+                                                     int Kpad) {
+  const int k8n = Kpad >> 3;
+  const long total = (long)N * OH * OW * k8n;
+  const int Kreal = kh * kw * C;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+    const int k8 = (int)(i % k8n);
+    long pix = i / k8n;
+    const int ow = (int)(pix % OW);
+    long t = pix / OW;
+    const int oh = (int)(t % OH), n = (int)(t / OH);
+    __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = k8 * 8 + j;
+      float val = 0.f;
+      if (k < Kreal) {
+        const int ci = k % C, rs = k / C, s = rs % kw, r = rs / kw;
+        const int ih = oh * sh - pt + r, iw = ow * sw - pl + s;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = __bfloat162float(x[(((long)n * H + ih) * W + iw) * C + ci]);
+      }
+      v[j] = __float2bfloat16(val);
+    }
+    *reinterpret_cast<uint4*>(out + pix * Kpad + k8 * 8) = *reinterpret_cast<const uint4*>(v);
+  }
+}
+}  // namespace dfb
+
+DFB_API int dfb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                            int pt, int pl, int Kpad, cudaStream_t stream) {
+  DFB_REQUIRE(Kpad % 8 == 0 && Kpad >= kh * kw * C, "im2col: Kpad must be a multiple of 8 covering kh*kw*C");
+  const long total = (long)N * OH * OW * (Kpad / 8);
+  DFB_REQUIRE(total > 0, "im2col: empty");
+  long blocks = (total + 255) / 256;
+  if (blocks > dfb::num_sms() * 32) blocks = dfb::num_sms() * 32;
+  dfb::im2col_kernel<<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, OH, OW, kh, kw, sh,
+                                                   sw, pt, pl, Kpad);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}

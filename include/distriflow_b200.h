@@ -73,6 +73,10 @@ int dfb_conv2d_tc(int mode, const void* a, const void* b, void* out, const void*
                   int C, int OH, int OW, int K, int kh, int kw, int sh, int sw, int pt, int pl, int dtype, int out_is_f32,
                   int act, int reserved, void* workspace, size_t workspace_bytes, void* stream);
 
+/* bf16 patch matrix for thin-channel convolutions (ResNet stem): the Dense GEMM then does forward and filter gradient. */
+int dfb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt,
+                    int pl, int Kpad, void* stream);
+
 /* ---- Fused softmax-cross-entropy forward + backward (csrc/softmax_ce.cu) ------------------------------
  * Replaces tf.losses.softmaxCrossEntropy(...).mean() + its gradient: /root/reference/src/common/models.ts:139.
  * mode of the dense form: 0 standard, 1 reference-compat (tfjs custom gradient), 2 reference-compat (true gradient). */

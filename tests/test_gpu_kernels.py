@@ -421,3 +421,17 @@ def test_fused_mlp_gelu_in_epilogues():
     assert rel_err(y, yr) < 2e-2
     for got, r in zip((x, w1, b1, w2, b2), ref):
         assert rel_err(got.grad, r.grad) < 3e-2
+
+
+def test_thin_channel_conv_stem_im2col_path():
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(4, 64, 64, 3, device=dev()).bfloat16()
+    w = (torch.randn(7, 7, 3, 64, device=dev()) * 0.05).bfloat16().requires_grad_(True)
+    y = ops.conv2d_nhwc(x, w, None, (2, 2), "same", None)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    wr = w.detach().float().cpu().requires_grad_(True)
+    yr = ops.conv2d_nhwc(x.float().cpu(), wr, None, (2, 2), "same", None)
+    yr.backward(gy.float().cpu())
+    assert y.shape == yr.shape and rel_err(y.cpu(), yr) < 2e-2 and rel_err(w.grad.cpu(), wr.grad) < 2e-2
