@@ -134,8 +134,19 @@ class _ThinConvFn(torch.autograd.Function):
             else:
                 dw = dw_full.to(kernel.dtype)
         if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x)
-            _conv_call(1, dy2.view(N, OH, OW, K), ctx.kernel_ref.to(x.dtype).contiguous(), dx, None, ctx.geom, None)
+            if sh == 1 and sw == 1 and K % 8 == 0 and C % 8 == 0:
+                # data gradient = stride-1 correlation of dY with the flipped, transposed filter: same patch-matrix GEMM
+                pth, plw = kh - 1 - pt, kw - 1 - pl
+                g2 = (N, OH, OW, K, H, W, C, kh, kw, 1, 1, pth, plw)
+                kreal2 = kh * kw * K
+                kpad2 = -(-kreal2 // 64) * 64
+                wflip = torch.zeros((kpad2, C), device=x.device, dtype=torch.bfloat16)
+                wflip[:kreal2] = kernel.detach().to(torch.bfloat16).flip(0, 1).permute(0, 1, 3, 2).reshape(kreal2, C)
+                pdy = _im2col(dy2.view(N, OH, OW, K), g2, kpad2)
+                dx = gemm(pdy, wflip, a_mn=False, b_mn=True, M=N * H * W, N=C, K=kpad2).view(N, H, W, C)
+            else:
+                dx = torch.empty_like(x)
+                _conv_call(1, dy2.view(N, OH, OW, K), ctx.kernel_ref.to(x.dtype).contiguous(), dx, None, ctx.geom, None)
         if bias is not None and ctx.needs_input_grad[2]:
             db = colsum(dy2)
             sink = getattr(bias, "_dfb_grad_sink", None)
@@ -217,7 +228,8 @@ class _Conv2dFn(torch.autograd.Function):
 
 def conv2d_cuda(x, kernel, bias, strides, padding, activation):
     C, K = kernel.shape[2], kernel.shape[3]
-    if x.dtype == torch.bfloat16 and C < 16 and K % 8 == 0 and not FORCE_SIMT and x.shape[0] * x.shape[1] * x.shape[2] >= 4096:
+    thin = C < 64 or K < 64            # no 128-byte channel rows for the TMA implicit-GEMM path
+    if x.dtype == torch.bfloat16 and thin and K % 16 == 0 and not FORCE_SIMT and x.shape[0] * x.shape[1] * x.shape[2] >= 4096:
         return _ThinConvFn.apply(x, kernel, bias, tuple(strides), padding, activation)
     return _Conv2dFn.apply(x, kernel, bias, tuple(strides), padding, activation)
 

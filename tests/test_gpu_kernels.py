@@ -435,3 +435,21 @@ def test_thin_channel_conv_stem_im2col_path():
     yr = ops.conv2d_nhwc(x.float().cpu(), wr, None, (2, 2), "same", None)
     yr.backward(gy.float().cpu())
     assert y.shape == yr.shape and rel_err(y.cpu(), yr) < 2e-2 and rel_err(w.grad.cpu(), wr.grad) < 2e-2
+
+
+@pytest.mark.parametrize("cfg", [dict(C=16, K=16, k=3, s=1), dict(C=16, K=32, k=3, s=2), dict(C=32, K=32, k=3, s=1),
+                                 dict(C=32, K=64, k=1, s=2), dict(C=64, K=32, k=3, s=1)])
+def test_small_channel_conv_patch_gemm_path(cfg):
+    """ResNet-20 channel counts (16 / 32): patch matrix + tcgen05 GEMM for forward, filter and (stride 1) data gradient."""
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(8, 32, 32, cfg["C"], device=dev()).bfloat16().requires_grad_(True)
+    w = (torch.randn(cfg["k"], cfg["k"], cfg["C"], cfg["K"], device=dev()) * 0.1).bfloat16().requires_grad_(True)
+    y = ops.conv2d_nhwc(x, w, None, (cfg["s"], cfg["s"]), "same", None)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr, wr = x.detach().float().cpu().requires_grad_(True), w.detach().float().cpu().requires_grad_(True)
+    yr = ops.conv2d_nhwc(xr, wr, None, (cfg["s"], cfg["s"]), "same", None)
+    yr.backward(gy.float().cpu())
+    assert y.shape == yr.shape and rel_err(y.cpu(), yr) < 2e-2
+    assert rel_err(x.grad.cpu(), xr.grad) < 2e-2 and rel_err(w.grad.cpu(), wr.grad) < 2e-2
