@@ -29,6 +29,8 @@ def _sigs():
         L.dfb_maxpool_nhwc_bwd.argtypes = [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_conv2d_tc.restype = c_int
         L.dfb_conv2d_tc.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 18 + [c_void_p, ctypes.c_size_t, c_void_p]
+        L.dfb_col2im_nhwc.restype = c_int
+        L.dfb_col2im_nhwc.argtypes = [c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_im2col_nhwc.restype = c_int
         L.dfb_im2col_nhwc.argtypes = [c_void_p, c_void_p] + [c_int] * 13 + [c_void_p]
         L.dfb_conv2d_tc_supported.restype = c_int
@@ -144,6 +146,12 @@ class _ThinConvFn(torch.autograd.Function):
                 wflip[:kreal2] = kernel.detach().to(torch.bfloat16).flip(0, 1).permute(0, 1, 3, 2).reshape(kreal2, C)
                 pdy = _im2col(dy2.view(N, OH, OW, K), g2, kpad2)
                 dx = gemm(pdy, wflip, a_mn=False, b_mn=True, M=N * H * W, N=C, K=kpad2).view(N, H, W, C)
+            elif C % 8 == 0 and K % 8 == 0:
+                # strided: patch gradient dP = dY @ Wmat^T on the tensor cores, then the gather form of col2im
+                dpatch = gemm(dy2, wmat, a_mn=False, b_mn=False, M=N * OH * OW, N=ctx.kpad, K=K)
+                dx = torch.empty_like(x)
+                check(_sigs().dfb_col2im_nhwc(ptr(dpatch), ptr(dx), N, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, ctx.kpad, stream()),
+                      "dfb_col2im_nhwc")
             else:
                 dx = torch.empty_like(x)
                 _conv_call(1, dy2.view(N, OH, OW, K), ctx.kernel_ref.to(x.dtype).contiguous(), dx, None, ctx.geom, None)

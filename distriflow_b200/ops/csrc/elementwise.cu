@@ -307,6 +307,17 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
     const int ow = (int)(pix % OW);
     long t = pix / OW;
     const int oh = (int)(t % OH), n = (int)(t / OH);
+    if ((C & 7) == 0) {           // 8 consecutive k = 8 consecutive channels of one tap: a single 16-byte load
+      const int k = k8 * 8;
+      uint4 q = make_uint4(0, 0, 0, 0);
+      if (k < Kreal) {
+        const int ci = k % C, rs = k / C, s = rs % kw, r = rs / kw;
+        const int ih = oh * sh - pt + r, iw = ow * sw - pl + s;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) q = *reinterpret_cast<const uint4*>(x + (((long)n * H + ih) * W + iw) * C + ci);
+      }
+      *reinterpret_cast<uint4*>(out + pix * Kpad + k) = q;
+      continue;
+    }
     __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -323,6 +334,58 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
   }
 }
 }  // namespace dfb
+
+namespace dfb {
+// dX[n, ih, iw, c..c+8) = sum over taps (r, s) with (ih+pt-r) % sh == 0, (iw+pl-s) % sw == 0 of
+// dP[(n, (ih+pt-r)/sh, (iw+pl-s)/sw), (r*kw+s)*C + c]   — the gather form of col2im (no atomics), C % 8 == 0.
+__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dp, __nv_bfloat16* __restrict__ dx, int N, int H,
+                                                     int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
+                                                     int Kpad) {
+  const int c8n = C >> 3;
+  const long total = (long)N * H * W * c8n;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+    const int c = (int)(i % c8n) * 8;
+    long t = i / c8n;
+    const int iw = (int)(t % W); t /= W;
+    const int ih = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < kh; ++r) {
+      const int th = ih + pt - r;
+      if (th < 0 || th % sh) continue;
+      const int oh = th / sh;
+      if (oh >= OH) continue;
+      for (int s = 0; s < kw; ++s) {
+        const int tw = iw + pl - s;
+        if (tw < 0 || tw % sw) continue;
+        const int ow = tw / sw;
+        if (ow >= OW) continue;
+        const uint4 q = *reinterpret_cast<const uint4*>(dp + (((long)n * OH + oh) * OW + ow) * Kpad + (r * kw + s) * C + c);
+        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&q);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += __bfloat162float(h[j]);
+      }
+    }
+    __align__(16) __nv_bfloat16 o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16(acc[j]);
+    *reinterpret_cast<uint4*>(dx + i * 8) = *reinterpret_cast<const uint4*>(o);
+  }
+}
+}  // namespace dfb
+
+DFB_API int dfb_col2im_nhwc(const void* dp, void* dx, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                            int pt, int pl, int Kpad, cudaStream_t stream) {
+  DFB_REQUIRE(C % 8 == 0 && Kpad % 8 == 0 && Kpad >= kh * kw * C, "col2im: C and Kpad must be multiples of 8");
+  const long total = (long)N * H * W * (C / 8);
+  long blocks = (total + 255) / 256;
+  if (blocks > dfb::num_sms() * 32) blocks = dfb::num_sms() * 32;
+  if (blocks < 1) blocks = 1;
+  dfb::col2im_kernel<<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)dp, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, kh, kw, sh,
+                                                   sw, pt, pl, Kpad);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
 
 DFB_API int dfb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
                             int pt, int pl, int Kpad, cudaStream_t stream) {

@@ -74,6 +74,8 @@ int dfb_conv2d_tc(int mode, const void* a, const void* b, void* out, const void*
                   int act, int reserved, void* workspace, size_t workspace_bytes, void* stream);
 
 /* bf16 patch matrix for thin-channel convolutions (ResNet stem): the Dense GEMM then does forward and filter gradient. */
+int dfb_col2im_nhwc(const void* dpatches, void* dx, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                    int pt, int pl, int Kpad, void* stream);
 int dfb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt,
                     int pl, int Kpad, void* stream);
 
