@@ -226,7 +226,7 @@ class AsyncEngine:
             loss.backward()
             self.state.push(None, self.grad_flat, ticket=t)
             self.state.apply()
-            wq.complete()
+            wq.complete(accepted=self.state.loc[self.rank].push_state[15:16])
             host = torch.empty(2, dtype=torch.int32, pin_memory=True)
             host.copy_(t, non_blocking=True)
             ev = torch.cuda.Event()

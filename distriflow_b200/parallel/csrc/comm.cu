@@ -304,34 +304,44 @@ struct AsyncPushArgs {
   const uint32_t* ticket;  // optional work-queue ticket of this step: 0xffffffff (dataset exhausted) turns the push into a no-op
 };
 
-// Phase 1 (one block): per owner, read its version, apply the staleness guard, register as in-flight pusher.
+// Phase 1 (one thread): read every owner's version, apply the staleness guard ONCE for the whole gradient (all owners or
+// none, so the shards keep counting the same set of gradients), then register as in-flight pusher on every owner.
+// push_state[0..R) = chosen buffer per owner or 0xffffffff, [8..8+R) = staleness, [15] = 1 if the gradient was accepted.
 __global__ void async_push_begin_kernel(const AsyncPushArgs a) {
-  const int o = threadIdx.x;
-  if (o >= a.R) return;
+  if (threadIdx.x != 0) return;
+  a.push_state[15] = 0;
   if (a.ticket != nullptr && a.ticket[0] == 0xffffffffu) {      // no batch was dispatched for this step: nothing to push
-    a.push_state[o] = 0xffffffffu;
+    for (int o = 0; o < a.R; ++o) a.push_state[o] = 0xffffffffu;
     return;
   }
-  uint32_t* ctl = reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase;
-  const uint32_t ver = ld_acquire_sys(ctl + A_VERSION);
-  const int staleness = (int)(ver - a.seen_version[o]);
-  if (staleness > a.max_staleness) {
-    atomicAdd_system(ctl + A_DROPPED, 1u);
-    a.push_state[o] = 0xffffffffu;
-    a.push_state[kMaxRanks + o] = (uint32_t)staleness;
+  int worst = 0;
+  for (int o = 0; o < a.R; ++o) {
+    const uint32_t* ctl = reinterpret_cast<const uint32_t*>(a.sig.p[o]) + kAsyncBase;
+    const int st = (int)(ld_acquire_sys(ctl + A_VERSION) - a.seen_version[o]);
+    a.push_state[kMaxRanks + o] = (uint32_t)(st < 0 ? 0 : st);
+    worst = max(worst, st);
+  }
+  if (worst > a.max_staleness) {
+    for (int o = 0; o < a.R; ++o) {
+      atomicAdd_system(reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase + A_DROPPED, 1u);
+      a.push_state[o] = 0xffffffffu;
+    }
     return;
   }
-  uint32_t b;
-  while (true) {                                        // register on the buffer that is open *now*
-    b = ld_acquire_sys(ctl + A_ACTIVE) & 1u;
-    atomicAdd_system(ctl + A_INFLIGHT + b, 1u);
-    __threadfence_system();
-    if ((ld_acquire_sys(ctl + A_ACTIVE) & 1u) == b) break;
-    atomicSub_system(ctl + A_INFLIGHT + b, 1u);         // the owner flipped in between: retry on the new one
+  for (int o = 0; o < a.R; ++o) {
+    uint32_t* ctl = reinterpret_cast<uint32_t*>(a.sig.p[o]) + kAsyncBase;
+    uint32_t b;
+    while (true) {                                        // register on the buffer that is open *now*
+      b = ld_acquire_sys(ctl + A_ACTIVE) & 1u;
+      atomicAdd_system(ctl + A_INFLIGHT + b, 1u);
+      __threadfence_system();
+      if ((ld_acquire_sys(ctl + A_ACTIVE) & 1u) == b) break;
+      atomicSub_system(ctl + A_INFLIGHT + b, 1u);         // the owner flipped in between: retry on the new one
+    }
+    a.push_state[o] = b;
+    atomicMax_system(ctl + A_MAXSEEN, (uint32_t)worst);
   }
-  a.push_state[o] = b;
-  a.push_state[kMaxRanks + o] = (uint32_t)staleness;
-  atomicMax_system(ctl + A_MAXSEEN, (uint32_t)staleness);
+  a.push_state[15] = 1;
 }
 
 // Phase 2: add every slice of the gradient into its owner's open accumulation buffer with P2P reductions.
@@ -499,8 +509,9 @@ __global__ void wq_take_kernel(uint32_t* wq, uint32_t* out) {
 }
 
 // Mark `batch` of `epoch` complete (idempotent).  The completion that finishes the epoch advances it.
-__global__ void wq_complete_kernel(uint32_t* wq, const uint32_t* ticket) {
+__global__ void wq_complete_kernel(uint32_t* wq, const uint32_t* ticket, const uint32_t* accepted) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (accepted != nullptr && *accepted == 0) return;    // the gradient of this batch was refused: leave it incomplete -> re-issued
   const uint32_t b = ticket[0], epoch = ticket[1];
   if (b == 0xffffffffu) return;
   if (ld_acquire_sys(wq + W_EPOCH) != epoch) return;    // stale completion from a previous epoch: ignored
@@ -738,8 +749,8 @@ DFB_API int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, cudaStream_t 
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
-DFB_API int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, cudaStream_t stream) {
-  wq_complete_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket2);
+DFB_API int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, const unsigned* accepted, cudaStream_t stream) {
+  wq_complete_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket2, accepted);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -340,7 +340,7 @@ def _comm_sigs():
         L.dfb_wq_take.restype = c_int
         L.dfb_wq_take.argtypes = [c_void_p, c_void_p, c_void_p]
         L.dfb_wq_complete.restype = c_int
-        L.dfb_wq_complete.argtypes = [c_void_p, c_void_p, c_void_p]
+        L.dfb_wq_complete.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p]
         L.dfb_wq_pad_words.restype = c_int
         L.dfb_wq_pad_words.argtypes = [ctypes.c_uint]
         L.dfb_gather_batch.restype = c_int

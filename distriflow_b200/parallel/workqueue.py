@@ -59,9 +59,11 @@ class DeviceWorkQueue:
         b, e = (int(v) & 0xFFFFFFFF for v in t.tolist())
         return Ticket(b if b != _DONE else -1, e, b == _DONE, t)
 
-    def complete(self, ticket: Optional[Ticket] = None) -> None:
+    def complete(self, ticket: Optional[Ticket] = None, accepted: Optional[torch.Tensor] = None) -> None:
+        """Mark the batch complete.  `accepted` (device uint32) makes it conditional: a batch whose gradient was refused by
+        the staleness guard stays incomplete and is re-issued, like a dropped upload on the host server."""
         t = self.ticket if ticket is None or ticket.dev is None else ticket.dev
-        check(self.L.dfb_wq_complete(self.home_pad, ptr(t), _lib.stream()), "dfb_wq_complete")
+        check(self.L.dfb_wq_complete(self.home_pad, ptr(t), ptr(accepted), _lib.stream()), "dfb_wq_complete")
 
     def gather(self, data: torch.Tensor, batch_size: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Rows of the batch named by the last ticket, straight from the device-resident `data` (no host index)."""

@@ -129,7 +129,7 @@ int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, void* strea
 /* device work queue (dataset.ts:43-67) */
 int dfb_wq_init(unsigned* pad, unsigned batches, unsigned epochs, void* stream);
 int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, void* stream);
-int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, void* stream);
+int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, const unsigned* accepted /* nullable */, void* stream);
 int dfb_wq_pad_words(unsigned batches);
 int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                      void* stream);

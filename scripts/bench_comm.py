@@ -88,7 +88,8 @@ def main():
         t_o, t_n = timeit(ours), timeit(nccl)
         nbytes = n * 2
         bus = lambda t: 2.0 * (world - 1) / world * nbytes / (t * 1e-3) / 1e9      # noqa: E731
-        link_bytes = (world - 1) / world * nbytes                                   # per direction per GPU (pull in, push out)
+        # per direction per GPU: inbound = the slices this rank pulls (N-1)/N*S + the weights the peers push into it (N-1)/N*S
+        link_bytes = 2.0 * (world - 1) / world * nbytes
         roof_ms = link_bytes / (LINK_GBS * 1e9) * 1e3
         row = {"bucket_mb": mb, "world": world, "opt": a.opt, "ours_us": round(t_o * 1e3, 1), "nccl_plus_opt_us": round(t_n * 1e3, 1),
                "ours_bus_gbs": round(bus(t_o), 1), "nccl_bus_gbs": round(bus(t_n), 1), "speedup": round(t_n / t_o, 2),
