@@ -114,3 +114,55 @@ def test_async_engine_invariants_two_gpus(tmp_path):
         assert c["applied"] + c["dropped"] == world * res["steps"], c
         assert c["version"] == c["applied"] and c["inflight"] == [0, 0] and c["arrived"] == [0, 0]
         assert c["max_staleness_seen"] <= 4
+
+
+def _stress_worker(rank, world, port, out):
+    """Cross-GPU signalling stress: many small buckets back to back, random per-rank delays before each launch, a
+    sequence-numbered audit of every result."""
+    import random
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from distriflow_b200.ops import _lib
+    from distriflow_b200.ops._lib import check, ptr
+    from distriflow_b200.parallel.engine import _comm_sigs
+    from distriflow_b200.parallel.symm import SymmetricHeap
+    L = _comm_sigs()
+    n = 64 * 64 * world
+    shard = n // world
+    heap = SymmetricHeap(n * 8 + 65536, rank, world, None, dev)
+    go, po = heap.alloc(n * 4), heap.alloc(n * 4)
+    g = heap.view(go, (n,), torch.float32)
+    p = heap.view(po, (n,), torch.float32)
+    master = torch.zeros(shard, device=dev)
+    rng = random.Random(1234 + rank)
+    bad = 0
+    iters = 300
+    for it in range(1, iters + 1):
+        g.fill_(float(it * (rank + 1)))                      # gradient of rank r at iteration it = it * (r + 1)
+        if rng.random() < 0.5:
+            torch.cuda._sleep(rng.randint(1000, 400000))     # desynchronise the ranks on the device
+        check(L.dfb_sync_rs_opt_ag(heap.ptrs(go), heap.ptrs(po), heap.ptrs(0), ptr(master), None, None, None, n, shard, rank, world,
+                                   it, 1, 0, 0, 0, 1.0, 0.0, 0.9, 0.999, 1e-8, 0.0, it, 8, 0, 0, _lib.stream()), "sync")
+        # after the kernel every rank's full weight buffer must hold -sum_{j<=it} j * mean_r(r+1)
+        want = -(it * (it + 1) / 2) * (sum(range(1, world + 1)) / world)
+        bad += int((p != want).sum().item())
+    torch.cuda.synchronize()
+    res = torch.tensor([bad], device=dev)
+    dist.all_reduce(res)
+    if rank == 0:
+        torch.save({"bad": int(res), "iters": iters}, out)
+    dist.destroy_process_group()
+
+
+def test_sync_kernel_signalling_stress(tmp_path):
+    import torch.multiprocessing as mp
+    world = 2
+    if torch.cuda.device_count() < world:
+        pytest.skip("not enough GPUs")
+    out = str(tmp_path / "res.pt")
+    mp.spawn(_stress_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    res = torch.load(out)
+    assert res["bad"] == 0, res
