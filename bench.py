@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--comm-ctas", type=int, default=148)
     ap.add_argument("--reserve-sms", type=int, default=0)
+    ap.add_argument("--graph", action="store_true", help="capture the step into a CUDA graph (launch-bound models)")
     return ap.parse_args()
 
 
@@ -163,7 +164,8 @@ def main():
             from distriflow_b200.parallel.engine import DataParallelEngine
             engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
                                                          "bucketBytes": int(args.bucket_mb * (1 << 20)),
-                                                         "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms},
+                                                         "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
+                                                         "cudaGraph": args.graph},
                                         rank=rank, world=world, device=device)
         step = engine.step
     else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)

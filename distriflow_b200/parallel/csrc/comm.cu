@@ -115,13 +115,24 @@ struct SyncArgs {
   uint32_t epoch;        // barrier generation, strictly increasing per launch; 0 = no cross-rank barriers (emulation)
   int push;              // 1 = push refreshed weights to every rank, 0 = only write the local copy
   long nopush_lo, nopush_hi;   // bucket-relative element range that is NOT pushed (its all-gather is fused into the consumer GEMM)
+  // CUDA-graph replay support: values that change from step to step are read from device memory instead of being baked in
+  const uint32_t* epoch_base;  // if set (and epoch != 0): barrier generation = *epoch_base + epoch
+  const int* step_ptr;         // if set: optimizer step count for Adam's bias correction
   OptParams opt;
 };
 
 template <typename TG, typename TP, int R_T>
 __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {   // 256 x <=128 regs: shares an SM with a GEMM CTA
   const int R = R_T > 0 ? R_T : a.R;
-  if (a.epoch) rank_barrier(a.sig, a.rank, R, kSigIn, a.epoch, blockIdx.x == 0);   // everybody's gradients are final
+  uint32_t epoch = a.epoch;
+  if (epoch && a.epoch_base) epoch += *a.epoch_base;
+  OptParams opt = a.opt;
+  if (a.step_ptr != nullptr && opt.kind == OPT_ADAM) {
+    const float t = (float)max(*a.step_ptr, 1);
+    opt.bias_c1 = 1.f - powf(opt.beta1, t);
+    opt.bias_c2 = 1.f - powf(opt.beta2, t);
+  }
+  if (epoch) rank_barrier(a.sig, a.rank, R, kSigIn, epoch, blockIdx.x == 0);   // everybody's gradients are final
   using VG = Vec16<TG>;
   constexpr int VN = 8;                       // elements per vector (16 B of bf16, or 2 x 16 B of fp32)
   constexpr int GV = VN / VG::kN;             // 16-byte loads per peer per vector
@@ -175,27 +186,27 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
         w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
       }
       float mm[VN], vv[VN];
-      if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
+      if (opt.kind == OPT_MOMENTUM || opt.kind == OPT_ADAM) {
         const float4 m0 = *reinterpret_cast<const float4*>(a.m + s), m1 = *reinterpret_cast<const float4*>(a.m + s + 4);
         mm[0] = m0.x; mm[1] = m0.y; mm[2] = m0.z; mm[3] = m0.w; mm[4] = m1.x; mm[5] = m1.y; mm[6] = m1.z; mm[7] = m1.w;
       }
-      if (a.opt.kind == OPT_ADAM) {
+      if (opt.kind == OPT_ADAM) {
         const float4 v0 = *reinterpret_cast<const float4*>(a.v + s), v1 = *reinterpret_cast<const float4*>(a.v + s + 4);
         vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
       }
 #pragma unroll
       for (int j = 0; j < VN; ++j) {
         acc[j] *= inv_r;
-        w[j] = opt_step(w[j], acc[j], &mm[j], &vv[j], a.opt);
+        w[j] = opt_step(w[j], acc[j], &mm[j], &vv[j], opt);
       }
-      if (a.opt.kind != OPT_NONE) {
+      if (opt.kind != OPT_NONE) {
         *reinterpret_cast<float4*>(a.master + s) = make_float4(w[0], w[1], w[2], w[3]);
         *reinterpret_cast<float4*>(a.master + s + 4) = make_float4(w[4], w[5], w[6], w[7]);
-        if (a.opt.kind == OPT_MOMENTUM || a.opt.kind == OPT_ADAM) {
+        if (opt.kind == OPT_MOMENTUM || opt.kind == OPT_ADAM) {
           *reinterpret_cast<float4*>(a.m + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
           *reinterpret_cast<float4*>(a.m + s + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
         }
-        if (a.opt.kind == OPT_ADAM) {
+        if (opt.kind == OPT_ADAM) {
           *reinterpret_cast<float4*>(a.v + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
           *reinterpret_cast<float4*>(a.v + s + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
         }
@@ -209,7 +220,7 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
           reinterpret_cast<uint4*>(reinterpret_cast<TG*>(a.reduced_out) + s)[h] = o[h].raw;
         }
       }
-      if (a.opt.kind != OPT_NONE) {
+      if (opt.kind != OPT_NONE) {
         using VP = Vec16<TP>;
         constexpr int PV = VN / VP::kN;
         VP o[PV];
@@ -229,7 +240,7 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
       }
     }
   }
-  if (a.epoch) {
+  if (epoch) {
     // all blocks done -> the last one publishes "my slice is everywhere" and waits for everybody else's
     __shared__ bool last;
     __threadfence_system();
@@ -240,7 +251,7 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
       if (last) *cnt = 0;
     }
     __syncthreads();
-    if (last) rank_barrier(a.sig, a.rank, R, kSigOut, a.epoch, true);
+    if (last) rank_barrier(a.sig, a.rank, R, kSigOut, epoch, true);
   }
 }
 
@@ -602,10 +613,11 @@ static void fill_peers(PeerPtrs& d, void* const* src, int R) {
 // Fused reduce-scatter + 1/R + optimizer + all-gather for one bucket.  grads/params/sig: arrays of R base pointers
 // (peer-mapped).  master/m/v: local fp32 slices.  grad_dtype/param_dtype: DT_*.  epoch = 0 disables the cross-rank
 // barriers (single-GPU emulation: launch once per rank, in any order, gradients must already be final).
-DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
-                               void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
-                               int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
-                               float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, cudaStream_t stream) {
+static int sync_impl(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
+                     void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
+                     int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
+                     float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, const unsigned* epoch_base,
+                     const int* step_ptr, cudaStream_t stream) {
   DFB_REQUIRE(R >= 1 && R <= kMaxRanks && rank >= 0 && rank < R, "sync: bad rank %d / world %d", rank, R);
   DFB_REQUIRE(shard > 0 && (shard % 8) == 0, "sync: shard must be a positive multiple of 8 elements");
   DFB_REQUIRE(shard * R >= n, "sync: shard * R must cover the bucket");
@@ -616,7 +628,7 @@ DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* co
   if (sig) fill_peers(a.sig, sig, R); else memset(&a.sig, 0, sizeof(a.sig));
   DFB_REQUIRE(epoch == 0 || sig != nullptr, "sync: barriers need signal pads");
   a.master = master; a.m = m; a.v = v; a.reduced_out = reduced_out; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
-  a.epoch = epoch; a.push = push; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi;
+  a.epoch = epoch; a.push = push; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi; a.epoch_base = epoch_base; a.step_ptr = step_ptr;
   a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
   a.opt.weight_decay = weight_decay;
   a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));
@@ -647,6 +659,25 @@ DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* co
 #undef DFB_SYNC_LAUNCH
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
+                               void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
+                               int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
+                               float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, cudaStream_t stream) {
+  return sync_impl(grads, params, sig, master, m, v, reduced_out, n, shard, rank, R, epoch, push, grad_dtype, param_dtype, opt_kind,
+                   lr, momentum, beta1, beta2, eps, weight_decay, step, ctas, nopush_lo, nopush_hi, nullptr, nullptr, stream);
+}
+
+// Same kernel for CUDA-graph replay: the barrier generation is *epoch_base + epoch and Adam's step count is *step_ptr, both
+// read on the device at run time, so one captured launch stays valid for every later step.
+DFB_API int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* params, void* const* sig, float* master, float* m,
+                                          float* v, long n, long shard, int rank, int R, unsigned epoch, int grad_dtype,
+                                          int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2,
+                                          float eps, float weight_decay, int ctas, long nopush_lo, long nopush_hi,
+                                          const unsigned* epoch_base, const int* step_ptr, cudaStream_t stream) {
+  return sync_impl(grads, params, sig, master, m, v, nullptr, n, shard, rank, R, epoch, 1, grad_dtype, param_dtype, opt_kind, lr,
+                   momentum, beta1, beta2, eps, weight_decay, 1, ctas, nopush_lo, nopush_hi, epoch_base, step_ptr, stream);
 }
 
 DFB_API int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R,

@@ -83,6 +83,11 @@ class DataParallelEngine:
                 self.fuse_allgather(w)
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.device)
+        self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.backend == "p2p"
+        self._graph, self._static_in, self._static_loss, self._warm, self._capturing, self._seq = None, None, None, 0, False, 0
+        if self._graph_mode:
+            self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
 
     # ------------------------------------------------------------------------------------ setup
     def _build_buckets(self, heap) -> None:
@@ -195,8 +200,39 @@ class DataParallelEngine:
             b.launched = False
 
     def step(self, *batch: Any) -> torch.Tensor:
-        """One synchronous data-parallel step: forward, backward (+ overlapped bucket collectives), new version."""
+        """One synchronous data-parallel step: forward, backward (+ overlapped bucket collectives), new version.
+
+        With `cudaGraph: True` the first steps run eagerly (warm-up), then the whole step — forward, backward, the fused
+        bucket kernels on the side stream — is captured once into a CUDA graph and replayed; launch-bound models (MNIST,
+        ResNet-20) then run at device speed.  Inputs must keep their shapes; the learning rate is baked into the graph."""
+        if not self._graph_mode:
+            return self._step_body(*batch)
+        if self._graph is None:
+            if self._warm < 3:
+                self._warm += 1
+                return self._step_body(*batch)
+            self._static_in = [t.clone() if isinstance(t, torch.Tensor) else t for t in batch]
+            torch.cuda.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            self._capturing = True
+            with torch.cuda.graph(self._graph):
+                self._static_loss = self._step_body(*self._static_in, _count=False)
+            self._capturing = False
+        for dst, src in zip(self._static_in, batch):
+            if isinstance(dst, torch.Tensor):
+                dst.copy_(src, non_blocking=True)
+        self._graph.replay()
+        old = self.version
+        self.version += 1
+        for cb in self.versionCallbacks:
+            cb(old, self.version)
+        return self._static_loss
+
+    def _step_body(self, *batch: Any, _count: bool = True) -> torch.Tensor:
         self.zero_pending()
+        self._seq = 0
+        if self._graph_mode:
+            self._step_dev.add_(1)
         if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"] and self.reserve_sms:
             from ..ops import dense as _lin
             _lin.set_max_ctas(_lin.NUM_SMS - self.reserve_sms)  # optionally leave SMs free for the collective kernels
@@ -209,10 +245,13 @@ class DataParallelEngine:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
             from ..ops import dense as _lin
             _lin.set_max_ctas(0)
-        old = self.version
-        self.version += 1
-        for cb in self.versionCallbacks:
-            cb(old, self.version)
+        if self._graph_mode and self.world > 1:
+            self._epoch_dev.add_(len(self.buckets))            # next step's barrier generations start after this step's
+        if _count:
+            old = self.version
+            self.version += 1
+            for cb in self.versionCallbacks:
+                cb(old, self.version)
         return loss.detach()
 
     def _launch_bucket(self, b: Bucket) -> None:
@@ -228,11 +267,23 @@ class DataParallelEngine:
         L = _comm_sigs()
         main = torch.cuda.current_stream()
         self.comm_stream.wait_stream(main)
+        c = self.cfg
+        if self._graph_mode:          # replayable launch: generation and step count are read from device memory
+            self._seq += 1
+            with torch.cuda.stream(self.comm_stream):
+                check(L.dfb_sync_rs_opt_ag_replayable(self.heap.ptrs(b.grad_off), self.heap.ptrs(b.param_off), self.heap.ptrs(0),
+                                                      ptr(b.master), ptr(b.m), ptr(b.v), b.numel, b.shard, self.rank, self.world,
+                                                      self._seq if self.world > 1 else 0, dt(b.grad_buf), dt(b.param_buf),
+                                                      _OPT[c["optimizer"]], self.lr, c["momentum"], c["beta1"], c["beta2"], c["eps"],
+                                                      c["weightDecay"], self.comm_ctas if self.world > 1 else 148 * 4, b.nopush[0],
+                                                      b.nopush[1], ptr(self._epoch_dev), ptr(self._step_dev), _lib.stream()),
+                      "dfb_sync_rs_opt_ag_replayable")
+            self._launches += 1
+            return
         epoch = 0
         if self.world > 1:
             self._epoch += 1
             epoch = self._epoch
-        c = self.cfg
         with torch.cuda.stream(self.comm_stream):
             check(L.dfb_sync_rs_opt_ag(self.heap.ptrs(b.grad_off), self.heap.ptrs(b.param_off), self.heap.ptrs(0),
                                        ptr(b.master), ptr(b.m), ptr(b.v), None, b.numel, b.shard, self.rank, self.world,
@@ -320,6 +371,10 @@ def _comm_sigs():
         L.dfb_sync_rs_opt_ag.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int,
                                          c_int, ctypes.c_uint, c_int, c_int, c_int, c_int, c_float, c_float, c_float, c_float,
                                          c_float, c_float, c_int, c_int, ctypes.c_long, ctypes.c_long, c_void_p]
+        L.dfb_sync_rs_opt_ag_replayable.restype = c_int
+        L.dfb_sync_rs_opt_ag_replayable.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
+                                                    ctypes.c_uint, c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_float,
+                                                    c_float, c_int, ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p]
         L.dfb_allgather_push.restype = c_int
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int

@@ -113,6 +113,11 @@ int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig
                        void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
                        int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
                        float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, void* stream);
+/* replayable form for CUDA graphs: barrier generation = *epoch_base + epoch, Adam step = *step_ptr (device memory) */
+int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
+                                  long n, long shard, int rank, int R, unsigned epoch, int grad_dtype, int param_dtype, int opt_kind,
+                                  float lr, float momentum, float beta1, float beta2, float eps, float weight_decay, int ctas,
+                                  long nopush_lo, long nopush_hi, const unsigned* epoch_base, const int* step_ptr, void* stream);
 int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
                        int ctas, void* stream);
 int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
