@@ -25,18 +25,19 @@ def _sync_worker(rank, world, port, out):
     from distriflow_b200.parallel.engine import DataParallelEngine
     cfg = GPT2Config.tiny()
     res = {}
-    for backend in ("p2p", "nccl"):
+    for backend in ("p2p", "nccl", "p2p-graph"):
         torch.manual_seed(0)
         model = GPT2(cfg).to(dev)
         eng = DataParallelEngine(model, gpt2_loss, {"optimizer": "adam", "learningRate": 1e-3, "bucketBytes": 1 << 18,
-                                                    "backend": backend}, rank=rank, world=world, device=dev)
+                                                    "backend": backend.split("-")[0], "cudaGraph": backend.endswith("graph")},
+                                 rank=rank, world=world, device=dev)
         g = torch.Generator().manual_seed(100 + rank)            # different data per rank
         losses = []
         idx = torch.randint(0, cfg.vocab_size, (4, 65), generator=g).to(dev)     # one fixed batch per rank: loss must fall
         for _ in range(6):
             losses.append(float(eng.step(idx[:, :-1].contiguous(), idx[:, 1:].contiguous())))
         torch.cuda.synchronize()
-        if backend == "p2p":
+        if backend.startswith("p2p"):
             with torch.no_grad():                      # one more forward: the fused all-gather GEMM refreshes its kernel
                 gpt2_loss(model, idx[:, :-1].contiguous(), idx[:, 1:].contiguous())
             torch.cuda.synchronize()
@@ -69,6 +70,8 @@ def test_sync_engine_p2p_matches_nccl(world, tmp_path):
     assert max(abs(a - b) for a, b in zip(lp, ln)) < 5e-2, (lp, ln)
     assert float((wp - wn).abs().max()) < 2e-2          # bf16 gradients: fp32 pull-reduce vs NCCL's bf16 ring
     assert res["fused"] and res["working_equals_master"], "a rank's working weights differ from the gathered masters"
+    lg, wg = res["p2p-graph"]                                # same engine replayed from a CUDA graph (cross-rank barriers inside)
+    assert res["p2p-graph_same"] and max(abs(a - b) for a, b in zip(lp, lg)) < 2e-2 and float((wp - wg).abs().max()) < 1e-2
 
 
 def _async_worker(rank, world, port, out):
