@@ -215,13 +215,19 @@ class DataParallelEngine:
             torch.cuda.synchronize()
             self._graph = torch.cuda.CUDAGraph()
             self._capturing = True
+            from ..ops import _lib
+            n0 = _lib.LAUNCHES[0]
             with torch.cuda.graph(self._graph):
                 self._static_loss = self._step_body(*self._static_in, _count=False)
+            self._graph_native = _lib.LAUNCHES[0] - n0        # native kernels recorded in the graph (none ran during capture)
+            _lib.LAUNCHES[0] = n0
             self._capturing = False
         for dst, src in zip(self._static_in, batch):
             if isinstance(dst, torch.Tensor):
                 dst.copy_(src, non_blocking=True)
         self._graph.replay()
+        from ..ops import _lib
+        _lib.LAUNCHES[0] += self._graph_native                # each replay launches every native kernel node of the graph
         old = self.version
         self.version += 1
         for cb in self.versionCallbacks:
