@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--reserve-sms", type=int, default=0)
     ap.add_argument("--graph", dest="graph", action="store_true", default=True,
                     help="capture the whole step into a CUDA graph after 3 eager steps (default)")
+    ap.add_argument("--nvls", action="store_true", help="reduce gradients / broadcast weights inside the NVSwitch (multicast heap)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches every step")
     return ap.parse_args()
 
@@ -167,7 +168,7 @@ def main():
             engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
                                                          "bucketBytes": int(args.bucket_mb * (1 << 20)),
                                                          "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
-                                                         "cudaGraph": args.graph},
+                                                         "cudaGraph": args.graph, "nvls": bool(args.nvls and world > 1)},
                                         rank=rank, world=world, device=device)
         step = engine.step
     else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)
@@ -240,7 +241,7 @@ def main():
                "impl": args.impl,
                "config": {**wcfg, "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
                           "optimizer": args.optimizer, "bucket_mb": args.bucket_mb,
-                          "cuda_graph": bool(prep), "graph_prep_steps": prep,
+                          "cuda_graph": bool(prep), "nvls": bool(args.nvls and world > 1), "graph_prep_steps": prep,
                           "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
                           "loss": float(loss)},
                "clocks": clocks, "gpu_launches": int(launches)}

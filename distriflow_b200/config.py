@@ -79,6 +79,7 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "backend": "p2p",             # "p2p" (own kernels) | "nccl" (baseline) | "gloo" (CPU plumbing)
     "fuseAllGather": True,        # all-gather fused into the first consuming GEMM
     "commCtas": 148,              # CTAs of the fused collective kernel (256 threads x <= 128 regs: co-resides with a GEMM CTA)
+    "nvls": False,                # gradients reduced and weights broadcast inside the NVSwitch (multicast heap; bf16 only)
     "cudaGraph": False,           # capture the whole step (forward, backward, bucket kernels) into a CUDA graph after warm-up
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
 }

@@ -255,6 +255,107 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
   }
 }
 
+// ---------------------------------------------------------------- sync over NVLS: the switch reduces and broadcasts
+// Same contract as sync_rs_opt_ag_kernel for bf16 gradients and bf16 working weights, with the two transfers handed to the
+// NVSwitch through a multicast mapping of the symmetric heap: ONE `multimem.ld_reduce` per 16 bytes returns the sum of
+// all R ranks' gradients (added inside the switch with fp32 accumulation, delivered rounded to bf16), and ONE `multimem.st`
+// writes the refreshed weights to all R ranks.  Per GPU the link then carries S/R in and S/R out per bucket instead of
+// (R-1)/R x S each way.  Barriers stay on the unicast signal pads.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+struct NvlsArgs {
+  SyncArgs s;                      // grads unused; params = unicast bases (local / no-push stores)
+  const __nv_bfloat16* mc_grads;   // multicast address of this bucket's gradient buffer
+  __nv_bfloat16* mc_params;        // multicast address of this bucket's working-weight buffer
+};
+
+__global__ void __launch_bounds__(256) sync_nvls_kernel(const NvlsArgs na) {
+  const SyncArgs& a = na.s;
+  const int R = a.R;
+  uint32_t epoch = a.epoch;
+  if (epoch && a.epoch_base) epoch += *a.epoch_base;
+  OptParams opt = a.opt;
+  if (a.step_ptr != nullptr && opt.kind == OPT_ADAM) {
+    const float t = (float)max(*a.step_ptr, 1);
+    opt.bias_c1 = 1.f - powf(opt.beta1, t);
+    opt.bias_c2 = 1.f - powf(opt.beta2, t);
+  }
+  rank_barrier(a.sig, a.rank, R, kSigIn, epoch, blockIdx.x == 0);
+  using V = Vec16<__nv_bfloat16>;
+  constexpr int VN = 8, U = 4;
+  const long lo = (long)a.rank * a.shard;
+  const long hi = min(a.n, lo + a.shard);
+  const long nvec = hi > lo ? (hi - lo + VN - 1) / VN : 0;
+  const float inv_r = 1.f / (float)R;
+  const long stride = (long)gridDim.x * blockDim.x;
+  for (long i0 = blockIdx.x * (long)blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * U) {
+    V g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * stride;
+      if (i < nvec) g[u].raw = multimem_ld_reduce_bf16x8(na.mc_grads + lo + i * VN);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * stride;
+      if (i >= nvec) continue;
+      const long e = lo + i * VN, s = i * VN;
+      float w[VN], mm[VN], vv[VN];
+      {
+        const float4 w0 = *reinterpret_cast<const float4*>(a.master + s), w1 = *reinterpret_cast<const float4*>(a.master + s + 4);
+        w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+      }
+      if (opt.kind == OPT_MOMENTUM || opt.kind == OPT_ADAM) {
+        const float4 m0 = *reinterpret_cast<const float4*>(a.m + s), m1 = *reinterpret_cast<const float4*>(a.m + s + 4);
+        mm[0] = m0.x; mm[1] = m0.y; mm[2] = m0.z; mm[3] = m0.w; mm[4] = m1.x; mm[5] = m1.y; mm[6] = m1.z; mm[7] = m1.w;
+      }
+      if (opt.kind == OPT_ADAM) {
+        const float4 v0 = *reinterpret_cast<const float4*>(a.v + s), v1 = *reinterpret_cast<const float4*>(a.v + s + 4);
+        vv[0] = v0.x; vv[1] = v0.y; vv[2] = v0.z; vv[3] = v0.w; vv[4] = v1.x; vv[5] = v1.y; vv[6] = v1.z; vv[7] = v1.w;
+      }
+      V o;
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        w[j] = opt_step(w[j], g[u].get(j) * inv_r, &mm[j], &vv[j], opt);
+        o.set(j, w[j]);
+      }
+      *reinterpret_cast<float4*>(a.master + s) = make_float4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<float4*>(a.master + s + 4) = make_float4(w[4], w[5], w[6], w[7]);
+      if (opt.kind == OPT_MOMENTUM || opt.kind == OPT_ADAM) {
+        *reinterpret_cast<float4*>(a.m + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(a.m + s + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+      }
+      if (opt.kind == OPT_ADAM) {
+        *reinterpret_cast<float4*>(a.v + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(a.v + s + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+      }
+      if (e >= a.nopush_lo && e < a.nopush_hi)       // gathered by the consumer GEMM: only the owner's copy is written
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.params.p[a.rank]) + e) = o.raw;
+      else
+        multimem_st_v4(na.mc_params + e, o.raw);
+    }
+  }
+  __shared__ bool last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(a.sig.p[a.rank]) + kSigBlocks;
+    last = (atomicAdd(cnt, 1u) == gridDim.x - 1);
+    if (last) *cnt = 0;
+  }
+  __syncthreads();
+  if (last) rank_barrier(a.sig, a.rank, R, kSigOut, epoch, true);
+}
+
 // ---------------------------------------------------------------- standalone all-gather (push own shard to everybody)
 struct GatherArgs {
   PeerPtrs bufs;
@@ -678,6 +779,41 @@ DFB_API int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* param
                                           const unsigned* epoch_base, const int* step_ptr, cudaStream_t stream) {
   return sync_impl(grads, params, sig, master, m, v, nullptr, n, shard, rank, R, epoch, 1, grad_dtype, param_dtype, opt_kind, lr,
                    momentum, beta1, beta2, eps, weight_decay, 1, ctas, nopush_lo, nopush_hi, epoch_base, step_ptr, stream);
+}
+
+// NVLS variant (bf16 gradients and weights; `mc_grads` / `mc_params`: multicast addresses of the bucket's buffers, from
+// dfb_mc_bind_map; `params`: unicast bases for the ranges that are not pushed).  epoch_base / step_ptr may be null
+// (eager launches) or device words (CUDA-graph replay), as in dfb_sync_rs_opt_ag_replayable.
+DFB_API int dfb_sync_nvls(const void* mc_grads, void* mc_params, void* const* params, void* const* sig, float* master, float* m,
+                          float* v, long n, long shard, int rank, int R, unsigned epoch, int opt_kind, float lr, float momentum,
+                          float beta1, float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo,
+                          long nopush_hi, const unsigned* epoch_base, const int* step_ptr, cudaStream_t stream) {
+  DFB_REQUIRE(R >= 2 && R <= kMaxRanks && rank >= 0 && rank < R, "nvls: bad rank %d / world %d", rank, R);
+  DFB_REQUIRE(shard > 0 && (shard % 8) == 0 && shard * R >= n, "nvls: shard must be a multiple of 8 elements and cover the bucket");
+  DFB_REQUIRE(mc_grads != nullptr && mc_params != nullptr && sig != nullptr && epoch != 0, "nvls: multicast addresses, signal pads and a barrier generation are required");
+  DFB_REQUIRE(opt_kind >= 0 && opt_kind <= 2, "nvls: optimizer kind");
+  DFB_REQUIRE(opt_kind == OPT_SGD || m != nullptr, "nvls: optimizer state missing");
+  DFB_REQUIRE(opt_kind != OPT_ADAM || v != nullptr, "nvls: Adam second moment missing");
+  NvlsArgs na;
+  SyncArgs& a = na.s;
+  memset(&a.grads, 0, sizeof(a.grads));
+  fill_peers(a.params, params, R);
+  fill_peers(a.sig, sig, R);
+  a.master = master; a.m = m; a.v = v; a.reduced_out = nullptr; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
+  a.epoch = epoch; a.push = 1; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi; a.epoch_base = epoch_base; a.step_ptr = step_ptr;
+  a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
+  a.opt.weight_decay = weight_decay;
+  a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));
+  a.opt.bias_c2 = 1.f - powf(beta2, (float)(step < 1 ? 1 : step));
+  na.mc_grads = reinterpret_cast<const __nv_bfloat16*>(mc_grads);
+  na.mc_params = reinterpret_cast<__nv_bfloat16*>(mc_params);
+  const long lo = (long)rank * shard, hi = lo + shard < n ? lo + shard : n;
+  long need = hi > lo ? ((hi - lo + 7) / 8 + 255) / 256 : 1;
+  int grid = ctas > 0 ? ctas : 64;
+  if (grid > need) grid = (int)need;
+  sync_nvls_kernel<<<grid, 256, 0, stream>>>(na);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
 }
 
 DFB_API int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R,

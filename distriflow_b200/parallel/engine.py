@@ -71,6 +71,14 @@ class DataParallelEngine:
         self.maximumStaleness = int(self.cfg["maximumStaleness"])
         self.comm_ctas = int(self.cfg["commCtas"])
         self.reserve_sms = int(self.cfg["reserveSMs"])
+        self.nvls = False
+        if self.cfg["nvls"] and self.world > 1 and self.backend == "p2p":
+            from .symm import multicast_supported
+            if self.param_dtype != torch.bfloat16 or self.grad_dtype != torch.bfloat16:
+                raise ValueError("nvls: the in-switch reduction path takes bf16 gradients and bf16 working weights")
+            if not multicast_supported(self.device):
+                raise RuntimeError("nvls requested but this device cannot join an NVSwitch multicast object")
+            self.nvls = True
         self._epoch = 0
         self._launches = 0                  # own-kernel launches issued by the engine (comm/optimizer kernels)
         self.versionCallbacks: List[Callable[[int, int], None]] = []
@@ -121,7 +129,9 @@ class DataParallelEngine:
         self.heap = None
         if self.backend == "p2p":
             from .symm import SymmetricHeap
-            self.heap = heap or SymmetricHeap(total + 4096, self.rank, self.world, self.group, self.device)
+            self.heap = heap or SymmetricHeap(total + 4096, self.rank, self.world, self.group, self.device, multicast=self.nvls)
+            if self.nvls and not self.heap.mc_base:
+                raise RuntimeError("nvls: the supplied symmetric heap has no multicast mapping")
         for b in buckets:
             flat32 = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
             for p, off in zip(b.params, b.offsets):
@@ -274,6 +284,23 @@ class DataParallelEngine:
         main = torch.cuda.current_stream()
         self.comm_stream.wait_stream(main)
         c = self.cfg
+        if self.nvls:                 # the switch reduces the gradients and broadcasts the weights (multimem.ld_reduce / .st)
+            graph = self._graph_mode
+            if graph:
+                self._seq += 1
+                epoch = self._seq
+            else:
+                self._epoch += 1
+                epoch = self._epoch
+            with torch.cuda.stream(self.comm_stream):
+                check(L.dfb_sync_nvls(self.heap.mc_ptr(b.grad_off), self.heap.mc_ptr(b.param_off), self.heap.ptrs(b.param_off),
+                                      self.heap.ptrs(0), ptr(b.master), ptr(b.m), ptr(b.v), b.numel, b.shard, self.rank, self.world,
+                                      epoch, _OPT[c["optimizer"]], self.lr, c["momentum"], c["beta1"], c["beta2"], c["eps"],
+                                      c["weightDecay"], self.version + 1, self.comm_ctas, b.nopush[0], b.nopush[1],
+                                      ptr(self._epoch_dev) if graph else None, ptr(self._step_dev) if graph else None,
+                                      _lib.stream()), "dfb_sync_nvls")
+            self._launches += 1
+            return
         if self._graph_mode:          # replayable launch: generation and step count are read from device memory
             self._seq += 1
             with torch.cuda.stream(self.comm_stream):
@@ -381,6 +408,10 @@ def _comm_sigs():
         L.dfb_sync_rs_opt_ag_replayable.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
                                                     ctypes.c_uint, c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_float,
                                                     c_float, c_int, ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p]
+        L.dfb_sync_nvls.restype = c_int
+        L.dfb_sync_nvls.argtypes = [c_void_p, c_void_p, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
+                                    ctypes.c_uint, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int,
+                                    ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p]
         L.dfb_allgather_push.restype = c_int
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int

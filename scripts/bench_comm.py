@@ -29,16 +29,18 @@ def main():
     ap.add_argument("--ctas", type=int, default=64)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default="")
+    ap.add_argument("--nvls", action="store_true", help="also time the in-switch variant (multimem.ld_reduce / multimem.st)")
+    ap.add_argument("--sizes", default="", help="comma-separated bucket sizes in MB (default: the full sweep)")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     L = _comm_sigs()
-    sizes_mb = [0.03125, 0.25, 1, 4, 16, 32, 64, 256]
+    sizes_mb = [float(x) for x in a.sizes.split(",")] if a.sizes else [0.03125, 0.25, 1, 4, 16, 32, 64, 256]
     nbuf = 3
     max_elems = int(sizes_mb[-1] * (1 << 20)) // 2
-    heap = SymmetricHeap(nbuf * max_elems * 4 + (1 << 20), rank, world, None, dev)
+    heap = SymmetricHeap(nbuf * max_elems * 4 + (1 << 20), rank, world, None, dev, multicast=a.nvls)
     offs = [(heap.alloc(max_elems * 2), heap.alloc(max_elems * 2)) for _ in range(nbuf)]
     for go, po in offs:
         heap.view(go, (max_elems,), torch.bfloat16).normal_()
@@ -59,6 +61,13 @@ def main():
             check(L.dfb_sync_rs_opt_ag(heap.ptrs(go), heap.ptrs(po), heap.ptrs(0), ptr(master), ptr(m), ptr(v), None, n, shard, rank,
                                        world, epoch[0], 1, 1, 1, _OPT[a.opt], 1e-3, 0.9, 0.9, 0.999, 1e-8, 0.0, 1, a.ctas, 0, 0,
                                        _lib.stream()), "sync")
+
+        def nvls(i):
+            go, po = offs[i % nbuf]
+            epoch[0] += 1
+            check(L.dfb_sync_nvls(heap.mc_ptr(go), heap.mc_ptr(po), heap.ptrs(po), heap.ptrs(0), ptr(master), ptr(m), ptr(v), n, shard,
+                                  rank, world, epoch[0], _OPT[a.opt], 1e-3, 0.9, 0.9, 0.999, 1e-8, 0.0, 1, a.ctas, 0, 0, None, None,
+                                  _lib.stream()), "sync_nvls")
 
         gl = [torch.randn(n, device=dev).bfloat16() for _ in range(nbuf)]
         wl = [torch.randn(n, device=dev).bfloat16() for _ in range(nbuf)]
@@ -94,6 +103,11 @@ def main():
         row = {"bucket_mb": mb, "world": world, "opt": a.opt, "ours_us": round(t_o * 1e3, 1), "nccl_plus_opt_us": round(t_n * 1e3, 1),
                "ours_bus_gbs": round(bus(t_o), 1), "nccl_bus_gbs": round(bus(t_n), 1), "speedup": round(t_n / t_o, 2),
                "nvlink_roofline_frac": round(roof_ms / t_o, 3)}
+        if a.nvls:
+            t_v = timeit(nvls)
+            # in-switch: per GPU and direction the link carries S/N of reduced gradients in + (N-1)/N*S of pushed weights in
+            row.update({"nvls_us": round(t_v * 1e3, 1), "nvls_bus_gbs": round(bus(t_v), 1), "nvls_vs_p2p": round(t_o / t_v, 2),
+                        "nvls_vs_nccl": round(t_n / t_v, 2)})
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)

@@ -15,7 +15,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _sync_worker(rank, world, port, out):
+def _sync_worker(rank, world, port, out, variants=("p2p", "nccl", "p2p-graph")):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.cuda.set_device(rank)
@@ -25,11 +25,12 @@ def _sync_worker(rank, world, port, out):
     from distriflow_b200.parallel.engine import DataParallelEngine
     cfg = GPT2Config.tiny()
     res = {}
-    for backend in ("p2p", "nccl", "p2p-graph"):
+    for backend in variants:
         torch.manual_seed(0)
         model = GPT2(cfg).to(dev)
         eng = DataParallelEngine(model, gpt2_loss, {"optimizer": "adam", "learningRate": 1e-3, "bucketBytes": 1 << 18,
-                                                    "backend": backend.split("-")[0], "cudaGraph": backend.endswith("graph")},
+                                                    "backend": backend.split("-")[0], "cudaGraph": "graph" in backend.split("-"),
+                                                    "nvls": "nvls" in backend.split("-")},
                                  rank=rank, world=world, device=dev)
         g = torch.Generator().manual_seed(100 + rank)            # different data per rank
         losses = []
@@ -72,6 +73,29 @@ def test_sync_engine_p2p_matches_nccl(world, tmp_path):
     assert res["fused"] and res["working_equals_master"], "a rank's working weights differ from the gathered masters"
     lg, wg = res["p2p-graph"]                                # same engine replayed from a CUDA graph (cross-rank barriers inside)
     assert res["p2p-graph_same"] and max(abs(a - b) for a, b in zip(lp, lg)) < 2e-2 and float((wp - wg).abs().max()) < 1e-2
+
+
+def test_sync_engine_nvls_matches_p2p(tmp_path):
+    """Gradients reduced inside the NVSwitch (`multimem.ld_reduce`) and weights broadcast by it (`multimem.st`): same training
+    trajectory as the P2P pull/push kernel up to the bf16 rounding of the reduced gradient; eager and CUDA-graph replay."""
+    import torch.multiprocessing as mp
+    from distriflow_b200.parallel.symm import multicast_supported
+    world = 2
+    if torch.cuda.device_count() < world:
+        pytest.skip("not enough GPUs")
+    if not multicast_supported(torch.device("cuda", 0)):
+        pytest.skip("device does not support multicast objects")
+    out = str(tmp_path / "res.pt")
+    mp.spawn(_sync_worker, args=(world, _free_port(), out, ("p2p", "p2p-nvls", "p2p-nvls-graph")), nprocs=world, join=True)
+    res = torch.load(out)
+    lp, wp = res["p2p"]
+    for v in ("p2p-nvls", "p2p-nvls-graph"):
+        lv, wv = res[v]
+        assert res[v + "_same"], "replicas diverged"
+        assert lv[-1] < lv[0]
+        assert max(abs(a - b) for a, b in zip(lp, lv)) < 5e-2, (lp, lv)
+        assert float((wp - wv).abs().max()) < 2e-2
+    assert res["fused"] and res["working_equals_master"]
 
 
 def _async_worker(rank, world, port, out):
