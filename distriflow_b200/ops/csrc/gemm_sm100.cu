@@ -429,6 +429,8 @@ constexpr int k2Stages = 6;
 constexpr int k2StageBytes = kATileBytes + 128 * kBlockK * 2;         // 16 KiB A + 16 KiB B half
 constexpr int k2SmemBytes = k2Stages * k2StageBytes + 2 * kStageOutBytes + 256 + 1024;
 constexpr int k2TmemCols = 512;
+constexpr int k2EpiGroups = 2;                           // two groups of 4 epilogue warps, each drains half of the 256 columns
+constexpr int k2Threads = 64 + k2EpiGroups * kEpiThreads;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -467,10 +469,24 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t targ
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(remote) : "memory");
 }
 
-template <typename OutT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+// tcgen05.fence::before_thread_sync orders the warp's TMEM loads before this arrival; no generic-memory release is needed
+// (the .release form costs a MEMBAR per tile and epilogue warp: 20 % of the epilogue's stall samples in ncu).
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint64_t* bar, uint32_t target_cta) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(remote) : "r"(smem_u32(bar)), "r"(target_cta));
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(remote) : "memory");
+}
+
+// kAux: the epilogue also moves a second [M, N] bf16 tensor through TMA (aux_mode 1: stores the pre-activation next to the
+// activated output; aux_mode 2: loads it and multiplies the accumulator by gelu'(aux)).  That variant trades one pipeline
+// stage for a second 4 KiB staging slab per epilogue warp.
+template <typename OutT, bool kAux>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(k2Threads, 1)
 gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmX, const GemmParams p) {
+  constexpr int k2Stages = kAux ? dfb::k2Stages - 1 : dfb::k2Stages;
+  constexpr int kSlabBytes = 32 * 128;
+  constexpr int kOutBytes = (kAux ? 2 : 1) * 8 * kSlabBytes;
   constexpr int BLOCK_N = 256;
   constexpr int kChunkN = 128 / (int)sizeof(OutT);
   constexpr int kChunks = BLOCK_N / kChunkN;
@@ -481,11 +497,12 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + k2Stages * kATileBytes;
   uint8_t* smem_out = smem + k2Stages * k2StageBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + 2 * kStageOutBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + kOutBytes);
   uint64_t* empty_bar = full_bar + k2Stages;
   uint64_t* tmem_full = empty_bar + k2Stages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* aux_bar = tmem_empty + 2;                       // one per epilogue warp (aux_mode 2 loads)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(aux_bar + 8);
 
   const int warp_idx = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
@@ -508,8 +525,9 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 8);
+      mbar_init(&tmem_empty[i], 2 * 4 * k2EpiGroups);       // one arrival per epilogue warp of both CTAs
     }
+    for (int i = 0; i < 8; ++i) mbar_init(&aux_bar[i], 1);
     fence_mbar_init();
   }
   if (warp_idx == 1) {
@@ -596,20 +614,36 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       }
     }
   } else {
+    // warps 2-5 = group 0 (column chunks of the first half), warps 6-9 = group 1 (second half); a warp may only touch
+    // TMEM lanes 32 * (warp % 4) .. + 31, so both groups cover all 128 rows.  Every warp stages and TMA-stores its own
+    // 32-row slab: no barrier between epilogue warps, only __syncwarp.
     const int quarter = warp_idx & 3, row = quarter * 32 + lane;
-    const bool issuer = (threadIdx.x == 64);
+    const int group = (warp_idx - 2) >> 2;
+    constexpr int kGroupChunks = kChunks / k2EpiGroups;
+    uint8_t* const slab = smem_out + (warp_idx - 2) * ((kAux ? 2 : 1) * kSlabBytes);   // output staging
+    uint8_t* const slab_x = slab + kSlabBytes;                                          // aux staging (kAux only)
+    uint64_t* const my_aux_bar = &aux_bar[warp_idx - 2];
+    uint32_t aux_phase = 0;
+    const bool aux_store = kAux && p.aux_mode == 1, aux_load = kAux && p.aux_mode == 2;
+    auto issue_aux_load = [&](int tile, int c) {           // lane 0: fetch this warp's 32 x 64 slab of the aux tensor
+      int m_blk, n_blk, split;
+      decode_tile(tile, m_blk, n_blk, split);
+      mbar_expect_tx(my_aux_bar, kSlabBytes);
+      tma_load_2d(slab_x, &tmX, my_aux_bar, n_blk * BLOCK_N + c * kChunkN, m_blk * 256 + (int)cta * 128 + quarter * 32);
+    };
+    if (aux_load && pair < num_tiles && lane == 0) issue_aux_load(pair, group * kGroupChunks);
     int acc = 0;
-    uint32_t acc_phase = 0, out_iter = 0;
+    uint32_t acc_phase = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int m_blk, n_blk, split;
       decode_tile(tile, m_blk, n_blk, split);
       const int m0 = m_blk * 256 + (int)cta * 128, n0 = n_blk * BLOCK_N;
-      const int out_row0 = m0 + split * p.split_rows;
+      const int out_row0 = m0 + split * p.split_rows + quarter * 32;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BLOCK_N;
 #pragma unroll 1
-      for (int c = 0; c < kChunks; ++c) {
+      for (int c = group * kGroupChunks; c < (group + 1) * kGroupChunks; ++c) {
         float v[kChunkN];
         {
           uint32_t r0[32];
@@ -626,16 +660,52 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r0[j]);
         }
-        if (c == kChunks - 1) {                        // accumulator drained: tell the leader's MMA thread
+        if (c == (group + 1) * kGroupChunks - 1) {     // this warp's part of the accumulator is drained: tell the leader's MMA thread
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);
+          if (lane == 0) mbar_arrive_cluster_relaxed(&tmem_empty[acc], 0);
         }
-        uint8_t* stage_out = smem_out + (out_iter & 1) * kStageOutBytes;
-        if (issuer) tma_store_wait_read<1>();
-        named_bar_sync(1, kEpiThreads);
         if (p.bias != nullptr) add_bias_chunk<kChunkN>(v, p.bias, p.bias_dtype, n0 + c * kChunkN, p.N);
-        if constexpr (kChunkN == 64) epilogue_aux(v, p, m0 + row, n0 + c * kChunkN, p.M, p.N);
+        if constexpr (kAux && kChunkN == 64) {
+          if (aux_load) {                              // v *= gelu'(aux): the slab was fetched while the accumulator was computed
+            mbar_wait(my_aux_bar, aux_phase);
+            aux_phase ^= 1;
+            const uint8_t* xr = slab_x + lane * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint4 q = *reinterpret_cast<const uint4*>(xr + ((j ^ (lane & 7)) << 4));
+              const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&q);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[8 * j + i] *= gelu_tanh_grad(__bfloat162float(h[i]));
+            }
+            fence_proxy_async_smem();
+            __syncwarp();                              // everybody has read the slab: the next fetch may overwrite it
+            if (lane == 0) {
+              if (c + 1 < (group + 1) * kGroupChunks) issue_aux_load(tile, c + 1);
+              else if (tile + num_pairs < num_tiles) issue_aux_load(tile + num_pairs, group * kGroupChunks);
+            }
+          } else if (aux_store) {                      // pre-activation -> aux, through its own slab and TMA store
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+            uint8_t* xr = slab_x + lane * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * j + 0], v[8 * j + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+              uint4 q = {*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1), *reinterpret_cast<uint32_t*>(&h2),
+                         *reinterpret_cast<uint32_t*>(&h3)};
+              *reinterpret_cast<uint4*>(xr + ((j ^ (lane & 7)) << 4)) = q;
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmX, slab_x, n0 + c * kChunkN, m0 + quarter * 32);
+              tma_store_commit();
+            }
+          }
+        }
         if (p.act == ACT_RELU) {
 #pragma unroll
           for (int j = 0; j < kChunkN; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -643,7 +713,11 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
           for (int j = 0; j < kChunkN; ++j) v[j] = gelu_tanh(v[j]);
         }
-        uint8_t* row_ptr = stage_out + row * 128;
+        if (lane == 0) {                               // the previous store from the output slab has left it
+          if (aux_store) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
+        }
+        __syncwarp();
+        uint8_t* row_ptr = slab + lane * 128;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           uint4 q;
@@ -662,19 +736,18 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             q.z = __float_as_uint(v[4 * j + 2]);
             q.w = __float_as_uint(v[4 * j + 3]);
           }
-          *reinterpret_cast<uint4*>(row_ptr + ((j ^ (row & 7)) << 4)) = q;
+          *reinterpret_cast<uint4*>(row_ptr + ((j ^ (lane & 7)) << 4)) = q;
         }
         fence_proxy_async_smem();
-        named_bar_sync(1, kEpiThreads);
-        if (issuer) {
-          tma_store_2d(&tmD, stage_out, n0 + c * kChunkN, out_row0);
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmD, slab, n0 + c * kChunkN, out_row0);
           tma_store_commit();
         }
-        ++out_iter;
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (issuer) tma_store_wait<0>();
+    if (lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -686,10 +759,10 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   }
 }
 
-template <typename OutT>
+template <typename OutT, bool kAux = false>
 static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmD, const GemmParams& p, int max_ctas,
-                        cudaStream_t stream) {
-  auto kern = gemm2_tcgen05_kernel<OutT>;
+                        cudaStream_t stream, const CUtensorMap* tmX = nullptr) {
+  auto kern = gemm2_tcgen05_kernel<OutT, kAux>;
   static bool configured = false;
   if (!configured) {
     DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, k2SmemBytes));
@@ -700,7 +773,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   if (max_ctas > 0 && pairs > max_ctas / 2) pairs = max_ctas / 2;
   if (pairs > tiles) pairs = tiles;
   if (pairs < 1) pairs = 1;
-  kern<<<2 * pairs, kThreads, k2SmemBytes, stream>>>(tmA, tmB, tmD, p);
+  kern<<<2 * pairs, k2Threads, k2SmemBytes, stream>>>(tmA, tmB, tmD, tmX ? *tmX : tmD, p);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -833,7 +906,7 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, in
     pk.bias = nullptr; pk.act = ACT_NONE;
     uint64_t dims[2] = {(uint64_t)N, (uint64_t)splits * mpad};
     uint64_t str[1] = {(uint64_t)N * 4};
-    uint32_t box[2] = {32, 128};
+    uint32_t box[2] = {32, two_cta ? 32u : 128u};          // the 2-CTA kernel stores one 32-row slab per epilogue warp
     if (encode_tmap(&tmD, workspace, 1, 2, dims, str, box, nullptr, 1)) return 4;
     int rc = two_cta ? launch_gemm2<float>(tmA, tmB, tmD, pk, max_ctas, stream)
              : block_n == 256 ? launch_gemm<256, float>(tmA, tmB, tmD, pk, max_ctas, stream)
@@ -856,8 +929,16 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, in
     const int esz = out_dtype == DT_BF16 ? 2 : 4;
     uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
     uint64_t str[1] = {(uint64_t)ldd * esz};
-    uint32_t box[2] = {(uint32_t)(128 / esz), 128};
+    uint32_t box[2] = {(uint32_t)(128 / esz), two_cta ? 32u : 128u};
     if (encode_tmap(&tmD, D, out_dtype == DT_BF16 ? 0 : 1, 2, dims, str, box, nullptr, 1)) return 4;
+  }
+  if (two_cta && aux_mode != 0) {                          // the aux tensor travels through TMA like the output
+    CUtensorMap tmX;
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)aux_ld * 2};
+    uint32_t box[2] = {64, 32};
+    if (encode_tmap(&tmX, aux, 0, 2, dims, str, box, nullptr, 1)) return 4;
+    return launch_gemm2<__nv_bfloat16, true>(tmA, tmB, tmD, p, max_ctas, stream, &tmX);
   }
   if (two_cta)
     return out_dtype == DT_BF16 ? launch_gemm2<__nv_bfloat16>(tmA, tmB, tmD, p, max_ctas, stream)

@@ -327,8 +327,11 @@ def _wgrad(x2, dy2, weight, K, N, M):
     return gemm(x2, dy2, a_mn=True, b_mn=True, M=K, N=N, K=M, out_dtype=weight.dtype)
 
 
-FUSE_GELU = False        # measured on B200 (scripts/bench_aux.py): the aux epilogues make the GEMM epilogue-bound
-                         # (fwd 274 us vs 226 us, bwd 315 us vs 204 us at 32768x768x3072), so the separate kernels stay
+import os as _os
+
+# GELU in the GEMM epilogues (forward: pre-activation and activation stored in one pass; backward: gelu'(pre) multiplied into
+# the data-gradient).  `DFB_FUSE_GELU=0/1` overrides for A/B runs (scripts/bench_aux.py).
+FUSE_GELU = _os.environ.get("DFB_FUSE_GELU", "1") == "1"
 
 
 def mlp_cuda(x, w1, b1, w2, b2):

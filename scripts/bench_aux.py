@@ -20,3 +20,4 @@ print("fwd gemm only           us", t(lambda: gemm(x, w1, a_mn=False, b_mn=True,
 print("bwd fused (aux gelu')   us", t(lambda: gemm_aux(dy, w2, a_mn=False, b_mn=False, M=M, N=H, K=K, aux=pre, aux_mode=2)))
 print("bwd gemm + act kernel   us", t(lambda: act_op(gemm(dy, w2, a_mn=False, b_mn=False, M=M, N=H, K=K), pre, 1)))
 print("bwd gemm only           us", t(lambda: gemm(dy, w2, a_mn=False, b_mn=False, M=M, N=H, K=K)))
+print("fwd gemm, no bias       us", t(lambda: gemm(x, w1, a_mn=False, b_mn=True, M=M, N=H, K=K)))

@@ -21,6 +21,14 @@ for _ in range(2):
     gemm(dy, w, a_mn=False, b_mn=False, M=T, N=K, K=N)          # fc1 dgrad    (both K-major)
     gemm(x, dy, a_mn=True, b_mn=True, M=K, N=N, K=T)            # fc1 wgrad    (both MN-major)
     gemm(x, x, a_mn=True, b_mn=True, M=K, N=K, K=T)             # proj wgrad   (split-K + reduce)
+# Dense layer with bias + GELU, forward and backward: GEMM epilogue, act_kernel, colsum_kernel
+xl = torch.randn(T, K, device=dev).bfloat16().requires_grad_(True)
+wl = (torch.randn(K, N, device=dev) * 0.02).bfloat16().requires_grad_(True)
+bl = torch.zeros(N, device=dev).bfloat16().requires_grad_(True)
+ops.linear(xl, wl, bl, activation="gelu").float().mean().backward()
+# attention wrapper: strided views into the library SDPA + the gradient pack kernel
+qkv = torch.randn(32, 1024, 3 * 768, device=dev).bfloat16().requires_grad_(True)
+ops.causal_self_attention(qkv, 12).float().mean().backward()
 logits = torch.randn(8192, 50304, device=dev).bfloat16().requires_grad_(True)
 lab = torch.randint(0, 50257, (8192,), device=dev)
 softmax_cross_entropy(logits, lab).backward()
