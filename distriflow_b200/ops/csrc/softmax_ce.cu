@@ -47,10 +47,13 @@ __device__ __forceinline__ void block_online_reduce(float& m, float& s, float* s
 
 // ------------------------------------------------------------------ index labels
 // `logits` and `dlogits` may alias (in-place gradient).
-template <typename T, typename LabelT, int kThreads>
+// kCache: the row (up to ~110 KB: a 50304-wide bf16 vocabulary is 100.6 KB) is parked in shared memory by the first pass, so
+// the gradient pass does not go back to L2 / HBM for it: one read and one write of the logits per step.
+template <typename T, typename LabelT, int kThreads, bool kCache>
 __global__ void __launch_bounds__(kThreads)
 softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, float* __restrict__ loss_rows, T* dlogits, int C,
                         long ld, long ldg, float scale, long ignore_index) {
+  extern __shared__ uint4 row_cache[];
   __shared__ float sh_m[32], sh_s[32];
   __shared__ float sh_label;
   const long row = blockIdx.x;
@@ -65,6 +68,7 @@ softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, floa
   for (int c = threadIdx.x * VN; c < cvec; c += kThreads * VN) {
     V v;
     v.raw = *reinterpret_cast<const uint4*>(x + c);
+    if constexpr (kCache) row_cache[c / VN] = v.raw;
     float lm = v.get(0);
 #pragma unroll
     for (int i = 1; i < VN; ++i) lm = fmaxf(lm, v.get(i));
@@ -88,7 +92,8 @@ softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, floa
   const float sc = ignored ? 0.f : scale;
   for (int c = threadIdx.x * VN; c < cvec; c += kThreads * VN) {
     V v, o;
-    v.raw = *reinterpret_cast<const uint4*>(x + c);
+    if constexpr (kCache) v.raw = row_cache[c / VN];       // written by this same thread in the first pass
+    else v.raw = *reinterpret_cast<const uint4*>(x + c);
 #pragma unroll
     for (int i = 0; i < VN; ++i) {
       float p = __expf(v.get(i) - lse);
@@ -165,10 +170,27 @@ DFB_API int dfb_softmax_ce_index(const void* logits, const void* labels, int lab
                                  cudaStream_t stream) {
   DFB_REQUIRE(rows > 0 && C > 0, "softmax_ce: empty problem");
   constexpr int T = 512;
+  // row cache: only when a gradient is wanted, the vector path applies and two CTAs still fit on an SM
+  const size_t esz = dtype == DT_BF16 ? 2 : 4;
+  const int vn = (int)(16 / esz);
+  const bool vec_ok = (ld % vn) == 0 && (ldg % vn) == 0 && ((uintptr_t)logits & 15) == 0 && ((uintptr_t)dlogits & 15) == 0;
+  const size_t cache_bytes = (size_t)(C / vn) * 16;
+  const bool cache = dlogits != nullptr && vec_ok && cache_bytes >= 16 * 1024 && cache_bytes <= 110 * 1024;
 #define DFB_CE_CASE(dt, lt, TT, LT)                                                                                         \
   if (dtype == dt && label_dtype == lt) {                                                                                   \
-    softmax_ce_index_kernel<TT, LT, T><<<rows, T, 0, stream>>>((const TT*)logits, (const LT*)labels, loss_rows, (TT*)dlogits, \
-                                                              C, ld, ldg, scale, ignore_index);                             \
+    if (cache) {                                                                                                            \
+      auto kern = softmax_ce_index_kernel<TT, LT, T, true>;                                                                 \
+      static bool configured = false;                                                                                       \
+      if (!configured) {                                                                                                    \
+        DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));                \
+        configured = true;                                                                                                  \
+      }                                                                                                                     \
+      kern<<<rows, T, cache_bytes, stream>>>((const TT*)logits, (const LT*)labels, loss_rows, (TT*)dlogits, C, ld, ldg,     \
+                                             scale, ignore_index);                                                          \
+    } else {                                                                                                                \
+      softmax_ce_index_kernel<TT, LT, T, false><<<rows, T, 0, stream>>>((const TT*)logits, (const LT*)labels, loss_rows,    \
+                                                                        (TT*)dlogits, C, ld, ldg, scale, ignore_index);    \
+    }                                                                                                                       \
     DFB_CUDA_CHECK(cudaGetLastError());                                                                                     \
     return 0;                                                                                                               \
   }
