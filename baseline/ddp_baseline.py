@@ -19,7 +19,11 @@ import torch.nn.functional as F
 def stock_ops():
     """Route distriflow_b200.ops through PyTorch library kernels (baseline arm only)."""
     from distriflow_b200 import ops
-    saved = (ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy)
+    saved = (ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc)
+    from distriflow_b200.ops.norm import batch_norm_reference
+
+    def bn(x, gamma, beta, rm, rv, training, momentum=0.1, eps=1e-5, activation=None, residual=None):
+        return batch_norm_reference(x, gamma, beta, rm, rv, training, momentum, eps, activation, residual)
 
     def linear(x, w, b=None, activation=None, transposed=False):
         y = F.linear(x, w if transposed else w.t(), b)
@@ -47,11 +51,11 @@ def stock_ops():
             return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), labels.reshape(-1).long())
         return (-(labels.float() * F.log_softmax(logits.float(), -1)).sum(-1)).mean()
 
-    ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy = linear, conv, pool, ce
+    ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc = linear, conv, pool, ce, bn
     try:
         yield
     finally:
-        ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy = saved
+        ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc = saved
 
 
 def make_ddp_step(model, loss_fn, optimizer: str, lr: float, world: int, device, bucket_mb: int = 32):

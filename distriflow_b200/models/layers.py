@@ -156,14 +156,10 @@ class BatchNormalization(nn.Module):
         self.register_buffer("moving_mean", torch.zeros(channels))
         self.register_buffer("moving_variance", torch.ones(channels))
 
-    def forward(self, x):
-        if x.dim() == 4:   # NHWC storage viewed as NCHW channels_last: no copy
-            xc = x.permute(0, 3, 1, 2)
-            y = F.batch_norm(xc, self.moving_mean, self.moving_variance, self.gamma, self.beta, self.training,
-                             1.0 - self.momentum, self.epsilon)
-            return y.permute(0, 2, 3, 1)
-        return F.batch_norm(x, self.moving_mean, self.moving_variance, self.gamma, self.beta, self.training,
-                            1.0 - self.momentum, self.epsilon)
+    def forward(self, x, residual=None, activation=None):
+        """`activation(BN(x) + residual)`: the add and the ReLU of a ResNet block ride on the normalisation kernel."""
+        return ops.batch_norm_nhwc(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, self.training,
+                                   1.0 - self.momentum, self.epsilon, activation, residual)
 
 
 class LayerNorm(nn.Module):

@@ -2,8 +2,8 @@
 
 Not in the reference (it ships only the MNIST models).  Built from this package's own layers: Conv2D with HWIO
 filters runs the hand-written implicit-GEMM kernels (tcgen05 for bf16 with C_in % 64 == 0, CUDA-core otherwise),
-the classifier head is the Dense GEMM, the loss is the fused softmax-CE.  BatchNorm, residual adds and pooling stay
-on PyTorch ops (last paragraph).
+the classifier head is the Dense GEMM, the loss is the fused softmax-CE, and BatchNorm with the residual add and the
+ReLU of a block is one fused op (`ops.batch_norm_nhwc`, `csrc/batchnorm.cu`).  Global average pooling stays on PyTorch.
 """
 from __future__ import annotations
 
@@ -25,9 +25,10 @@ class ConvBN(nn.Module):
         self.relu = relu
         nn.init.kaiming_normal_(self.conv.kernel.data.permute(3, 2, 0, 1), mode="fan_out", nonlinearity="relu")
 
-    def forward(self, x):
-        y = self.bn(self.conv(x))
-        return F.relu(y) if self.relu else y
+    def forward(self, x, residual=None, relu=None):
+        """`relu(bn(conv(x)) + residual)`; the add and the ReLU are fused into the BatchNorm kernels."""
+        relu = self.relu if relu is None else relu
+        return self.bn(self.conv(x), residual, "relu" if relu else None)
 
 
 class BasicBlock(nn.Module):
@@ -38,8 +39,7 @@ class BasicBlock(nn.Module):
         self.short = None if (stride == 1 and cin == cout) else ConvBN(cin, cout, 1, stride, False, name + "/short")
 
     def forward(self, x):
-        y = self.c2(self.c1(x))
-        return F.relu(y + (x if self.short is None else self.short(x)))
+        return self.c2(self.c1(x), x if self.short is None else self.short(x), True)
 
 
 class Bottleneck(nn.Module):
@@ -52,8 +52,7 @@ class Bottleneck(nn.Module):
         self.short = None if (stride == 1 and cin == cout) else ConvBN(cin, cout, 1, stride, False, name + "/short")
 
     def forward(self, x):
-        y = self.c3(self.c2(self.c1(x)))
-        return F.relu(y + (x if self.short is None else self.short(x)))
+        return self.c3(self.c2(self.c1(x)), x if self.short is None else self.short(x), True)
 
 
 class ResNet(nn.Module):

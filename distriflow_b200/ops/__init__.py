@@ -16,7 +16,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 import torch.nn.functional as F
 
-__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "add_layer_norm", "causal_self_attention", "mlp",
+__all__ = ["linear", "conv2d_nhwc", "maxpool2d_nhwc", "layer_norm", "add_layer_norm", "batch_norm_nhwc", "causal_self_attention", "mlp",
            "softmax_cross_entropy", "native_available", "same_padding"]
 
 
@@ -113,6 +113,17 @@ def add_layer_norm(x: torch.Tensor, r: torch.Tensor, gamma: torch.Tensor, beta: 
         return add_layer_norm_cuda(x, r, gamma, beta, eps)
     s = x + r
     return s, F.layer_norm(s.float(), (s.shape[-1],), gamma.float(), beta.float(), eps).to(s.dtype)
+
+
+def batch_norm_nhwc(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, running_mean: Optional[torch.Tensor],
+                    running_var: Optional[torch.Tensor], training: bool, momentum: float = 0.1, eps: float = 1e-5,
+                    activation: Optional[str] = None, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`act(BatchNorm(x) [+ residual])` over the last axis; `momentum` weighs the new statistics (PyTorch convention)."""
+    if x.is_cuda:
+        from .norm import batch_norm_cuda
+        return batch_norm_cuda(x, gamma, beta, running_mean, running_var, training, momentum, eps, activation, residual)
+    from .norm import batch_norm_reference
+    return batch_norm_reference(x, gamma, beta, running_mean, running_var, training, momentum, eps, activation, residual)
 
 
 def causal_self_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:

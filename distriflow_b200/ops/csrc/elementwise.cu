@@ -301,6 +301,15 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
   const int k8n = Kpad >> 3;
   const long total = (long)N * OH * OW * k8n;
   const int Kreal = kh * kw * C;
+  __shared__ int tab[1024];                        // k -> (r << 24) | (s << 16) | ci
+  const bool use_tab = (C & 7) != 0 && Kreal <= 1024 && kh < 128 && kw < 256;
+  if (use_tab) {
+    for (int k = threadIdx.x; k < Kreal; k += 256) {
+      const int ci = k % C, rs = k / C;
+      tab[k] = ((rs / kw) << 24) | ((rs % kw) << 16) | ci;
+    }
+    __syncthreads();
+  }
   for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
     const int k8 = (int)(i % k8n);
     long pix = i / k8n;
@@ -318,17 +327,28 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
       *reinterpret_cast<uint4*>(out + pix * Kpad + k) = q;
       continue;
     }
+    // thin inputs (the 3-channel stem): per-k tap coordinates come from a table built once per block instead of four
+    // integer divisions per element
     __align__(16) __nv_bfloat16 v[8];
+    const int ih0 = oh * sh - pt, iw0 = ow * sw - pl;
+    const __nv_bfloat16* xb = x + (((long)n * H + ih0) * W + iw0) * C;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int k = k8 * 8 + j;
-      float val = 0.f;
+      __nv_bfloat16 val = __float2bfloat16(0.f);
       if (k < Kreal) {
-        const int ci = k % C, rs = k / C, s = rs % kw, r = rs / kw;
-        const int ih = oh * sh - pt + r, iw = ow * sw - pl + s;
-        if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = __bfloat162float(x[(((long)n * H + ih) * W + iw) * C + ci]);
+        int r, s2, off;
+        if (use_tab) {
+          const int e = tab[k];
+          r = e >> 24; s2 = (e >> 16) & 0xff; off = (r * W + s2) * C + (e & 0xffff);
+        } else {
+          const int ci = k % C, rs = k / C;
+          s2 = rs % kw; r = rs / kw; off = (r * W + s2) * C + ci;
+        }
+        const int ih = ih0 + r, iw = iw0 + s2;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = xb[off];
       }
-      v[j] = __float2bfloat16(val);
+      v[j] = val;
     }
     *reinterpret_cast<uint4*>(out + pix * Kpad + k8 * 8) = *reinterpret_cast<const uint4*>(v);
   }

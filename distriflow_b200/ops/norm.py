@@ -28,6 +28,14 @@ def _sigs():
         L.dfb_add_layernorm_bwd.argtypes = [c_void_p] * 10 + [c_int, c_int, c_int, c_void_p]
         L.dfb_permute_rows.restype = c_int
         L.dfb_permute_rows.argtypes = [c_void_p, c_void_p] + [c_int] * 4 + [ctypes.c_long] * 8 + [c_int, c_void_p]
+        L.dfb_bn_partial_blocks.restype = c_int
+        L.dfb_bn_partial_blocks.argtypes = [ctypes.c_long, c_int, c_int]
+        L.dfb_bn_fwd_train.restype = c_int
+        L.dfb_bn_fwd_train.argtypes = [c_void_p] * 11 + [ctypes.c_long, c_int, c_float, c_float, c_int, c_int, c_int, c_void_p]
+        L.dfb_bn_fwd_eval.restype = c_int
+        L.dfb_bn_fwd_eval.argtypes = [c_void_p] * 8 + [ctypes.c_long, c_int, c_float, c_int, c_int, c_int, c_void_p]
+        L.dfb_bn_bwd.restype = c_int
+        L.dfb_bn_bwd.argtypes = [c_void_p] * 12 + [ctypes.c_long, c_int, c_int, c_int, c_int, c_void_p]
         L._dfb_norm_sigs = True
     return L
 
@@ -117,3 +125,120 @@ def permute_rows(src: torch.Tensor, dst: torch.Tensor, dims, src_strides, dst_st
     ss = [int(v) * es for v in src_strides] + [0] * (4 - len(dims))
     ds = [int(v) * es for v in dst_strides] + [0] * (4 - len(dims))
     check(L.dfb_permute_rows(ptr(src), ptr(dst), *n, *ss, *ds, row_elems * es, stream()), "dfb_permute_rows")
+
+
+# ------------------------------------------------------------------------------------------------ BatchNorm (channels last)
+def _bn_supported(x: torch.Tensor, gamma: torch.Tensor) -> bool:
+    vn = 8 if x.dtype == torch.bfloat16 else 4
+    return x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and x.shape[-1] % vn == 0 and \
+        gamma.dtype in (torch.bfloat16, torch.float32)
+
+
+class _BatchNormFn(torch.autograd.Function):
+    """y = act(BN(x) [+ residual]) over the last axis, batch statistics (training) — `csrc/batchnorm.cu`."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, momentum, eps, relu):
+        L = _sigs()
+        C = x.shape[-1]
+        x2 = x.reshape(-1, C)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        r2 = None
+        if residual is not None:
+            r2 = residual.reshape(-1, C)
+            if not r2.is_contiguous() or r2.dtype != x2.dtype:
+                r2 = r2.to(x2.dtype).contiguous()
+        rows = x2.shape[0]
+        b = beta if beta.dtype == gamma.dtype else beta.to(gamma.dtype)
+        y = torch.empty_like(x2)
+        dev = x.device
+        stats = torch.empty(2 * C, dtype=torch.float32, device=dev)           # saved mean | saved invstd
+        gy = int(L.dfb_bn_partial_blocks(rows, C, dt(x2)))
+        part = torch.empty(gy * 2 * C, dtype=torch.float32, device=dev)
+        ab = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        direct = running_mean is not None and running_mean.dtype == torch.float32 and running_var.dtype == torch.float32 \
+            and running_mean.is_cuda and running_mean.is_contiguous() and running_var.is_contiguous()
+        check(L.dfb_bn_fwd_train(ptr(x2), ptr(r2), ptr(gamma), ptr(b), ptr(running_mean) if direct else None,
+                                 ptr(running_var) if direct else None, ptr(y), ptr(stats), ptr(stats[C:]), ptr(part), ptr(ab), rows, C,
+                                 eps, momentum, int(bool(relu)), dt(x2), dt(gamma), stream()), "dfb_bn_fwd_train")
+        if running_mean is not None and not direct:                            # e.g. bf16 buffers of a `.to(bfloat16)` model
+            n = float(rows)
+            var = (1.0 / stats[C:].square() - eps).clamp_min_(0) * (n / max(n - 1.0, 1.0))
+            running_mean.mul_(1 - momentum).add_(stats[:C].to(running_mean.dtype), alpha=momentum)
+            running_var.mul_(1 - momentum).add_(var.to(running_var.dtype), alpha=momentum)
+        ctx.save_for_backward(x2, y if relu else None, gamma, stats)
+        ctx.refs = (gamma, beta)
+        ctx.relu, ctx.has_res, ctx.shape = bool(relu), residual is not None, x.shape
+        ctx.res_dtype = residual.dtype if residual is not None else None
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _sigs()
+        x2, y, g, stats = ctx.saved_tensors
+        gamma, beta = ctx.refs
+        rows, C = x2.shape
+        dy2 = dy.reshape(rows, C)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dev = x2.device
+        dx = torch.empty_like(x2)
+        need_dres = ctx.has_res and ctx.relu
+        dres = torch.empty_like(x2) if need_dres else None
+        gy = int(L.dfb_bn_partial_blocks(rows, C, dt(x2)))
+        part = torch.empty(gy * 2 * C, dtype=torch.float32, device=dev)
+        coef = torch.empty(3 * C, dtype=torch.float32, device=dev)
+        sg, sb = getattr(gamma, "_dfb_grad_sink", None), getattr(beta, "_dfb_grad_sink", None)
+        direct = sg is not None and sb is not None and sg.dtype == g.dtype and sb.dtype == g.dtype
+        dgamma = sg if direct else torch.empty(C, dtype=g.dtype, device=dev)
+        dbeta = sb if direct else torch.empty(C, dtype=g.dtype, device=dev)
+        check(L.dfb_bn_bwd(ptr(dy2), ptr(y), ptr(x2), ptr(g), ptr(stats), ptr(stats[C:]), ptr(dx), ptr(dres), ptr(dgamma), ptr(dbeta),
+                           ptr(part), ptr(coef), rows, C, int(ctx.relu), dt(x2), dt(g), stream()), "dfb_bn_bwd")
+        if direct:
+            gamma._dfb_grad_ready()
+            beta._dfb_grad_ready()
+            dgamma = dbeta = None
+        else:
+            dgamma, dbeta = dgamma.to(gamma.dtype), dbeta.to(beta.dtype)
+        d_res = None
+        if ctx.has_res:
+            d_res = (dres if need_dres else dy2).view(ctx.shape)
+            if d_res.dtype != ctx.res_dtype:
+                d_res = d_res.to(ctx.res_dtype)
+        return dx.view(ctx.shape), d_res, dgamma, dbeta, None, None, None, None, None
+
+
+def batch_norm_cuda(x, gamma, beta, running_mean, running_var, training: bool, momentum: float, eps: float,
+                    activation=None, residual=None) -> torch.Tensor:
+    """Channels-last BatchNorm + optional residual add + optional ReLU.  `momentum` is the weight of the NEW statistics."""
+    relu = activation == "relu"
+    if activation not in (None, "relu"):
+        raise ValueError(f"batch_norm: unsupported activation {activation}")
+    if training and _bn_supported(x, gamma):
+        return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, float(momentum), float(eps), relu)
+    if (not training) and _bn_supported(x, gamma) and not torch.is_grad_enabled() and running_mean is not None \
+            and running_mean.dtype == torch.float32 and running_var.dtype == torch.float32:
+        L = _sigs()
+        C = x.shape[-1]
+        x2 = x.reshape(-1, C).contiguous()
+        r2 = residual.reshape(-1, C).to(x2.dtype).contiguous() if residual is not None else None
+        y = torch.empty_like(x2)
+        ab = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+        b = beta if beta.dtype == gamma.dtype else beta.to(gamma.dtype)
+        check(L.dfb_bn_fwd_eval(ptr(x2), ptr(r2), ptr(gamma), ptr(b), ptr(running_mean), ptr(running_var), ptr(y), ptr(ab),
+                                x2.shape[0], C, eps, int(relu), dt(x2), dt(gamma), stream()), "dfb_bn_fwd_eval")
+        return y.view(x.shape)
+    return batch_norm_reference(x, gamma, beta, running_mean, running_var, training, momentum, eps, activation, residual)
+
+
+def batch_norm_reference(x, gamma, beta, running_mean, running_var, training: bool, momentum: float, eps: float,
+                         activation=None, residual=None) -> torch.Tensor:
+    """Plain PyTorch statement of the same op (CPU path, eval-mode training graphs, and the baseline arm)."""
+    if x.dim() == 4:                                  # NHWC storage viewed as NCHW channels_last: no copy
+        y = F.batch_norm(x.permute(0, 3, 1, 2), running_mean, running_var, gamma, beta, training, momentum, eps).permute(0, 2, 3, 1)
+    else:
+        y = F.batch_norm(x, running_mean, running_var, gamma, beta, training, momentum, eps)
+    if residual is not None:
+        y = y + residual
+    return F.relu(y) if activation == "relu" else y

@@ -453,3 +453,49 @@ def test_small_channel_conv_patch_gemm_path(cfg):
     yr.backward(gy.float().cpu())
     assert y.shape == yr.shape and rel_err(y.cpu(), yr) < 2e-2
     assert rel_err(x.grad.cpu(), xr.grad) < 2e-2 and rel_err(w.grad.cpu(), wr.grad) < 2e-2
+
+
+# ----------------------------------------------------------------------------------------- fused BatchNorm (+ residual + ReLU)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(8, 14, 14, 64), (4, 7, 7, 2048), (16, 8, 8, 16), (3, 5, 5, 24)])
+@pytest.mark.parametrize("with_res,relu", [(False, False), (False, True), (True, True), (True, False)])
+def test_batch_norm_nhwc_fused(dtype, shape, with_res, relu):
+    """`csrc/batchnorm.cu` against PyTorch's batch_norm (+ add + relu) evaluated in fp32 on the same (rounded) inputs."""
+    from distriflow_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(3)
+    C = shape[-1]
+    x = (torch.randn(shape, device=dev(), generator=g) * 2 + 0.5).to(dtype).requires_grad_(True)
+    res = torch.randn(shape, device=dev(), generator=g).to(dtype).requires_grad_(True) if with_res else None
+    gamma = (torch.rand(C, device=dev(), generator=g) + 0.5).to(dtype).requires_grad_(True)
+    beta = (torch.randn(C, device=dev(), generator=g) * 0.1).to(dtype).requires_grad_(True)
+    rm, rv = torch.zeros(C, device=dev()), torch.ones(C, device=dev())
+    act = "relu" if relu else None
+    y = ops.batch_norm_nhwc(x, gamma, beta, rm, rv, True, 0.1, 1e-5, act, res)
+    dy = torch.randn(shape, device=dev(), generator=g).to(dtype)
+    grads = torch.autograd.grad(y, [t for t in (x, res, gamma, beta) if t is not None], dy)
+    # fp32 reference on the same inputs
+    xf, gf, bf = (t.detach().float().requires_grad_(True) for t in (x, gamma, beta))
+    rf = res.detach().float().requires_grad_(True) if with_res else None
+    rm2, rv2 = torch.zeros(C, device=dev()), torch.ones(C, device=dev())
+    yr = F.batch_norm(xf.permute(0, 3, 1, 2), rm2, rv2, gf, bf, True, 0.1, 1e-5).permute(0, 2, 3, 1)
+    if with_res:
+        yr = yr + rf
+    if relu:
+        yr = F.relu(yr)
+    if relu and dtype == torch.bfloat16:      # the kernel's ReLU mask is y > 0 on the bf16 output: use the same mask
+        pass
+    gref = torch.autograd.grad(yr, [t for t in (xf, rf, gf, bf) if t is not None], dy.float())
+    tol = 2e-2 if dtype == torch.bfloat16 else 2e-4
+    assert rel_err(y, yr) < tol
+    for a, b in zip(grads, gref):
+        assert rel_err(a, b) < (4e-2 if dtype == torch.bfloat16 else 1e-3), (a.shape, rel_err(a, b))
+    assert rel_err(rm, rm2) < 1e-3 and rel_err(rv, rv2) < 1e-3
+    # inference mode uses the running statistics
+    with torch.no_grad():
+        ye = ops.batch_norm_nhwc(x.detach(), gamma.detach(), beta.detach(), rm, rv, False, 0.1, 1e-5, act, res.detach() if with_res else None)
+        yer = F.batch_norm(xf.detach().permute(0, 3, 1, 2), rm2, rv2, gf.detach(), bf.detach(), False, 0.1, 1e-5).permute(0, 2, 3, 1)
+        if with_res:
+            yer = yer + rf.detach()
+        if relu:
+            yer = F.relu(yer)
+    assert rel_err(ye, yer) < tol
