@@ -8,6 +8,8 @@
 // Index labels (`int64/int32 [B]`, one-hot folded in) are the perf path; dense labels (`[B,C]` one-hot or
 // soft) serve the MNIST configs; MODE_REFCOMPAT_* is the reference's swapped-argument loss with
 // both gradient variants.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "device_utils.cuh"
 
@@ -48,7 +50,7 @@ __device__ __forceinline__ void block_online_reduce(float& m, float& s, float* s
 // ------------------------------------------------------------------ index labels
 // `logits` and `dlogits` may alias (in-place gradient).
 // kCache: the row (up to ~110 KB: a 50304-wide bf16 vocabulary is 100.6 KB) is parked in shared memory by the first pass, so
-// the gradient pass does not go back to L2 / HBM for it: one read and one write of the logits per step.
+// the gradient pass does not go back to L2 / HBM for it.  Kept as an option; measured slower than the L2-served second pass.
 template <typename T, typename LabelT, int kThreads, bool kCache>
 __global__ void __launch_bounds__(kThreads)
 softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, float* __restrict__ loss_rows, T* dlogits, int C,
@@ -65,9 +67,7 @@ softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, floa
                       ((reinterpret_cast<uintptr_t>(dlogits) & 15) == 0);
   const int cvec = vec_ok ? (C / VN) * VN : 0;
   float m = -INFINITY, s = 0.f;
-  for (int c = threadIdx.x * VN; c < cvec; c += kThreads * VN) {
-    V v;
-    v.raw = *reinterpret_cast<const uint4*>(x + c);
+  auto consume = [&](const V& v, int c) {
     if constexpr (kCache) row_cache[c / VN] = v.raw;
     float lm = v.get(0);
 #pragma unroll
@@ -76,7 +76,24 @@ softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, floa
 #pragma unroll
     for (int i = 0; i < VN; ++i) ls += __expf(v.get(i) - lm);
     online_combine(m, s, lm, ls);
-    if (label >= c && label < c + VN) sh_label = v.get((int)(label - c));
+    if (label >= c && label < c + VN) sh_label = to_f32<T>(x[label]);   // scalar reload: keeps v in registers
+  };
+  {
+    constexpr int U = 4;                            // 4 x 16-byte loads in flight per thread: the row pass is latency bound
+    constexpr int kStep = kThreads * VN;
+    int c = threadIdx.x * VN;
+    for (; c + (U - 1) * kStep < cvec; c += U * kStep) {
+      V v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u].raw = *reinterpret_cast<const uint4*>(x + c + u * kStep);
+#pragma unroll
+      for (int u = 0; u < U; ++u) consume(v[u], c + u * kStep);
+    }
+    for (; c < cvec; c += kStep) {
+      V v;
+      v.raw = *reinterpret_cast<const uint4*>(x + c);
+      consume(v, c);
+    }
   }
   for (int c = cvec + threadIdx.x; c < C; c += kThreads) {
     float xv = to_f32<T>(x[c]);
@@ -90,6 +107,7 @@ softmax_ce_index_kernel(const T* logits, const LabelT* __restrict__ labels, floa
   if (dlogits == nullptr) return;
   T* g = dlogits + row * ldg;
   const float sc = ignored ? 0.f : scale;
+#pragma unroll 4
   for (int c = threadIdx.x * VN; c < cvec; c += kThreads * VN) {
     V v, o;
     if constexpr (kCache) v.raw = row_cache[c / VN];       // written by this same thread in the first pass
@@ -175,7 +193,10 @@ DFB_API int dfb_softmax_ce_index(const void* logits, const void* labels, int lab
   const int vn = (int)(16 / esz);
   const bool vec_ok = (ld % vn) == 0 && (ldg % vn) == 0 && ((uintptr_t)logits & 15) == 0 && ((uintptr_t)dlogits & 15) == 0;
   const size_t cache_bytes = (size_t)(C / vn) * 16;
-  const bool cache = dlogits != nullptr && vec_ok && cache_bytes >= 16 * 1024 && cache_bytes <= 110 * 1024;
+  // Measured on B200 (scripts/bench_ce.py, 8192 x 50304 bf16): 426.8 us with the row cache (two 100 KB CTAs per SM leave too
+  // few loads in flight) against 325.6 us without it, where the second pass is served by L2: off unless DFB_CE_CACHE is set.
+  static const bool want_cache = getenv("DFB_CE_CACHE") != nullptr;
+  const bool cache = want_cache && dlogits != nullptr && vec_ok && cache_bytes >= 16 * 1024 && cache_bytes <= 110 * 1024;
 #define DFB_CE_CASE(dt, lt, TT, LT)                                                                                         \
   if (dtype == dt && label_dtype == lt) {                                                                                   \
     if (cache) {                                                                                                            \

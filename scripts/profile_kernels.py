@@ -43,6 +43,12 @@ s, y = ops.add_layer_norm(xs, rs, g, b)
 xc = torch.randn(64, 28, 28, 128, device=dev).bfloat16().requires_grad_(True)
 wc = (torch.randn(3, 3, 128, 128, device=dev) * 0.03).bfloat16().requires_grad_(True)
 ops.conv2d_nhwc(xc, wc, None, (1, 1), "same", "relu").float().mean().backward()
+# fused BatchNorm + residual + ReLU, ResNet-50 stage-1 shape (64 x 56 x 56 x 256), forward and backward
+xb = torch.randn(64, 56, 56, 256, device=dev).bfloat16().requires_grad_(True)
+rb = torch.randn(64, 56, 56, 256, device=dev).bfloat16().requires_grad_(True)
+gb = torch.ones(256, device=dev).bfloat16().requires_grad_(True)
+bb = torch.zeros(256, device=dev).bfloat16().requires_grad_(True)
+ops.batch_norm_nhwc(xb, gb, bb, torch.zeros(256, device=dev), torch.ones(256, device=dev), True, 0.1, 1e-5, "relu", rb).float().mean().backward()
 # fused bucket kernel, world = 1 (optimizer half of the fused gradient path), 32 MB bucket, Adam
 from distriflow_b200.ops import _lib
 from distriflow_b200.ops._lib import check, ptr
