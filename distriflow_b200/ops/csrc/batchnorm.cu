@@ -115,6 +115,25 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
   return v;
 }
 
+// A lane's share of the per-block partials of channel c; four independent loads per round (the loop is latency bound).
+__device__ __forceinline__ void bn_gather_partials(const float* __restrict__ part, int gy, int C, int c, int lane, double& s0,
+                                                   double& s1) {
+  const long pitch = 2L * C;
+  int b = lane;
+  for (; b + 96 < gy; b += 128) {
+    const float a0 = part[b * pitch + c], a1 = part[(b + 32) * pitch + c], a2 = part[(b + 64) * pitch + c],
+                a3 = part[(b + 96) * pitch + c];
+    const float q0 = part[b * pitch + C + c], q1 = part[(b + 32) * pitch + C + c], q2 = part[(b + 64) * pitch + C + c],
+                q3 = part[(b + 96) * pitch + C + c];
+    s0 += ((double)a0 + (double)a1) + ((double)a2 + (double)a3);
+    s1 += ((double)q0 + (double)q1) + ((double)q2 + (double)q3);
+  }
+  for (; b < gy; b += 32) {
+    s0 += (double)part[b * pitch + c];
+    s1 += (double)part[b * pitch + C + c];
+  }
+}
+
 __global__ void __launch_bounds__(256) bn_stats_finalize_kernel(const float* __restrict__ part, int gy, long rows, long rpb, int C,
                                                                 const void* gamma, const void* beta, int pdt, float eps,
                                                                 float momentum, float* running_mean, float* running_var,
@@ -122,10 +141,7 @@ __global__ void __launch_bounds__(256) bn_stats_finalize_kernel(const float* __r
   const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
   double s = 0.0, q = 0.0;
-  for (int b = lane; b < gy; b += 32) {
-    s += (double)part[(long)b * 2 * C + c];
-    q += (double)part[(long)b * 2 * C + C + c];
-  }
+  bn_gather_partials(part, gy, C, c, lane, s, q);
   s = warp_sum_f64(s);
   q = warp_sum_f64(q);
   if (lane != 0) return;
@@ -255,10 +271,7 @@ __global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __res
   const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;      // one warp per channel
   if (c >= C) return;
   double d1 = 0.0, d2 = 0.0;
-  for (int b = lane; b < gy; b += 32) {
-    d1 += (double)part[(long)b * 2 * C + c];
-    d2 += (double)part[(long)b * 2 * C + C + c];
-  }
+  bn_gather_partials(part, gy, C, c, lane, d1, d2);
   const float s1 = (float)warp_sum_f64(d1), s2 = (float)warp_sum_f64(d2);
   if (lane != 0) return;
   const float is = invstd[c];

@@ -295,62 +295,71 @@ DFB_API int dfb_accuracy(const void* pred, const void* labels, int label_kind, f
 // Kpad, a multiple of 8).  With C_in < 64 the implicit-GEMM TMA path has no 128-byte channel rows to fetch, so the patch
 // matrix is materialised once (bf16) and the tcgen05 Dense GEMM does forward and filter gradient on it.
 namespace dfb {
+// Division by a runtime constant as multiply-high + shift (host-computed magic; exact for dividends below 2^31): the patch
+// index decomposition (pixel / tap / channel) was the whole cost of this kernel when done with hardware-emulated division.
+struct FastDiv {
+  uint32_t d, magic, shift;
+  __device__ __forceinline__ uint32_t div(uint32_t n) const { return (__umulhi(n, magic) + n) >> shift; }
+  __device__ __forceinline__ void divmod(uint32_t n, uint32_t& q, uint32_t& r) const {
+    q = div(n);
+    r = n - q * d;
+  }
+};
+static FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  uint32_t shift = 0;
+  while ((1ull << shift) < d) ++shift;
+  f.shift = shift;
+  f.magic = (uint32_t)((((1ull << 32) * ((1ull << shift) - d)) / d) + 1);
+  return f;
+}
+
 __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int H,
                                                      int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
-                                                     int Kpad) {
-  const int k8n = Kpad >> 3;
-  const long total = (long)N * OH * OW * k8n;
+                                                     int Kpad, FastDiv d_k8n, FastDiv d_ow, FastDiv d_oh, long total) {
   const int Kreal = kh * kw * C;
-  __shared__ int tab[1024];                        // k -> (r << 24) | (s << 16) | ci
-  const bool use_tab = (C & 7) != 0 && Kreal <= 1024 && kh < 128 && kw < 256;
-  if (use_tab) {
-    for (int k = threadIdx.x; k < Kreal; k += 256) {
-      const int ci = k % C, rs = k / C;
-      tab[k] = ((rs / kw) << 24) | ((rs % kw) << 16) | ci;
-    }
-    __syncthreads();
+  __shared__ int tab[1024];                        // k -> (r << 24) | (s << 16) | ci, built once per block
+  const bool vec = (C & 7) == 0;
+  const int entries = vec ? (Kreal >> 3) : Kreal;  // vector path: one entry per 8 consecutive channels of a tap
+  for (int e = threadIdx.x; e < entries; e += 256) {
+    const int k = vec ? e * 8 : e;
+    const int ci = k % C, rs = k / C;
+    tab[e] = ((rs / kw) << 24) | ((rs % kw) << 16) | ci;
   }
+  __syncthreads();
   for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
-    const int k8 = (int)(i % k8n);
-    long pix = i / k8n;
-    const int ow = (int)(pix % OW);
-    long t = pix / OW;
-    const int oh = (int)(t % OH), n = (int)(t / OH);
-    if ((C & 7) == 0) {           // 8 consecutive k = 8 consecutive channels of one tap: a single 16-byte load
-      const int k = k8 * 8;
+    uint32_t pix, k8, t, ow, n, oh;
+    d_k8n.divmod((uint32_t)i, pix, k8);
+    d_ow.divmod(pix, t, ow);
+    d_oh.divmod(t, n, oh);
+    const int ih0 = (int)oh * sh - pt, iw0 = (int)ow * sw - pl;
+    const __nv_bfloat16* xb = x + (((long)n * H + ih0) * W + iw0) * C;
+    if (vec) {                    // 8 consecutive k = 8 consecutive channels of one tap: a single 16-byte load
       uint4 q = make_uint4(0, 0, 0, 0);
-      if (k < Kreal) {
-        const int ci = k % C, rs = k / C, s = rs % kw, r = rs / kw;
-        const int ih = oh * sh - pt + r, iw = ow * sw - pl + s;
-        if (ih >= 0 && ih < H && iw >= 0 && iw < W) q = *reinterpret_cast<const uint4*>(x + (((long)n * H + ih) * W + iw) * C + ci);
+      if ((int)k8 * 8 < Kreal) {
+        const int e = tab[k8];
+        const int r = e >> 24, s2 = (e >> 16) & 0xff;
+        const int ih = ih0 + r, iw = iw0 + s2;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) q = *reinterpret_cast<const uint4*>(xb + (r * W + s2) * C + (e & 0xffff));
       }
-      *reinterpret_cast<uint4*>(out + pix * Kpad + k) = q;
+      *reinterpret_cast<uint4*>(out + (long)pix * Kpad + k8 * 8) = q;
       continue;
     }
-    // thin inputs (the 3-channel stem): per-k tap coordinates come from a table built once per block instead of four
-    // integer divisions per element
-    __align__(16) __nv_bfloat16 v[8];
-    const int ih0 = oh * sh - pt, iw0 = ow * sw - pl;
-    const __nv_bfloat16* xb = x + (((long)n * H + ih0) * W + iw0) * C;
+    __align__(16) __nv_bfloat16 v[8];              // thin inputs (the 3-channel stem): element-wise gather
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int k = k8 * 8 + j;
+      const int k = (int)k8 * 8 + j;
       __nv_bfloat16 val = __float2bfloat16(0.f);
       if (k < Kreal) {
-        int r, s2, off;
-        if (use_tab) {
-          const int e = tab[k];
-          r = e >> 24; s2 = (e >> 16) & 0xff; off = (r * W + s2) * C + (e & 0xffff);
-        } else {
-          const int ci = k % C, rs = k / C;
-          s2 = rs % kw; r = rs / kw; off = (r * W + s2) * C + ci;
-        }
+        const int e = tab[k];
+        const int r = e >> 24, s2 = (e >> 16) & 0xff;
         const int ih = ih0 + r, iw = iw0 + s2;
-        if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = xb[off];
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = xb[(r * W + s2) * C + (e & 0xffff)];
       }
       v[j] = val;
     }
-    *reinterpret_cast<uint4*>(out + pix * Kpad + k8 * 8) = *reinterpret_cast<const uint4*>(v);
+    *reinterpret_cast<uint4*>(out + (long)pix * Kpad + k8 * 8) = *reinterpret_cast<const uint4*>(v);
   }
 }
 }  // namespace dfb
@@ -411,11 +420,14 @@ DFB_API int dfb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C
                             int pt, int pl, int Kpad, cudaStream_t stream) {
   DFB_REQUIRE(Kpad % 8 == 0 && Kpad >= kh * kw * C, "im2col: Kpad must be a multiple of 8 covering kh*kw*C");
   const long total = (long)N * OH * OW * (Kpad / 8);
-  DFB_REQUIRE(total > 0, "im2col: empty");
+  DFB_REQUIRE(total > 0 && total < (1L << 31), "im2col: empty or more than 2^31 patch vectors");
+  DFB_REQUIRE(kh < 128 && kw < 256 && C < 65536 && (((C & 7) == 0 ? kh * kw * C / 8 : kh * kw * C) <= 1024),
+              "im2col: filter too large for the tap table (kh*kw*C <= 1024 scalars or 8192 with C %% 8 == 0)");
   long blocks = (total + 255) / 256;
-  if (blocks > dfb::num_sms() * 32) blocks = dfb::num_sms() * 32;
+  if (blocks > dfb::num_sms() * 16) blocks = dfb::num_sms() * 16;
   dfb::im2col_kernel<<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, OH, OW, kh, kw, sh,
-                                                   sw, pt, pl, Kpad);
+                                                   sw, pt, pl, Kpad, dfb::make_fastdiv((uint32_t)(Kpad / 8)),
+                                                   dfb::make_fastdiv((uint32_t)OW), dfb::make_fastdiv((uint32_t)OH), total);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
