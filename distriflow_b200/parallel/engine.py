@@ -389,6 +389,83 @@ class DataParallelEngine:
             for p, d in zip(live, saved):
                 p.data = d
 
+    # ------------------------------------------------------------------------------------ resume
+    def _gather_flat(self, t: Optional[torch.Tensor], b: Bucket) -> Optional[torch.Tensor]:
+        """Whole-bucket fp32 tensor from this rank's shard `t` (master / m / v)."""
+        if t is None:
+            return None
+        if self.backend == "p2p" and self.world > 1:
+            import torch.distributed as dist
+            parts = [torch.empty_like(t) for _ in range(self.world)]
+            dist.all_gather(parts, t, group=self.group)
+            return torch.cat(parts)
+        return t
+
+    def state_dict(self) -> Dict[str, Any]:
+        """Everything a resumed run needs: version (= optimizer step count), fp32 masters and optimizer moments per
+        parameter.  Shards are gathered, so the result does not depend on the world size it was saved at (collective: call
+        on every rank).  The reference checkpoints weights only (server/models.ts:132-138); optimizer state is new."""
+        names = {id(p): n for n, p in self.model.named_parameters()}
+        params: Dict[str, Dict[str, torch.Tensor]] = {}
+        for b in self.buckets:
+            flats = {k: self._gather_flat(getattr(b, k, None), b) for k in ("master", "m", "v")}
+            for p, off in zip(b.params, b.offsets):
+                entry = {k: f[off:off + p.numel()].view(p.shape).cpu().clone() for k, f in flats.items() if f is not None}
+                params[names[id(p)]] = entry
+        return {"format": "distriflow_b200.engine/1", "version": int(self.version), "optimizer": self.cfg["optimizer"],
+                "learningRate": self.lr, "params": params}
+
+    def load_state_dict(self, sd: Dict[str, Any]) -> None:
+        """Inverse of `state_dict` at ANY world size: every rank takes its slice of every bucket, the working copies are
+        refreshed from the masters, the step counter continues."""
+        if sd.get("format") != "distriflow_b200.engine/1":
+            raise ValueError("not an engine state dict")
+        names = {id(p): n for n, p in self.model.named_parameters()}
+        for b in self.buckets:
+            flats = {"master": torch.zeros(b.numel, dtype=torch.float32, device=self.device)}
+            for k in ("m", "v"):
+                if getattr(b, k, None) is not None:
+                    flats[k] = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
+            for p, off in zip(b.params, b.offsets):
+                entry = sd["params"].get(names[id(p)])
+                if entry is None or tuple(entry["master"].shape) != tuple(p.shape):
+                    raise ValueError(f"state dict has no matching entry for parameter {names[id(p)]}")
+                for k, f in flats.items():
+                    if k in entry:                       # a state saved by plain SGD resumes under Adam with zero moments
+                        f[off:off + p.numel()].copy_(entry[k].reshape(-1))
+            lo = self.rank * b.shard
+            lo, hi = (lo, lo + b.shard) if self.backend == "p2p" else (0, b.numel)
+            for k, f in flats.items():
+                getattr(b, k).copy_(f[lo:hi])
+            b.param_buf.copy_(flats["master"])
+        self.version = int(sd["version"])
+        if self._graph_mode:
+            self._step_dev.fill_(self.version)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.barrier(group=self.group)
+
+    def save_state(self, directory: str) -> Optional[str]:
+        """`<directory>/engine_state.pt` (rank 0 writes; collective).  Together with `save_checkpoint` (tf.js layout of the
+        weights) this is the resume point of a synchronous run."""
+        import os
+        sd = self.state_dict()
+        if self.rank != 0:
+            return None
+        os.makedirs(directory, exist_ok=True)
+        path = os.path.join(directory, "engine_state.pt")
+        tmp = path + ".tmp"
+        torch.save(sd, tmp)
+        os.replace(tmp, path)                            # never leaves a half-written state behind
+        return path
+
+    def load_state(self, directory: str) -> None:
+        import os
+        self.load_state_dict(torch.load(os.path.join(directory, "engine_state.pt"), map_location="cpu"))
+
     def gpu_launches_per_step(self) -> int:
         return len(self.buckets)
 

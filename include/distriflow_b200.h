@@ -139,6 +139,50 @@ int dfb_wq_pad_words(unsigned batches);
 int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                      void* stream);
 
+/* ---- normalisation and layout kernels (no counterpart in the reference: its models are Dense / Conv2D / MaxPool) ------------
+ * fused residual add + LayerNorm: s = x + r (r nullable), y = LN(s) * gamma + beta; mean / rstd: [rows] fp32 */
+int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamma, const void* beta, void* s_out, void* y, float* mean,
+                          float* rstd, int rows, int D, float eps, int dtype, void* stream);
+int dfb_layernorm_bwd_blocks(int rows);                     /* row blocks of the `part` scratch: 2 * D * blocks floats */
+int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
+                          void* dx, void* dgamma, void* dbeta, float* part, int rows, int D, int dtype, void* stream);
+/* strided copy of rows of `row_bytes` (multiple of 16): src + sum(i_k * s_k) -> dst + sum(i_k * d_k), strides in bytes */
+int dfb_permute_rows(const void* src, void* dst, int n0, int n1, int n2, int n3, long s0, long s1, long s2, long s3, long d0,
+                     long d1, long d2, long d3, int row_bytes, void* stream);
+/* channels-last BatchNorm fused with the residual add and ReLU of a ResNet block (csrc/batchnorm.cu).
+ * x, res (nullable), y: [rows, C] of `dtype`; gamma/beta of `param_dtype`; running stats fp32 (nullable);
+ * part: 2 * C * dfb_bn_partial_blocks(rows, C, dtype) floats; ab: 2 * C floats; coef: 3 * C floats. */
+int dfb_bn_partial_blocks(long rows, int C, int dtype);
+int dfb_bn_fwd_train(const void* x, const void* res, const void* gamma, const void* beta, float* running_mean, float* running_var,
+                     void* y, float* save_mean, float* save_invstd, float* part, float* ab, long rows, int C, float eps,
+                     float momentum, int relu, int dtype, int param_dtype, void* stream);
+int dfb_bn_fwd_eval(const void* x, const void* res, const void* gamma, const void* beta, const float* running_mean,
+                    const float* running_var, void* y, float* ab, long rows, int C, float eps, int relu, int dtype,
+                    int param_dtype, void* stream);
+int dfb_bn_bwd(const void* dy, const void* y, const void* x, const void* gamma, const float* save_mean, const float* save_invstd,
+               void* dx, void* dres, void* dgamma, void* dbeta, float* part, float* coef, long rows, int C, int relu, int dtype,
+               int param_dtype, void* stream);
+
+/* ---- multicast (NVLS) heap: driver VMM allocation + NVSwitch multicast object (parallel/csrc/mcast.cu).  No counterpart in
+ * the reference (socket.io star, abstract_server.ts:81-89).  Descriptors are POSIX fds handed between the rank processes. */
+int dfb_mc_supported(int* out);                                            /* 1: device can join a multicast object */
+int dfb_mc_round_size(size_t bytes, int ndev, size_t* rounded_out);        /* physical and multicast granularity */
+int dfb_vmm_create(size_t bytes, unsigned long long* handle_out, int* fd_out, void** va_out);      /* zero-filled, mapped */
+int dfb_vmm_import(int fd, size_t bytes, unsigned long long* handle_out, void** va_out);           /* peer's allocation */
+int dfb_vmm_release(unsigned long long handle, void* va, size_t bytes);
+int dfb_mc_create(int ndev, size_t bytes, unsigned long long* mc_out, int* fd_out);                /* rank 0 */
+int dfb_mc_import(int fd, unsigned long long* mc_out);                                             /* other ranks */
+int dfb_mc_add_device(unsigned long long mc);                               /* every rank, before anybody binds */
+int dfb_mc_bind_map(unsigned long long mc, unsigned long long mem, size_t bytes, void** mc_va_out);
+int dfb_mc_release(unsigned long long mc, void* mc_va, size_t bytes);
+/* sync path through the switch: multimem.ld_reduce of the gradients, multimem.st of the refreshed weights (bf16 only).
+ * mc_grads / mc_params: multicast addresses of the bucket; params: unicast bases (ranges that are not pushed);
+ * epoch_base / step_ptr: null for eager launches, device words for CUDA-graph replay. */
+int dfb_sync_nvls(const void* mc_grads, void* mc_params, void* const* params, void* const* sig, float* master, float* m, float* v,
+                  long n, long shard, int rank, int R, unsigned epoch, int opt_kind, float lr, float momentum, float beta1,
+                  float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi,
+                  const unsigned* epoch_base, const int* step_ptr, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

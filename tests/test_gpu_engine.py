@@ -205,3 +205,30 @@ def test_engine_cuda_graph_matches_eager(opt):
         out[graph] = [float(eng.step(x, y)) for x, y in batches]
         assert eng.version == 8
     assert max(abs(a - b) for a, b in zip(out[False], out[True])) < 2e-2, out
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_engine_state_resume_on_gpu(tmp_path, graph):
+    """bf16 working weights + fp32 master shards + Adam moments saved and restored: the resumed run continues the original
+    one step for step (eager and CUDA-graph mode, where the step counter lives in device memory)."""
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev(), generator=g)
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    conf = {"optimizer": "adam", "learningRate": 1e-3, "bucketBytes": 1 << 18, "cudaGraph": graph}
+    torch.manual_seed(0)
+    eng = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, conf, device=dev())
+    for _ in range(5):
+        eng.step(x, y)
+    eng.save_state(str(tmp_path))
+    cont = [float(eng.step(x, y)) for _ in range(4)]
+    torch.manual_seed(123)                                   # different initial weights: the state must replace them
+    eng2 = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, conf, device=dev())
+    eng2.load_state(str(tmp_path))
+    assert eng2.version == 5
+    resumed = [float(eng2.step(x, y)) for _ in range(4)]
+    assert max(abs(a - b) for a, b in zip(cont, resumed)) < 2e-3, (cont, resumed)
+    for a, b in zip(eng.full_precision_weights(), eng2.full_precision_weights()):
+        assert float((a - b).abs().max()) < 1e-4

@@ -146,3 +146,34 @@ def test_connect_and_upload_timeouts():
         c.emit("uploadVars", {}, 0.1)
     with pytest.raises(ConnectTimeout):
         c.wait_event("downloadVars", 0.1)
+
+
+def test_batch_norm_nhwc_cpu_matches_torch_and_fuses_add_relu():
+    """`ops.batch_norm_nhwc` (CPU statement of the fused CUDA op): BN over the last axis + residual + ReLU, running stats."""
+    import torch.nn.functional as F
+    from distriflow_b200 import ops
+    torch.manual_seed(0)
+    x, r = torch.randn(4, 5, 5, 8), torch.randn(4, 5, 5, 8)
+    g, b = torch.rand(8) + 0.5, torch.randn(8)
+    rm, rv = torch.zeros(8), torch.ones(8)
+    y = ops.batch_norm_nhwc(x, g, b, rm, rv, True, 0.1, 1e-5, "relu", r)
+    rm2, rv2 = torch.zeros(8), torch.ones(8)
+    ref = F.relu(F.batch_norm(x.permute(0, 3, 1, 2), rm2, rv2, g, b, True, 0.1, 1e-5).permute(0, 2, 3, 1) + r)
+    assert torch.allclose(y, ref, atol=1e-6) and torch.allclose(rm, rm2) and torch.allclose(rv, rv2)
+    ye = ops.batch_norm_nhwc(x, g, b, rm, rv, False, 0.1, 1e-5)
+    assert torch.allclose(ye, F.batch_norm(x.permute(0, 3, 1, 2), rm2, rv2, g, b, False, 0.1, 1e-5).permute(0, 2, 3, 1), atol=1e-6)
+
+
+def test_resnet20_cpu_forward_backward_and_keras_momentum():
+    from distriflow_b200.models.resnet import resnet20, resnet_loss
+    torch.manual_seed(0)
+    m = resnet20()
+    x, y = torch.randn(2, 32, 32, 3), torch.randint(0, 10, (2,))
+    loss = resnet_loss(m, x, y)
+    loss.backward()
+    assert torch.isfinite(loss) and all(p.grad is not None for p in m.parameters())
+    bn = m.stem.bn                       # Keras momentum 0.9 keeps 90 % of the old moving statistic
+    assert bn.momentum == 0.9 and not torch.equal(bn.moving_mean, torch.zeros_like(bn.moving_mean))
+    m.eval()
+    with torch.no_grad():
+        assert m(x).shape == (2, 10)
