@@ -81,6 +81,8 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "commCtas": 148,              # CTAs of the fused collective kernel (256 threads x <= 128 regs: co-resides with a GEMM CTA)
     "nvls": False,                # gradients reduced and weights broadcast inside the NVSwitch (multicast heap; bf16 only)
     "cudaGraph": False,           # capture the whole step (forward, backward, bucket kernels) into a CUDA graph after warm-up
+    "trace": False,               # CUDA-event phase timers + NVTX ranges (forward / backward / collective tail); eager steps only
+    "watchdogSeconds": 0.0,       # > 0: host thread reports a rank whose device-written step counter stops advancing
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
 }
 

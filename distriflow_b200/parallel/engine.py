@@ -18,7 +18,7 @@ Back ends: "p2p" = own kernels over peer memory (the product); "nccl" / "gloo" =
 from __future__ import annotations
 
 import math
-from typing import Any, Callable, Dict, List, Optional, Sequence
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 import torch.nn as nn
@@ -92,6 +92,15 @@ class DataParallelEngine:
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.device)
         self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.backend == "p2p"
+        self.tracer = None
+        if self.cfg["trace"]:
+            from ..utils.tracing import PhaseTimer
+            self.tracer = PhaseTimer(self.device)
+            self._graph_mode = False                       # events inside a captured graph cannot be timed: trace eagerly
+        self.watchdog = None
+        self._prog_pin = None
+        if float(self.cfg["watchdogSeconds"]) > 0:
+            self._start_watchdog(float(self.cfg["watchdogSeconds"]))
         self._graph, self._static_in, self._static_loss, self._warm, self._capturing, self._seq = None, None, None, 0, False, 0
         if self._graph_mode:
             self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -252,15 +261,22 @@ class DataParallelEngine:
         if self.device.type == "cuda" and self.world > 1 and self.backend == "p2p" and self.cfg["overlap"] and self.reserve_sms:
             from ..ops import dense as _lin
             _lin.set_max_ctas(_lin.NUM_SMS - self.reserve_sms)  # optionally leave SMs free for the collective kernels
-        loss = self.loss_fn(self.model, *batch)
-        loss.backward()
-        for b in self.buckets:                                 # anything not launched from a hook (unused params, overlap off)
-            if not getattr(b, "launched", False):
-                self._launch_bucket(b)
-        if self.device.type == "cuda":
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
-            from ..ops import dense as _lin
-            _lin.set_max_ctas(0)
+        tr = self.tracer
+        with (tr.phase("forward") if tr else _NULL):
+            loss = self.loss_fn(self.model, *batch)
+        with (tr.phase("backward") if tr else _NULL):          # bucket kernels launched from hooks overlap this phase
+            loss.backward()
+        with (tr.phase("collective_tail") if tr else _NULL):   # what is left of the gradient path after backward ends
+            for b in self.buckets:                             # anything not launched from a hook (unused params, overlap off)
+                if not getattr(b, "launched", False):
+                    self._launch_bucket(b)
+            if self.device.type == "cuda":
+                torch.cuda.current_stream().wait_stream(self.comm_stream)
+                from ..ops import dense as _lin
+                _lin.set_max_ctas(0)
+        if self._prog_pin is not None:                         # device-written progress word for the watchdog (capturable)
+            self._prog_dev.add_(1)
+            self._prog_pin.copy_(self._prog_dev, non_blocking=True)
         if self._graph_mode and self.world > 1:
             self._epoch_dev.add_(len(self.buckets))            # next step's barrier generations start after this step's
         if _count:
@@ -466,8 +482,52 @@ class DataParallelEngine:
         import os
         self.load_state_dict(torch.load(os.path.join(directory, "engine_state.pt"), map_location="cpu"))
 
+    # ------------------------------------------------------------------------------------ observability
+    def trace_summary(self) -> Dict[str, Dict[str, float]]:
+        """Per-phase device time (mean over steps, max over ranks); needs `trace: True`.  Collective."""
+        if self.tracer is None:
+            raise RuntimeError("engine was built without trace=True")
+        return self.tracer.summary(self.group)
+
+    def _start_watchdog(self, seconds: float) -> None:
+        from ..utils.tracing import ProgressWatchdog
+        if self.device.type == "cuda":
+            self._prog_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
+            self._prog_pin = torch.zeros(1, dtype=torch.int64).pin_memory()
+            read = lambda: int(self._prog_pin[0])              # noqa: E731  (written by the GPU at the end of every step)
+        else:
+            read = lambda: int(self.version)                   # noqa: E731
+        self.stall_reports: List[Tuple[int, float]] = []
+
+        def on_stall(last: int, secs: float) -> None:
+            self.stall_reports.append((last, secs))
+            import sys
+            print(f"[distriflow_b200] rank {self.rank}: no step completed for {secs:.1f} s (last finished step {last}); "
+                  f"a peer may be down or a collective is stuck", file=sys.stderr, flush=True)
+            for cb in self.stallCallbacks:
+                cb(self.rank, last, secs)
+
+        self.stallCallbacks: List[Callable[[int, int, float], None]] = []
+        self.watchdog = ProgressWatchdog(read, seconds, on_stall).start()
+
+    def on_stall(self, cb: Callable[[int, int, float], None]) -> None:
+        """`cb(rank, last_finished_step, seconds)` from the watchdog thread (needs `watchdogSeconds > 0`)."""
+        if self.watchdog is None:
+            raise RuntimeError("engine was built without watchdogSeconds > 0")
+        self.stallCallbacks.append(cb)
+
+    def close(self) -> None:
+        if self.watchdog is not None:
+            self.watchdog.stop()
+            self.watchdog = None
+
     def gpu_launches_per_step(self) -> int:
         return len(self.buckets)
+
+
+import contextlib as _contextlib
+
+_NULL = _contextlib.nullcontext()
 
 
 def _comm_sigs():

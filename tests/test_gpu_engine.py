@@ -232,3 +232,43 @@ def test_engine_state_resume_on_gpu(tmp_path, graph):
     assert max(abs(a - b) for a, b in zip(cont, resumed)) < 2e-3, (cont, resumed)
     for a, b in zip(eng.full_precision_weights(), eng2.full_precision_weights()):
         assert float((a - b).abs().max()) < 1e-4
+
+
+def test_engine_trace_phases_and_watchdog_counter_on_gpu():
+    """`trace: True` gives device-timed forward / backward / collective phases; the watchdog's progress word is written by
+    the GPU (pinned host memory) at the end of every step."""
+    import time
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev())
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    torch.manual_seed(0)
+    eng = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, {"optimizer": "adam", "learningRate": 1e-3, "trace": True,
+                                                             "watchdogSeconds": 0.3, "cudaGraph": True}, device=dev())
+    for _ in range(5):
+        eng.step(x, y)
+    s = eng.trace_summary()
+    assert set(s) == {"forward", "backward", "collective_tail"}
+    assert s["forward"]["count"] == 5 and s["forward"]["mean_ms"] > 0 and s["backward"]["mean_ms"] > 0
+    torch.cuda.synchronize()
+    assert int(eng._prog_pin[0]) == 5
+    time.sleep(0.9)
+    eng.close()
+    assert eng.stall_reports and eng.stall_reports[0][0] == 5
+
+
+def test_engine_watchdog_counter_inside_cuda_graph():
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev())
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    torch.manual_seed(0)
+    eng = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, {"optimizer": "sgd", "learningRate": 1e-2, "watchdogSeconds": 30.0,
+                                                             "cudaGraph": True}, device=dev())
+    for _ in range(7):                       # 3 eager + capture/replay + 3 replays
+        eng.step(x, y)
+    torch.cuda.synchronize()
+    eng.close()
+    assert eng._graph is not None and int(eng._prog_pin[0]) == 7 and eng.stall_reports == []
