@@ -87,6 +87,10 @@ def build(force: bool = False, jobs: int = 8, verbose: bool = False) -> str:
     os.replace(OUT + ".tmp", OUT)
     with open(stamp_file, "w") as f:
         f.write(stamp)
+    keep = set(objs)                                    # drop objects of older source revisions from the cache
+    for f in glob.glob(os.path.join(BUILD_DIR, "*.o")):
+        if f not in keep:
+            os.remove(f)
     return OUT
 
 
