@@ -118,6 +118,7 @@ struct SyncArgs {
   // CUDA-graph replay support: values that change from step to step are read from device memory instead of being baked in
   const uint32_t* epoch_base;  // if set (and epoch != 0): barrier generation = *epoch_base + epoch
   const int* step_ptr;         // if set: optimizer step count for Adam's bias correction
+  const float* lr_ptr;         // if set: learning rate (schedules keep working under a captured graph)
   OptParams opt;
 };
 
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(256) sync_rs_opt_ag_kernel(const SyncArgs a) {
   uint32_t epoch = a.epoch;
   if (epoch && a.epoch_base) epoch += *a.epoch_base;
   OptParams opt = a.opt;
+  if (a.lr_ptr != nullptr) opt.lr = *a.lr_ptr;
   if (a.step_ptr != nullptr && opt.kind == OPT_ADAM) {
     const float t = (float)max(*a.step_ptr, 1);
     opt.bias_c1 = 1.f - powf(opt.beta1, t);
@@ -284,6 +286,7 @@ __global__ void __launch_bounds__(256) sync_nvls_kernel(const NvlsArgs na) {
   uint32_t epoch = a.epoch;
   if (epoch && a.epoch_base) epoch += *a.epoch_base;
   OptParams opt = a.opt;
+  if (a.lr_ptr != nullptr) opt.lr = *a.lr_ptr;
   if (a.step_ptr != nullptr && opt.kind == OPT_ADAM) {
     const float t = (float)max(*a.step_ptr, 1);
     opt.bias_c1 = 1.f - powf(opt.beta1, t);
@@ -718,7 +721,7 @@ static int sync_impl(void* const* grads, void* const* params, void* const* sig, 
                      void* reduced_out, long n, long shard, int rank, int R, unsigned epoch, int push, int grad_dtype,
                      int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
                      float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, const unsigned* epoch_base,
-                     const int* step_ptr, cudaStream_t stream) {
+                     const int* step_ptr, const float* lr_ptr, cudaStream_t stream) {
   DFB_REQUIRE(R >= 1 && R <= kMaxRanks && rank >= 0 && rank < R, "sync: bad rank %d / world %d", rank, R);
   DFB_REQUIRE(shard > 0 && (shard % 8) == 0, "sync: shard must be a positive multiple of 8 elements");
   DFB_REQUIRE(shard * R >= n, "sync: shard * R must cover the bucket");
@@ -730,6 +733,7 @@ static int sync_impl(void* const* grads, void* const* params, void* const* sig, 
   DFB_REQUIRE(epoch == 0 || sig != nullptr, "sync: barriers need signal pads");
   a.master = master; a.m = m; a.v = v; a.reduced_out = reduced_out; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
   a.epoch = epoch; a.push = push; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi; a.epoch_base = epoch_base; a.step_ptr = step_ptr;
+  a.lr_ptr = lr_ptr;
   a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
   a.opt.weight_decay = weight_decay;
   a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));
@@ -767,18 +771,20 @@ DFB_API int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* co
                                int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2, float eps,
                                float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi, cudaStream_t stream) {
   return sync_impl(grads, params, sig, master, m, v, reduced_out, n, shard, rank, R, epoch, push, grad_dtype, param_dtype, opt_kind,
-                   lr, momentum, beta1, beta2, eps, weight_decay, step, ctas, nopush_lo, nopush_hi, nullptr, nullptr, stream);
+                   lr, momentum, beta1, beta2, eps, weight_decay, step, ctas, nopush_lo, nopush_hi, nullptr, nullptr, nullptr, stream);
 }
 
-// Same kernel for CUDA-graph replay: the barrier generation is *epoch_base + epoch and Adam's step count is *step_ptr, both
-// read on the device at run time, so one captured launch stays valid for every later step.
+// Same kernel for CUDA-graph replay: the barrier generation is *epoch_base + epoch, Adam's step count is *step_ptr and the
+// learning rate is *lr_ptr (nullable: then `lr`), all read on the device at run time, so one captured launch stays valid for
+// every later step and learning-rate schedules keep working.
 DFB_API int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* params, void* const* sig, float* master, float* m,
                                           float* v, long n, long shard, int rank, int R, unsigned epoch, int grad_dtype,
                                           int param_dtype, int opt_kind, float lr, float momentum, float beta1, float beta2,
                                           float eps, float weight_decay, int ctas, long nopush_lo, long nopush_hi,
-                                          const unsigned* epoch_base, const int* step_ptr, cudaStream_t stream) {
+                                          const unsigned* epoch_base, const int* step_ptr, const float* lr_ptr,
+                                          cudaStream_t stream) {
   return sync_impl(grads, params, sig, master, m, v, nullptr, n, shard, rank, R, epoch, 1, grad_dtype, param_dtype, opt_kind, lr,
-                   momentum, beta1, beta2, eps, weight_decay, 1, ctas, nopush_lo, nopush_hi, epoch_base, step_ptr, stream);
+                   momentum, beta1, beta2, eps, weight_decay, 1, ctas, nopush_lo, nopush_hi, epoch_base, step_ptr, lr_ptr, stream);
 }
 
 // NVLS variant (bf16 gradients and weights; `mc_grads` / `mc_params`: multicast addresses of the bucket's buffers, from
@@ -787,7 +793,8 @@ DFB_API int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* param
 DFB_API int dfb_sync_nvls(const void* mc_grads, void* mc_params, void* const* params, void* const* sig, float* master, float* m,
                           float* v, long n, long shard, int rank, int R, unsigned epoch, int opt_kind, float lr, float momentum,
                           float beta1, float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo,
-                          long nopush_hi, const unsigned* epoch_base, const int* step_ptr, cudaStream_t stream) {
+                          long nopush_hi, const unsigned* epoch_base, const int* step_ptr, const float* lr_ptr,
+                          cudaStream_t stream) {
   DFB_REQUIRE(R >= 2 && R <= kMaxRanks && rank >= 0 && rank < R, "nvls: bad rank %d / world %d", rank, R);
   DFB_REQUIRE(shard > 0 && (shard % 8) == 0 && shard * R >= n, "nvls: shard must be a multiple of 8 elements and cover the bucket");
   DFB_REQUIRE(mc_grads != nullptr && mc_params != nullptr && sig != nullptr && epoch != 0, "nvls: multicast addresses, signal pads and a barrier generation are required");
@@ -801,6 +808,7 @@ DFB_API int dfb_sync_nvls(const void* mc_grads, void* mc_params, void* const* pa
   fill_peers(a.sig, sig, R);
   a.master = master; a.m = m; a.v = v; a.reduced_out = nullptr; a.n = n; a.shard = shard; a.rank = rank; a.R = R;
   a.epoch = epoch; a.push = 1; a.nopush_lo = nopush_lo; a.nopush_hi = nopush_hi; a.epoch_base = epoch_base; a.step_ptr = step_ptr;
+  a.lr_ptr = lr_ptr;
   a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;
   a.opt.weight_decay = weight_decay;
   a.opt.bias_c1 = 1.f - powf(beta1, (float)(step < 1 ? 1 : step));

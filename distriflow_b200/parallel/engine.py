@@ -105,6 +105,7 @@ class DataParallelEngine:
         if self._graph_mode:
             self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
             self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._lr_dev = torch.full((1,), self.lr, dtype=torch.float32, device=self.device)
 
     # ------------------------------------------------------------------------------------ setup
     def _build_buckets(self, heap) -> None:
@@ -314,7 +315,7 @@ class DataParallelEngine:
                                       epoch, _OPT[c["optimizer"]], self.lr, c["momentum"], c["beta1"], c["beta2"], c["eps"],
                                       c["weightDecay"], self.version + 1, self.comm_ctas, b.nopush[0], b.nopush[1],
                                       ptr(self._epoch_dev) if graph else None, ptr(self._step_dev) if graph else None,
-                                      _lib.stream()), "dfb_sync_nvls")
+                                      ptr(self._lr_dev) if graph else None, _lib.stream()), "dfb_sync_nvls")
             self._launches += 1
             return
         if self._graph_mode:          # replayable launch: generation and step count are read from device memory
@@ -325,7 +326,8 @@ class DataParallelEngine:
                                                       self._seq if self.world > 1 else 0, dt(b.grad_buf), dt(b.param_buf),
                                                       _OPT[c["optimizer"]], self.lr, c["momentum"], c["beta1"], c["beta2"], c["eps"],
                                                       c["weightDecay"], self.comm_ctas if self.world > 1 else 148 * 4, b.nopush[0],
-                                                      b.nopush[1], ptr(self._epoch_dev), ptr(self._step_dev), _lib.stream()),
+                                                      b.nopush[1], ptr(self._epoch_dev), ptr(self._step_dev), ptr(self._lr_dev),
+                                                      _lib.stream()),
                       "dfb_sync_rs_opt_ag_replayable")
             self._launches += 1
             return
@@ -482,6 +484,13 @@ class DataParallelEngine:
         import os
         self.load_state_dict(torch.load(os.path.join(directory, "engine_state.pt"), map_location="cpu"))
 
+    def set_learning_rate(self, lr: float) -> None:
+        """Learning-rate schedules: takes effect at the next step, also when the step replays from a CUDA graph (the bucket
+        kernels then read the rate from device memory)."""
+        self.lr = float(lr)
+        if getattr(self, "_lr_dev", None) is not None:
+            self._lr_dev.fill_(self.lr)
+
     # ------------------------------------------------------------------------------------ observability
     def trace_summary(self) -> Dict[str, Dict[str, float]]:
         """Per-phase device time (mean over steps, max over ranks); needs `trace: True`.  Collective."""
@@ -544,11 +553,11 @@ def _comm_sigs():
         L.dfb_sync_rs_opt_ag_replayable.restype = c_int
         L.dfb_sync_rs_opt_ag_replayable.argtypes = [P, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
                                                     ctypes.c_uint, c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_float,
-                                                    c_float, c_int, ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p]
+                                                    c_float, c_int, ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p, c_void_p]
         L.dfb_sync_nvls.restype = c_int
         L.dfb_sync_nvls.argtypes = [c_void_p, c_void_p, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
                                     ctypes.c_uint, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int,
-                                    ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p]
+                                    ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p, c_void_p]
         L.dfb_allgather_push.restype = c_int
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int

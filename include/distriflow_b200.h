@@ -117,7 +117,8 @@ int dfb_sync_rs_opt_ag(void* const* grads, void* const* params, void* const* sig
 int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* params, void* const* sig, float* master, float* m, float* v,
                                   long n, long shard, int rank, int R, unsigned epoch, int grad_dtype, int param_dtype, int opt_kind,
                                   float lr, float momentum, float beta1, float beta2, float eps, float weight_decay, int ctas,
-                                  long nopush_lo, long nopush_hi, const unsigned* epoch_base, const int* step_ptr, void* stream);
+                                  long nopush_lo, long nopush_hi, const unsigned* epoch_base, const int* step_ptr,
+                                  const float* lr_ptr /* nullable: learning rate read on the device */, void* stream);
 int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
                        int ctas, void* stream);
 int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
@@ -177,11 +178,11 @@ int dfb_mc_bind_map(unsigned long long mc, unsigned long long mem, size_t bytes,
 int dfb_mc_release(unsigned long long mc, void* mc_va, size_t bytes);
 /* sync path through the switch: multimem.ld_reduce of the gradients, multimem.st of the refreshed weights (bf16 only).
  * mc_grads / mc_params: multicast addresses of the bucket; params: unicast bases (ranges that are not pushed);
- * epoch_base / step_ptr: null for eager launches, device words for CUDA-graph replay. */
+ * epoch_base / step_ptr / lr_ptr: null for eager launches, device words for CUDA-graph replay. */
 int dfb_sync_nvls(const void* mc_grads, void* mc_params, void* const* params, void* const* sig, float* master, float* m, float* v,
                   long n, long shard, int rank, int R, unsigned epoch, int opt_kind, float lr, float momentum, float beta1,
                   float beta2, float eps, float weight_decay, int step, int ctas, long nopush_lo, long nopush_hi,
-                  const unsigned* epoch_base, const int* step_ptr, void* stream);
+                  const unsigned* epoch_base, const int* step_ptr, const float* lr_ptr, void* stream);
 
 #ifdef __cplusplus
 }

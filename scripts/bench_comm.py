@@ -66,7 +66,7 @@ def main():
             go, po = offs[i % nbuf]
             epoch[0] += 1
             check(L.dfb_sync_nvls(heap.mc_ptr(go), heap.mc_ptr(po), heap.ptrs(po), heap.ptrs(0), ptr(master), ptr(m), ptr(v), n, shard,
-                                  rank, world, epoch[0], _OPT[a.opt], 1e-3, 0.9, 0.9, 0.999, 1e-8, 0.0, 1, a.ctas, 0, 0, None, None,
+                                  rank, world, epoch[0], _OPT[a.opt], 1e-3, 0.9, 0.9, 0.999, 1e-8, 0.0, 1, a.ctas, 0, 0, None, None, None,
                                   _lib.stream()), "sync_nvls")
 
         gl = [torch.randn(n, device=dev).bfloat16() for _ in range(nbuf)]

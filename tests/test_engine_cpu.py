@@ -123,3 +123,17 @@ def test_engine_gloo_two_ranks_equal_one_rank_on_the_global_batch(tmp_path):
     assert torch.equal(w2, res["w"])
     a, b = float(again.step(*_batch(200, 16))), float(solo.step(*_batch(200, 16)))
     assert abs(a - b) < 1e-5
+
+
+def test_set_learning_rate_takes_effect_on_cpu():
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    eng = DataParallelEngine(_net(4), _loss, {"optimizer": "sgd", "learningRate": 0.1, "dtype": "fp32", "gradDtype": "fp32"},
+                             device=torch.device("cpu"))
+    eng.step(*_batch(0))
+    w0 = [t.clone() for t in eng.full_precision_weights()]
+    eng.set_learning_rate(0.0)
+    eng.step(*_batch(1))
+    assert all(torch.equal(a, b) for a, b in zip(w0, eng.full_precision_weights()))
+    eng.set_learning_rate(0.1)
+    eng.step(*_batch(2))
+    assert not all(torch.equal(a, b) for a, b in zip(w0, eng.full_precision_weights()))

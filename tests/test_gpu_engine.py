@@ -272,3 +272,28 @@ def test_engine_watchdog_counter_inside_cuda_graph():
     torch.cuda.synchronize()
     eng.close()
     assert eng._graph is not None and int(eng._prog_pin[0]) == 7 and eng.stall_reports == []
+
+
+def test_learning_rate_schedule_reaches_replayed_graph():
+    """`set_learning_rate` under `cudaGraph`: the captured bucket kernels read the rate from device memory."""
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev())
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    torch.manual_seed(0)
+    eng = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, {"optimizer": "sgd", "learningRate": 0.05, "cudaGraph": True},
+                             device=dev())
+    for _ in range(5):
+        eng.step(x, y)
+    assert eng._graph is not None
+    w0 = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
+    eng.set_learning_rate(0.0)
+    for _ in range(2):
+        eng.step(x, y)
+    w1 = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
+    assert torch.equal(w0, w1), "rate 0 must freeze the weights in replayed steps"
+    eng.set_learning_rate(0.05)
+    eng.step(x, y)
+    w2 = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
+    assert not torch.equal(w1, w2)
