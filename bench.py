@@ -161,7 +161,8 @@ def main():
         if args.mode == "async":
             from distriflow_b200.parallel.async_engine import AsyncEngine
             engine = AsyncEngine(model, loss_fn, {"optimizer": args.optimizer if args.optimizer != "adam" else "sgd",
-                                                  "learningRate": 1e-3, "maximumStaleness": 4, "mode": "async"},
+                                                  "learningRate": 1e-3, "maximumStaleness": 4, "mode": "async",
+                                                  "cudaGraph": args.graph},
                                  rank=rank, world=world, device=device)
         else:
             from distriflow_b200.parallel.engine import DataParallelEngine
@@ -184,7 +185,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    prep = 4 if (args.graph and args.impl == "ours" and args.mode == "sync") else 0
+    prep = 4 if (args.graph and args.impl == "ours") else 0
     for i in range(prep):                      # engine set-up: 3 eager steps + the graph capture; never timed, not counted in W
         step(*dev[i % len(dev)])
     for i in range(args.warmup):

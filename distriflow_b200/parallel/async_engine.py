@@ -194,18 +194,52 @@ class AsyncEngine:
 
             p.register_post_accumulate_grad_hook(hook)
         self.version = 0
+        # whole-step CUDA graph (pull -> fit -> push -> apply): every argument of the async kernels is constant from step to
+        # step (versions, buffer choice and the staleness decision live in device memory), except Adam's step count
+        self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.cfg["optimizer"] != "adam"
+        self._graph, self._static_in, self._static_loss, self._warm, self._graph_native = None, None, None, 0, 0
         if world > 1:
             import torch.distributed as dist
             dist.barrier(group=group)
 
-    def step(self, *batch: Any) -> torch.Tensor:
+    def _step_body(self, *batch: Any) -> torch.Tensor:
         self.state.pull()
         loss = self.loss_fn(self.model, *batch)
         loss.backward()
         self.state.push(None, self.grad_flat)
         self.state.apply()
-        self.version += 1
         return loss.detach()
+
+    def step(self, *batch: Any) -> torch.Tensor:
+        """pull -> fit -> push -> apply.  With `cudaGraph: True` (SGD / momentum) the step is captured after three eager
+        steps and replayed; input shapes must then stay fixed."""
+        if not self._graph_mode:
+            loss = self._step_body(*batch)
+            self.version += 1
+            return loss
+        if self._graph is None:
+            if self._warm < 3:
+                self._warm += 1
+                loss = self._step_body(*batch)
+                self.version += 1
+                return loss
+            self._static_in = [t.clone() if isinstance(t, torch.Tensor) else t for t in batch]
+            torch.cuda.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            n0 = _lib.LAUNCHES[0]
+            with torch.cuda.graph(self._graph):
+                self._static_loss = self._step_body(*self._static_in)
+            self._graph_native = _lib.LAUNCHES[0] - n0
+            _lib.LAUNCHES[0] = n0
+            self.state.steps -= 1                            # the capture pass launched nothing
+        for dst, src in zip(self._static_in, batch):
+            if isinstance(dst, torch.Tensor):
+                dst.copy_(src, non_blocking=True)
+        self._graph.replay()
+        _lib.LAUNCHES[0] += self._graph_native
+        self.state.steps += 1
+        self.version += 1
+        return self._static_loss
 
     def run_dataset(self, wq, x_all: torch.Tensor, y_all: torch.Tensor, batch_size: int, max_steps: int = 1 << 30,
                     on_step: Optional[Callable[[int, torch.Tensor], None]] = None) -> int:

@@ -98,7 +98,7 @@ def test_sync_engine_nvls_matches_p2p(tmp_path):
     assert res["fused"] and res["working_equals_master"]
 
 
-def _async_worker(rank, world, port, out):
+def _async_worker(rank, world, port, out, graph=False):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.cuda.set_device(rank)
@@ -111,7 +111,8 @@ def _async_worker(rank, world, port, out):
     net = mnist_cnn(10, softmax_output=False, dropout=False).to(dev)
     ce = get_loss("softmaxCrossEntropy")
     eng = AsyncEngine(net, lambda m, x, y: ce(y, m(x)), {"optimizer": "sgd", "learningRate": 1e-3, "maximumStaleness": 4,
-                                                          "dtype": "fp32", "gradDtype": "fp32"}, rank=rank, world=world, device=dev)
+                                                          "dtype": "fp32", "gradDtype": "fp32", "cudaGraph": graph},
+                      rank=rank, world=world, device=dev)
     g = torch.Generator().manual_seed(rank)
     steps = 12
     losses = []
@@ -128,13 +129,14 @@ def _async_worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-def test_async_engine_invariants_two_gpus(tmp_path):
+@pytest.mark.parametrize("graph", [False, True])
+def test_async_engine_invariants_two_gpus(tmp_path, graph):
     import torch.multiprocessing as mp
     world = 2
     if torch.cuda.device_count() < world:
         pytest.skip("not enough GPUs")
     out = str(tmp_path / "res.pt")
-    mp.spawn(_async_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    mp.spawn(_async_worker, args=(world, _free_port(), out, graph), nprocs=world, join=True)
     res = torch.load(out)
     for c in res["counters"]:
         # every push to this shard was either applied or refused by the staleness guard: nothing lost
