@@ -13,7 +13,7 @@ restatement on CPU tensors.
 from __future__ import annotations
 
 import math
-from typing import Optional, Sequence, Tuple
+from typing import Optional
 
 import torch
 import torch.nn as nn

@@ -11,7 +11,6 @@ from typing import List, Sequence
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from .. import ops
 from . import layers as L

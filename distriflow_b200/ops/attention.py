@@ -27,11 +27,16 @@ class _PackedAttention(torch.autograd.Function):
         B, T, C3 = qkv.shape
         D = C3 // (3 * n_head)
         base = qkv.detach().contiguous().view(B, T, 3, n_head, D)
-        q, k, v = (base[:, :, i].permute(0, 2, 1, 3).requires_grad_() for i in range(3))
-        with torch.enable_grad():
-            o = F.scaled_dot_product_attention(q, k, v, is_causal=True)          # [B,H,T,D] logical
-        ctx.inner = (q, k, v, o)
+        q, k, v = (base[:, :, i].permute(0, 2, 1, 3) for i in range(3))
         ctx.dims = (B, T, n_head, D)
+        if ctx.needs_input_grad[0]:
+            q, k, v = (t.requires_grad_() for t in (q, k, v))
+            with torch.enable_grad():
+                o = F.scaled_dot_product_attention(q, k, v, is_causal=True)      # [B,H,T,D] logical
+            ctx.inner = (q, k, v, o)
+        else:                                                                    # inference: no graph, nothing retained
+            o = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+            ctx.inner = None
         od = o.detach()
         if _bthd_dense(od, B, n_head, T, D):
             return od.permute(0, 2, 1, 3).reshape(B, T, n_head * D)              # a view: memory is already [B,T,H,D]

@@ -9,7 +9,7 @@ Replaces K2/K4 of SURVEY §2.5.
 from __future__ import annotations
 
 import ctypes
-from typing import Optional, Tuple
+from typing import Tuple
 
 import torch
 

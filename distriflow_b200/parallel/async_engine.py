@@ -18,7 +18,6 @@ training loop: device work-queue ticket -> gather batch -> pull -> fit -> push -
 """
 from __future__ import annotations
 
-import ctypes
 from typing import Any, Callable, Dict, List, Optional
 
 import torch
@@ -26,9 +25,9 @@ import torch.nn as nn
 
 from ..config import engine_config
 from ..ops import _lib
-from ..ops._lib import c_void_p, check, dt, ptr
+from ..ops._lib import check, dt, ptr
 from .engine import _OPT, _TORCH_DT, _comm_sigs, _round_up
-from .symm import PAD_BYTES, SymmetricHeap
+from .symm import SymmetricHeap
 
 __all__ = ["AsyncShardState", "AsyncEngine"]
 

@@ -17,8 +17,7 @@ Back ends: "p2p" = own kernels over peer memory (the product); "nccl" / "gloo" =
 """
 from __future__ import annotations
 
-import math
-from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.nn as nn

@@ -26,9 +26,8 @@ import os
 import time
 from typing import Any, Callable, Dict, List, Optional, Set
 
-import torch
 
-from .checkpoint import DistriServerInMemoryModel, DistriServerTorchModel, is_distributed_server_model
+from .checkpoint import DistriServerTorchModel, is_distributed_server_model
 from .config import client_hyperparams, server_hyperparams
 from .dataset import DistriDataset, batch_to_data_msg
 from .messages import DataMsg, DownloadMsg, Events, GradientMsg, ModelMsg, UploadMsg

@@ -27,7 +27,7 @@ from .config import DEFAULT_CLIENT_HYPERPARAMS, client_hyperparams
 from .messages import DownloadMsg, Events, GradientMsg, UploadMsg
 from .model import DistriModel, DistriTorchModel
 from .serialization import deserialize_var, serialize_vars
-from .transport import AckTimeout, ConnectTimeout, TcpClientEndpoint
+from .transport import AckTimeout, TcpClientEndpoint
 
 __all__ = ["AbstractClient", "AsynchronousSGDClient", "FederatedClient", "DistriWorker",
            "DistriClientTorchModel", "is_distributed_client_model", "add_rows", "concat_with_empty",

@@ -52,3 +52,18 @@ def test_server_and_two_clients_over_tcp():
         c.join(60)
     st.join(60)
     assert not st.is_alive() and not any(c.is_alive() for c in cs)
+
+
+def test_bench_reference_arm_reports_unavailable():
+    """`bench.py --impl reference` contract: one JSON line with `"impl": "reference"` and `"unavailable"`, exit code 0
+    (the reference is TypeScript on tf.js / socket.io and cannot be installed offline)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "2",
+                        "--warmup", "1"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and isinstance(line["unavailable"], str) and line["unavailable"]
