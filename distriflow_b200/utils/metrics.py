@@ -70,21 +70,28 @@ class ThroughputMeter:
 
     def __init__(self, samples_per_step: int, grad_bytes: int = 0, world: int = 1):
         self.samples, self.grad_bytes, self.world = samples_per_step, grad_bytes, world
-        self.e0 = torch.cuda.Event(enable_timing=True)
-        self.e1 = torch.cuda.Event(enable_timing=True)
-        self.steps = 0
+        self.cuda = torch.cuda.is_available()            # host clock on a CPU-only box (plumbing configs)
+        if self.cuda:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+        self.steps, self._t0 = 0, 0.0
 
     def start(self) -> None:
-        self.e0.record()
+        if self.cuda:
+            self.e0.record()
+        self._t0 = time.perf_counter()
         self.steps = 0
 
     def step(self) -> None:
         self.steps += 1
 
     def stop(self) -> Dict[str, float]:
-        self.e1.record()
-        self.e1.synchronize()
-        ms = self.e0.elapsed_time(self.e1)
+        if self.cuda:
+            self.e1.record()
+            self.e1.synchronize()
+            ms = self.e0.elapsed_time(self.e1)
+        else:
+            ms = (time.perf_counter() - self._t0) * 1e3
         per = ms / max(self.steps, 1)
         bus = 2.0 * (self.world - 1) / self.world * self.grad_bytes / (per * 1e-3) / 1e9 if self.world > 1 else 0.0
         return {"ms_per_step": per, "samples_per_sec": self.samples * self.world / (per * 1e-3), "grad_bus_gbs": bus}
@@ -98,3 +105,12 @@ class JsonlLogger:
         kw.setdefault("ts", time.time())
         self.f.write(json.dumps(kw) + "\n")
         self.f.flush()
+
+    def close(self) -> None:
+        self.f.close()
+
+    def __enter__(self) -> "JsonlLogger":
+        return self
+
+    def __exit__(self, *exc: Any) -> None:
+        self.close()

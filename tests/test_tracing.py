@@ -74,3 +74,23 @@ def test_engine_trace_and_watchdog_on_cpu():
     time.sleep(0.6)                            # no more steps: the watchdog reports the stall after version 3
     eng.close()
     assert seen and seen[0] == (0, 3) and eng.stall_reports[0][0] == 3
+
+
+def test_throughput_meter_and_jsonl_logger_on_cpu(tmp_path):
+    import json
+    from distriflow_b200.utils.metrics import JsonlLogger, ThroughputMeter
+    if torch.cuda.is_available():
+        pytest.skip("host-clock branch is for CPU-only boxes")
+    m = ThroughputMeter(samples_per_step=32, grad_bytes=1 << 20, world=2)
+    m.start()
+    for _ in range(4):
+        time.sleep(0.005)
+        m.step()
+    r = m.stop()
+    assert r["ms_per_step"] >= 4.5 and r["samples_per_sec"] > 0 and r["grad_bus_gbs"] > 0
+    path = str(tmp_path / "log.jsonl")
+    with JsonlLogger(path) as log:
+        log.log(step=1, loss=0.5)
+        log.log(step=2, loss=0.25, version="v2")
+    rows = [json.loads(line) for line in open(path)]
+    assert [r["step"] for r in rows] == [1, 2] and rows[1]["version"] == "v2" and "ts" in rows[0]
