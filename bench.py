@@ -133,6 +133,8 @@ def build_workload(args, device, torch):
 def main():
     args = parse()
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:          # launched under torchrun for N > 1: one line, from rank 0
+            return 0
         print(json.dumps({"impl": "reference", "unavailable": "reference is TypeScript on tf.js/socket.io: no setup.py/pyproject "
                           "(pip: 'not installable'), and node/npm/tfjs are absent offline; see DESIGN.md"}))
         return 0
