@@ -177,3 +177,39 @@ def test_resnet20_cpu_forward_backward_and_keras_momentum():
     m.eval()
     with torch.no_grad():
         assert m(x).shape == (2, 10)
+
+
+def test_converter_style_checkpoint_with_manifest_groups_and_shards(tmp_path):
+    """The layout of the reference's `experiment/mnist/model.json`: topology wrapped with
+    `keras_version` / `backend` / `model_config`, several manifest groups, each with its own shard files."""
+    import json
+    import numpy as np
+    from distriflow_b200 import load_layers_model
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.models.topology import topology_from_model
+    torch.manual_seed(0)
+    src = mnist_mlp()
+    topo = topology_from_model(src)
+    named = [(n, p.detach().numpy()) for n, p in
+             [(f"{layer.layer_name}/{k}", getattr(layer, k)) for layer in src.layers if hasattr(layer, "kernel")
+              for k in ("kernel", "bias")]]
+    groups = [named[:2], named[2:]]
+    manifest = []
+    for gi, grp in enumerate(groups, 1):
+        blob = b"".join(np.ascontiguousarray(a, dtype="<f4").tobytes() for _, a in grp)
+        half = len(blob) // 2 // 4 * 4
+        paths = [f"group{gi}-shard1of2", f"group{gi}-shard2of2"]          # a tensor may straddle two shards
+        (tmp_path / paths[0]).write_bytes(blob[:half])
+        (tmp_path / paths[1]).write_bytes(blob[half:])
+        manifest.append({"paths": paths, "weights": [{"name": n, "shape": list(a.shape), "dtype": "float32"} for n, a in grp]})
+    wrapped = {"keras_version": "2.1.4", "backend": "tensorflow", "model_config": topo.get("model_config", topo),
+               "training_config": {"loss": "categorical_crossentropy"}}
+    (tmp_path / "model.json").write_text(json.dumps({"modelTopology": wrapped, "weightsManifest": manifest}))
+    dst = load_layers_model(str(tmp_path))
+    x = torch.rand(3, 28, 28, 1)
+    assert torch.allclose(dst(x), src(x), atol=1e-6)
+    # a manifest that promises more bytes than the shards hold is an error, not a silent truncation
+    manifest[1]["weights"][-1]["shape"] = [1000]
+    (tmp_path / "model.json").write_text(json.dumps({"modelTopology": wrapped, "weightsManifest": manifest}))
+    with pytest.raises(ValueError):
+        load_layers_model(str(tmp_path))
