@@ -206,3 +206,30 @@ def test_async_over_tcp_two_workers():
     for w in ws:
         w.dispose()
     ep.close()
+
+
+def test_worker_crash_mid_batch_is_reissued_to_the_survivor():
+    """Fault injection (failure detection): a worker takes a micro-batch and disconnects without uploading.
+    The server notices the disconnect (`numClients`), the batch stays in the incomplete set and the dispatcher re-issues it
+    to the surviving worker (reference: `dataset.ts:57-60`, `asynchronousSGD_server.ts:54-57`)."""
+    x, y = _data(96, seed=11)                       # 3 micro-batches per epoch
+    hub = LoopbackHub()
+    smodel = DistriServerInMemoryModel(mnist_mlp(), {"loss": "softmaxCrossEntropy", "learningRate": 0.001})
+    ds = DistriDataset(x, y, {"batchSize": 32, "epochs": 1})
+    server = AsynchronousSGDServer(hub, smodel, ds)
+    done_batches = []
+    server.on_upload(lambda m: done_batches.append(m.batch))
+    server.setup()
+    crasher = AsynchronousSGDClient(hub.client, mnist_mlp(), {"clientId": "crasher"})
+    crasher.setup(process_first=False)             # connected: holds micro-batch 0, never computes it
+    held = crasher.msg.data.batch
+    survivor = AsynchronousSGDClient(hub.client, mnist_mlp(), {"clientId": "survivor"})
+    survivor.setup(process_first=False)
+    assert server.numClients == 2
+    crasher.dispose()                              # the crash
+    hub.pump()
+    assert server.numClients == 1
+    n = survivor.run()
+    assert ds.next().done, "the epoch must still complete"
+    assert sorted(done_batches) == [0, 1, 2] and held in done_batches and n == 3
+    assert server.workerIDs == {"survivor"}        # the crasher never delivered anything
