@@ -335,8 +335,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + acc * BLOCK_N;
+      // column chunks that lie entirely beyond N are never read, converted or stored (thin outputs: ResNet-20's 16-channel
+      // layers use one chunk of a 128-wide tile, and their tiles are epilogue-bound: 3 k-blocks of MMA per tile)
+      const int live_chunks = min(kChunks, ceil_div(p.N - n0, kChunkN));
 #pragma unroll 1
-      for (int c = 0; c < kChunks; ++c) {
+      for (int c = 0; c < live_chunks; ++c) {
         float v[kChunkN];
         {
           uint32_t r[32];
@@ -353,7 +356,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
         }
-        if (c == kChunks - 1) {                        // whole accumulator is in registers: release TMEM early
+        if (c == live_chunks - 1) {                    // whole accumulator is in registers: release TMEM early
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tmem_empty[acc]);
