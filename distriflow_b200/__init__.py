@@ -22,5 +22,6 @@ from .transport import LoopbackHub, TcpClientEndpoint, TcpServerEndpoint
 from .server import AbstractServer, AsynchronousSGDServer, DistriServer, FederatedServer, SynchronousSGDServer
 from .worker import (AbstractClient, AsynchronousSGDClient, DistriClientTorchModel, DistriWorker, FederatedClient,
                      is_distributed_client_model)
+from .trainer import Trainer
 
 __version__ = "0.1.0"
