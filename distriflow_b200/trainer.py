@@ -141,11 +141,21 @@ class Trainer:
         step = int(eng.version)                              # steps already applied = position in the data stream
         start, done_now, last_loss = step, 0, None
         every = int(self.cfg["checkpointEvery"])
+        dev = getattr(eng, "device", torch.device("cpu"))
+
+        def stream_of_batches():
+            s = step
+            while s < total:
+                yield self.batch(s % self.batches)
+                s += 1
+
+        from .utils.prefetch import DevicePrefetcher
+        feed = DevicePrefetcher(stream_of_batches(), dev, depth=2)      # pass-through on CPU; H2D on a copy stream on CUDA
         while step < total and (max_steps is None or done_now < max_steps):
             epoch, b = divmod(step, self.batches)
             if self.lr_schedule is not None:
                 eng.set_learning_rate(float(self.lr_schedule(step)))
-            xb, yb = self.batch(b)
+            xb, yb = next(feed)
             last_loss = eng.step(xb, yb)
             step += 1
             done_now += 1

@@ -297,3 +297,40 @@ def test_learning_rate_schedule_reaches_replayed_graph():
     eng.step(x, y)
     w2 = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
     assert not torch.equal(w1, w2)
+
+
+def test_trainer_on_gpu_with_host_data_prefetch_and_resume(tmp_path):
+    """`Trainer` over host-resident data: batches reach the GPU through `DevicePrefetcher` (pinned memory, copy stream); an
+    interrupted run resumed from `<saveDir>/current` ends with the weights of the uninterrupted one."""
+    from distriflow_b200 import Trainer
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    from distriflow_b200.utils.prefetch import DevicePrefetcher
+    g = torch.Generator().manual_seed(1)
+    x = torch.rand(96, 28, 28, 1, generator=g)
+    y = torch.randint(0, 10, (96,), generator=g)
+    pf = DevicePrefetcher([(x[i:i + 32], y[i:i + 32]) for i in range(0, 96, 32)], dev(), depth=2)
+    got = list(pf)
+    assert len(got) == 3 and all(t.device == dev() for b in got for t in b) and pf.h2d_bytes == x.numel() * 4 + y.numel() * 8
+    torch.cuda.synchronize()
+    assert torch.equal(torch.cat([b[0] for b in got]).cpu(), x) and torch.equal(torch.cat([b[1] for b in got]).cpu(), y)
+
+    ce = get_loss("softmaxCrossEntropy")
+    conf = {"optimizer": "momentum", "learningRate": 0.01, "dtype": "fp32", "gradDtype": "fp32"}
+    tconf = {"batchSize": 32, "epochs": 4, "checkpointEvery": 5}
+
+    def make(seed):
+        torch.manual_seed(seed)
+        return DataParallelEngine(mnist_mlp(softmax_output=False).to(dev()), lambda m, a, b: ce(b, m(a)), conf, device=dev())
+
+    ref = make(0)
+    Trainer(ref, x, y, tconf).fit()
+    first = make(0)
+    out1 = Trainer(first, x, y, {**tconf, "saveDir": str(tmp_path)}).fit(max_steps=7)
+    assert out1["steps"] == 7 and not out1["finished"]
+    second = make(9)
+    out2 = Trainer(second, x, y, {**tconf, "saveDir": str(tmp_path)}).fit()
+    assert out2["resumed_from"] == 7 and out2["steps"] == 12 and out2["finished"]
+    for a, b in zip(ref.full_precision_weights(), second.full_precision_weights()):
+        assert float((a - b).abs().max()) < 1e-5

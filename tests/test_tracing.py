@@ -94,3 +94,22 @@ def test_throughput_meter_and_jsonl_logger_on_cpu(tmp_path):
         log.log(step=2, loss=0.25, version="v2")
     rows = [json.loads(line) for line in open(path)]
     assert [r["step"] for r in rows] == [1, 2] and rows[1]["version"] == "v2" and "ts" in rows[0]
+
+
+def test_device_prefetcher_is_a_pass_through_on_cpu():
+    from distriflow_b200.utils.prefetch import DevicePrefetcher
+    batches = [(torch.full((2, 3), float(i)), torch.tensor([i])) for i in range(5)]
+    pulled = []
+
+    def gen():
+        for b in batches:
+            pulled.append(int(b[1]))
+            yield b
+
+    pf = DevicePrefetcher(gen(), torch.device("cpu"), depth=2)
+    first = next(pf)
+    assert first[0] is batches[0][0] and pulled == [0, 1, 2]          # depth 2 staged, then refilled after handing one out
+    rest = list(pf)
+    assert [int(b[1]) for b in rest] == [1, 2, 3, 4] and pf.h2d_bytes == 0
+    with pytest.raises(ValueError):
+        DevicePrefetcher([], torch.device("cpu"), depth=0)
