@@ -129,3 +129,22 @@ def test_trainer_two_ranks_slice_the_global_batch(tmp_path):
     Trainer(solo, *_data(64), {"batchSize": 8, "epochs": 2}).fit()           # one rank on the same global batches
     assert torch.allclose(_weights(solo), res["w"], atol=1e-5)
     assert os.path.exists(os.path.join(str(tmp_path), "ck", "current", "engine_state.pt"))
+
+
+def test_command_line_trainer_on_cpu(tmp_path, capsys):
+    from distriflow_b200 import train
+    rc = train.main(["--model", "mnist-mlp", "--device", "cpu", "--epochs", "2", "--batch", "16", "--examples", "64",
+                     "--optimizer", "momentum", "--lr", "0.0005", "--warmup-steps", "3", "--save-dir", str(tmp_path / "ck"),
+                     "--checkpoint-every", "3", "--log", str(tmp_path / "log.jsonl"), "--trace"])
+    assert rc == 0
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert out["steps"] == 8 and out["finished"] and out["version"] == 8 and out["device"] == "cpu"
+    assert set(out["phases_ms"]) == {"forward", "backward", "collective_tail"}
+    assert os.path.exists(tmp_path / "ck" / "current" / "model.json")
+    rows = [json.loads(line) for line in open(tmp_path / "log.jsonl")]
+    assert abs(rows[0]["lr"] - 0.0005 / 3) < 1e-12 and rows[-1]["lr"] == 0.0005
+    # a second invocation finds the finished run and has nothing left to do
+    rc = train.main(["--model", "mnist-mlp", "--device", "cpu", "--epochs", "2", "--batch", "16", "--examples", "64",
+                     "--optimizer", "momentum", "--save-dir", str(tmp_path / "ck")])
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert rc == 0 and out["resumed_from"] == 8 and out["steps_this_call"] == 0
