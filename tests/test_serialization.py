@@ -49,3 +49,32 @@ def test_flat_format():
     back = flat_deserialize(data, meta)
     for a, b in zip(ts, back):
         assert a.dtype == b.dtype and torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------------------------- randomized round trips
+from hypothesis import given, settings, strategies as st    # noqa: E402
+
+
+@settings(max_examples=80, deadline=None)
+@given(shape=st.lists(st.integers(min_value=0, max_value=5), min_size=0, max_size=4),
+       dtype=st.sampled_from(["float32", "int32", "bool", "uint8", "float16", "int64"]), seed=st.integers(0, 10 ** 6))
+def test_serialize_round_trip_any_shape_and_dtype(shape, dtype, seed):
+    """`serializeVar` / `deserializeVar` (`/root/reference/src/common/utils.ts:32-51`) for every dtype of the table, scalars
+    and empty tensors included; the flat format (`server/models.ts:236-267`) must give the same tensors back in order."""
+    import numpy as np
+    import torch
+    from distriflow_b200 import deserialize_var, flat_deserialize, flat_serialize, serialize_var
+    from distriflow_b200.serialization import DTYPES
+    if dtype not in DTYPES:
+        return
+    rng = np.random.default_rng(seed)
+    arr = (rng.random(shape) * 100).astype(np.dtype(DTYPES[dtype][0])) if dtype != "bool" else rng.random(shape) > 0.5
+    arr = np.asarray(arr).reshape(shape)             # (ascontiguousarray would promote a scalar to 1-d)
+    t = torch.from_numpy(arr.copy())
+    s = serialize_var(t)
+    assert s.dtype == dtype and list(s.shape) == list(shape) and len(bytes(s.data)) == arr.nbytes
+    back = deserialize_var(s)
+    assert back.dtype == t.dtype and tuple(back.shape) == tuple(t.shape) and torch.equal(back, t)
+    data, meta = flat_serialize([t, t.reshape(-1)])
+    a, b = flat_deserialize(data, meta)
+    assert torch.equal(a, t) and torch.equal(b, t.reshape(-1))
