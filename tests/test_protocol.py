@@ -233,3 +233,46 @@ def test_worker_crash_mid_batch_is_reissued_to_the_survivor():
     assert ds.next().done, "the epoch must still complete"
     assert sorted(done_batches) == [0, 1, 2] and held in done_batches and n == 3
     assert server.workerIDs == {"survivor"}        # the crasher never delivered anything
+
+
+@pytest.mark.parametrize("workers,bound,seed", [(2, 0, 1), (3, 1, 2), (4, 2, 3), (3, 1 << 30, 4)])
+def test_async_server_invariants_under_random_worker_order(workers, bound, seed):
+    """Bounded-staleness async SGD with workers advancing in random order: uploads = applied + dropped, every micro-batch
+    of every epoch is completed (re-issued ones possibly twice), no accepted gradient is staler than the bound, versions
+    only move forward.  (The reference checks none of this: `asynchronousSGD_server.ts:65-108`)"""
+    import random
+    rng = random.Random(seed)
+    x, y = _data(160, seed=seed)                     # 5 micro-batches per epoch
+    hub = LoopbackHub()
+    smodel = DistriServerInMemoryModel(mnist_mlp(), {"loss": "softmaxCrossEntropy", "learningRate": 0.001})
+    ds = DistriDataset(x, y, {"batchSize": 32, "epochs": 2})
+    server = AsynchronousSGDServer(hub, smodel, ds, {"serverHyperparams": {"maximumStaleness": bound}})
+    accepted, versions = [], []
+    orig_update = server.update_model
+
+    def spy(grads, weight=1.0):
+        accepted.append(server.staleness_of(grads.version))
+        return orig_update(grads, weight)
+
+    server.update_model = spy
+    server.on_new_version(lambda old, new: versions.append((old, new)))
+    server.setup()
+    ws = [AsynchronousSGDClient(hub.client, mnist_mlp(False), {"modelCompileConfig": {"loss": "softmaxCrossEntropy"},
+                                                               "clientId": f"w{i}"}) for i in range(workers)]
+    for w in ws:
+        w.setup(process_first=False)
+    idle = 0
+    while idle < 3 * workers:
+        w = rng.choice(ws)
+        idle = 0 if w.step() else idle + 1
+    assert ds.next().done and ds.epoch == 2
+    assert server.numUpdates == len(accepted) + server.numDropped
+    # every micro-batch of both epochs was completed; a batch re-issued at the end of an epoch while its first holder was
+    # still computing yields a second, equally valid gradient, which is applied like the reference does
+    # (`asynchronousSGD_server.ts:95-108` applies every upload) — so accepted >= batches, never fewer
+    assert 2 * ds.batches <= len(accepted) <= 2 * ds.batches + 2 * (workers - 1)
+    assert all(s is not None and 0 <= s <= bound for s in accepted)
+    assert len(versions) == len(accepted) and all(o != n for o, n in versions)
+    assert [n for _, n in versions[:-1]] == [o for o, _ in versions[1:]]          # a chain: no version skipped or repeated
+    if bound >= 1 << 30:
+        assert server.numDropped == 0
