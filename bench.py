@@ -150,6 +150,9 @@ def main():
                    "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
             return subprocess.call(cmd)
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); the CPU plumbing configuration is exercised by "
+                         "`pytest -m 'not gpu'` and `python -m distriflow_b200.train --device cpu`")
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
