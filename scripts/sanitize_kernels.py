@@ -37,6 +37,24 @@ wc = (torch.randn(3, 3, 64, 64, device=dev) * 0.05).bfloat16().requires_grad_(Tr
 ops.conv2d_nhwc(xc, wc, None, (2, 2), "same", "relu").float().sum().backward()
 q = torch.randn(2, 64, 3 * 2 * 64, device=dev).bfloat16().requires_grad_(True)
 ops.causal_self_attention(q, 2).float().sum().backward()
+# fused BatchNorm + residual + ReLU (forward, backward, inference), fused GELU epilogues, packed attention gradient
+xb = torch.randn(4, 6, 6, 16, device=dev).bfloat16().requires_grad_(True)
+rb = torch.randn(4, 6, 6, 16, device=dev).bfloat16().requires_grad_(True)
+gb = torch.ones(16, device=dev).bfloat16().requires_grad_(True)
+bb = torch.zeros(16, device=dev).bfloat16().requires_grad_(True)
+rm, rv = torch.zeros(16, device=dev), torch.ones(16, device=dev)
+ops.batch_norm_nhwc(xb, gb, bb, rm, rv, True, 0.1, 1e-5, "relu", rb).float().sum().backward()
+with torch.no_grad():
+    ops.batch_norm_nhwc(xb, gb, bb, rm, rv, False, 0.1, 1e-5, "relu", rb)
+xm = torch.randn(256, 64, device=dev).bfloat16().requires_grad_(True)
+w1 = (torch.randn(64, 256, device=dev) * 0.05).bfloat16().requires_grad_(True)
+w2 = (torch.randn(256, 64, device=dev) * 0.05).bfloat16().requires_grad_(True)
+b1 = torch.zeros(256, device=dev).bfloat16().requires_grad_(True)
+b2 = torch.zeros(64, device=dev).bfloat16().requires_grad_(True)
+ops.mlp(xm, w1, b1, w2, b2).float().sum().backward()
+qkv = torch.randn(2, 16, 3 * 4 * 16, device=dev).bfloat16().requires_grad_(True)
+ops.causal_self_attention(qkv, 4).float().sum().backward()
+
 # collectives with two emulated ranks
 from distriflow_b200.ops import _lib
 from distriflow_b200.ops._lib import check, ptr
