@@ -1,7 +1,8 @@
 """PyTorch DDP + NCCL (+ cuBLAS/cuDNN) baseline of the identical model and schedule (BASELINE.json "Baselines").
 
-The model is the same module as in the product arm but every hot op is forced onto the stock PyTorch/cuBLAS
-kernels (`F.linear`, `F.conv2d`, `F.cross_entropy`), gradients are averaged by `DistributedDataParallel`'s
+The model is the same module as in the product arm but every op of `distriflow_b200.ops` is forced onto the stock
+PyTorch/cuBLAS/cuDNN kernels (`F.linear`, `F.conv2d`, `F.cross_entropy`, `F.layer_norm`, `F.gelu`, SDPA; none of this
+repo's kernels run in this arm), gradients are averaged by `DistributedDataParallel`'s
 bucketed NCCL all-reduce overlapped with backward, and the optimizer is `torch.optim` (fused).  Weights and
 gradients are bf16 like the product arm's working copies, with the same bucket size.
 """
@@ -19,7 +20,9 @@ import torch.nn.functional as F
 def stock_ops():
     """Route distriflow_b200.ops through PyTorch library kernels (baseline arm only)."""
     from distriflow_b200 import ops
-    saved = (ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc)
+    names = ("linear", "conv2d_nhwc", "maxpool2d_nhwc", "softmax_cross_entropy", "batch_norm_nhwc", "mlp", "layer_norm",
+             "add_layer_norm", "causal_self_attention")
+    saved = tuple(getattr(ops, n) for n in names)
     from distriflow_b200.ops.norm import batch_norm_reference
 
     def bn(x, gamma, beta, rm, rv, training, momentum=0.1, eps=1e-5, activation=None, residual=None):
@@ -51,14 +54,33 @@ def stock_ops():
             return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), labels.reshape(-1).long())
         return (-(labels.float() * F.log_softmax(logits.float(), -1)).sum(-1)).mean()
 
-    ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc = linear, conv, pool, ce, bn
+    def mlp(x, w1, b1, w2, b2):
+        return F.linear(F.gelu(F.linear(x, w1.t(), b1), approximate="tanh"), w2.t(), b2)
+
+    def layer_norm(x, gamma, beta, eps=1e-5):
+        return F.layer_norm(x, (x.shape[-1],), gamma.to(x.dtype), beta.to(x.dtype), eps)
+
+    def add_layer_norm(x, r, gamma, beta, eps=1e-5):
+        s = x + r
+        return s, F.layer_norm(s, (s.shape[-1],), gamma.to(s.dtype), beta.to(s.dtype), eps)
+
+    def attention(qkv, n_head):
+        B, T, C3 = qkv.shape
+        D = C3 // (3 * n_head)
+        q, k, v = qkv.view(B, T, 3, n_head, D).permute(2, 0, 3, 1, 4)
+        return F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, n_head * D)
+
+    for n, f in zip(names, (linear, conv, pool, ce, bn, mlp, layer_norm, add_layer_norm, attention)):
+        setattr(ops, n, f)
     try:
         yield
     finally:
-        ops.linear, ops.conv2d_nhwc, ops.maxpool2d_nhwc, ops.softmax_cross_entropy, ops.batch_norm_nhwc = saved
+        for n, f in zip(names, saved):
+            setattr(ops, n, f)
 
 
-def make_ddp_step(model, loss_fn, optimizer: str, lr: float, world: int, device, bucket_mb: int = 32):
+def make_ddp_step(model, loss_fn, optimizer: str, lr: float, world: int, device, bucket_mb: int = 32, compile_model: bool = False):
+    """Returns `(step, close)`; `close()` restores `distriflow_b200.ops` (the patch is process-wide while the arm runs)."""
     model = model.to(device).to(torch.bfloat16)
     ddp = model
     if world > 1:
@@ -72,20 +94,28 @@ def make_ddp_step(model, loss_fn, optimizer: str, lr: float, world: int, device,
     else:
         opt = torch.optim.SGD(params, lr=lr)
     global _STOCK_CTX
-    _STOCK_CTX = stock_ops()        # kept referenced: a collected generator would run its `finally` and undo the patch
-    _STOCK_CTX.__enter__()          # stays on for the life of the process (baseline arm)
+    _STOCK_CTX = ctx = stock_ops()  # kept referenced: a collected generator would run its `finally` and undo the patch
+    ctx.__enter__()
+    target = _Wrap(ddp, model) if world > 1 else model
+
+    def fwd_loss(*batch):
+        return loss_fn(target, *batch)
+
+    run = torch.compile(fwd_loss) if compile_model else fwd_loss     # stronger variant of the baseline (never of the product)
 
     def step(*batch):
         opt.zero_grad(set_to_none=True)
-        if world > 1:
-            loss = loss_fn(ddp.module if False else _Wrap(ddp, model), *batch)
-        else:
-            loss = loss_fn(model, *batch)
+        loss = run(*batch)
         loss.backward()
         opt.step()
         return loss.detach()
 
-    return step
+    def close():
+        global _STOCK_CTX
+        ctx.__exit__(None, None, None)
+        _STOCK_CTX = None
+
+    return step, close
 
 
 class _Wrap:

@@ -8,17 +8,24 @@ sequence 1024, bf16 — BASELINE.json config 5 — through `distriflow_b200.para
 Prints ONE JSON line on rank 0 (contract in the task statement).  `--impl reference` prints the
 "unavailable" line: the reference is TypeScript on tf.js/socket.io and has no Python package
 (`pip install ... /root/reference` -> "Neither 'setup.py' nor 'pyproject.toml' found"; no node/npm offline).
-`--impl ddp` runs the PyTorch DDP + NCCL (+cuBLAS) baseline of the identical model and schedule
-(BASELINE.json "Baselines"); `--model` / `--mode` select the other BASELINE configs.
+
+Because that reference arm can never produce a number, the product arm measures its own comparison baseline ON THE
+SAME BOX IN THE SAME PROCESSES right after its timed steps: PyTorch DDP + NCCL + cuBLAS/cuDNN on the identical model,
+batch, sequence length, optimizer, bucket size, steps and warm-up (BASELINE.json "Baselines"), and fills
+`vs_baseline = ours / ddp` and a `baseline` record with its own clocks (`--baseline none` skips it, `--ddp-compile`
+runs the DDP arm under torch.compile).  `--impl ddp` runs only that arm; `--model` / `--mode` select the other
+BASELINE configs.  The line also carries correctness evidence for the multi-GPU runs: `replicas_identical` (a 64-bit
+checksum of every rank's working weights after the timed steps) and the first-step losses of both arms from the same
+initial weights and batches.
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
@@ -44,45 +51,12 @@ def parse():
                     help="capture the whole step into a CUDA graph after 3 eager steps (default)")
     ap.add_argument("--nvls", action="store_true", help="reduce gradients / broadcast weights inside the NVSwitch (multicast heap)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches every step")
+    ap.add_argument("--no-fuse-allgather", dest="fuse_ag", action="store_false", default=True)
+    ap.add_argument("--baseline", default="auto", choices=["auto", "none", "ddp"],
+                    help="same-box comparison arm run after the product arm (auto: DDP for --impl ours)")
+    ap.add_argument("--ddp-compile", action="store_true", help="DDP arm under torch.compile (slow to start; stronger baseline)")
+    ap.add_argument("--trace", action="store_true", help="eager steps with device-timed forward/backward/collective_tail phases")
     return ap.parse_args()
-
-
-class ClockSampler:
-    """Samples nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
-
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, gpu_index: int = 0):
-        self.rows, self.proc, self.idx = [], None, gpu_index
-
-    def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
-                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except OSError:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
-
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
-        self.proc.terminate()
-        sm = sorted(int(r[1]) for r in self.rows if len(r) >= 9 and r[1].isdigit())
-        mx = [int(r[2]) for r in self.rows if len(r) >= 9 and r[2].isdigit()]
-        reasons = set()
-        for r in self.rows:
-            if len(r) >= 9:
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
 
 
 def build_workload(args, device, torch):
@@ -130,39 +104,30 @@ def build_workload(args, device, torch):
     return model, loss_fn, make, bs, {"model": args.model, "per_gpu_batch": bs}
 
 
-def main():
-    args = parse()
-    if args.impl == "reference":
-        if int(os.environ.get("RANK", "0")) != 0:          # launched under torchrun for N > 1: one line, from rank 0
-            return 0
-        print(json.dumps({"impl": "reference", "unavailable": "reference is TypeScript on tf.js/socket.io: no setup.py/pyproject "
-                          "(pip: 'not installable'), and node/npm/tfjs are absent offline; see DESIGN.md"}))
-        return 0
+def weights_checksum(engine, torch):
+    """64-bit checksum of this rank's working weights (the bits, not the values).  The range whose all-gather is fused into
+    its consumer GEMM is refreshed by the next forward pass, so it is left out."""
+    total = torch.zeros((), dtype=torch.int64, device=engine.device)
+    for b in getattr(engine, "buckets", []):
+        bits = b.param_buf.view(torch.int16 if b.param_buf.element_size() == 2 else torch.int32)
+        lo, hi = getattr(b, "nopush", (0, 0))
+        for part in (bits[:lo], bits[hi:]) if hi > lo else (bits,):
+            idx = torch.arange(1, part.numel() + 1, device=part.device, dtype=torch.int64)
+            total = total + (part.to(torch.int64) * (idx % 8191 + 1)).sum()
+    return total
+
+
+def run_arm(args, impl, rank, local_rank, world, device, host_seed):
+    """Build the model + step function of one arm, warm it up, time `args.steps` steps with CUDA events, then measure the
+    same steps end to end from pinned host memory.  Returns a dict of raw measurements (this rank's)."""
     import torch
     import torch.distributed as dist
-
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:            # convenience: re-launch under torchrun
-            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
-                   "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
-            return subprocess.call(cmd)
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device (B200); the CPU plumbing configuration is exercised by "
-                         "`pytest -m 'not gpu'` and `python -m distriflow_b200.train --device cpu`")
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
+    from distriflow_b200.ops import _lib
+    from distriflow_b200.utils.clocks import ClockSampler
 
     model, loss_fn, make_batch, bs, wcfg = build_workload(args, device, torch)
-    from distriflow_b200.ops import _lib
-
-    if args.impl == "ours":
+    engine = None
+    if impl == "ours":
         if args.mode == "async":
             from distriflow_b200.parallel.async_engine import AsyncEngine
             engine = AsyncEngine(model, loss_fn, {"optimizer": args.optimizer if args.optimizer != "adam" else "sgd",
@@ -174,13 +139,19 @@ def main():
             engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
                                                          "bucketBytes": int(args.bucket_mb * (1 << 20)),
                                                          "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
-                                                         "cudaGraph": args.graph, "nvls": bool(args.nvls and world > 1)},
+                                                         "cudaGraph": args.graph and not args.trace, "trace": args.trace,
+                                                         "fuseAllGather": args.fuse_ag,
+                                                         "nvls": bool(args.nvls and world > 1)},
                                         rank=rank, world=world, device=device)
         step = engine.step
+        close = lambda: None                                                      # noqa: E731
     else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)
         from baseline.ddp_baseline import make_ddp_step
-        step = make_ddp_step(model, loss_fn, args.optimizer, 3e-4, world, device, int(args.bucket_mb))
+        step, close = make_ddp_step(model, loss_fn, args.optimizer, 3e-4, world, device, int(args.bucket_mb),
+                                    compile_model=args.ddp_compile)
 
+    g = torch.Generator().manual_seed(host_seed + rank)
+    torch.set_rng_state(g.get_state())                    # same synthetic batches in both arms
     host = [make_batch() for _ in range(4)]
     dev = [(x.to(device, non_blocking=True), y.to(device, non_blocking=True)) for x, y in host]
     torch.cuda.synchronize()
@@ -190,9 +161,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    prep = 4 if (args.graph and args.impl == "ours") else 0
-    for i in range(prep):                      # engine set-up: 3 eager steps + the graph capture; never timed, not counted in W
-        step(*dev[i % len(dev)])
+    graph = bool(args.graph and impl == "ours" and not args.trace)
+    prep = 4 if graph else 0
+    first_losses = []
+    for i in range(max(prep, 3)):              # engine set-up (3 eager steps + the graph capture); never timed, not counted in W
+        loss_i = step(*dev[i % len(dev)])
+        if i < 3:
+            first_losses.append(round(float(loss_i), 5))
+    prep = max(prep, 3)
     for i in range(args.warmup):
         step(*dev[i % len(dev)])
     barrier()
@@ -201,7 +177,7 @@ def main():
         sampler.start()
     l0 = _lib.LAUNCHES[0]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    prof = os.environ.get("DFB_PROFILE_RANGE") == "1"       # ncu --profile-from-start off: capture the timed steps only
+    prof = os.environ.get("DFB_PROFILE_RANGE") == "1" and impl == args.impl     # ncu --profile-from-start off: timed steps only
     if prof:
         torch.cuda.profiler.start()
     e0.record()
@@ -233,27 +209,107 @@ def main():
         hx, hy = host[0]
         e2e = (e2e_ms, hx.numel() * hx.element_size() + hy.numel() * hy.element_size(), 4, last)
 
+    identical = None
+    if impl == "ours" and args.mode == "sync" and engine is not None and hasattr(engine, "buckets"):
+        cs = weights_checksum(engine, torch).reshape(1)
+        if world > 1:
+            allcs = [torch.zeros_like(cs) for _ in range(world)]
+            dist.all_gather(allcs, cs)
+            identical = all(int(c) == int(allcs[0]) for c in allcs)
+        else:
+            identical = True
+    trace = None
+    if args.trace and engine is not None and getattr(engine, "tracer", None) is not None:
+        trace = engine.trace_summary()
+
     t = torch.tensor([ms, e2e[0] if e2e else 0.0], device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = float(t[0]), float(t[1])
+    out = {"ms": float(t[0]), "e2e_ms": float(t[1]), "e2e": e2e, "loss": float(loss), "launches": int(launches),
+           "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "graph": graph, "first_losses": first_losses,
+           "replicas_identical": identical, "trace": trace,
+           "buckets": len(engine.buckets) if engine is not None and hasattr(engine, "buckets") else None}
+    close()
+    del step, engine, model, dev
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:          # launched under torchrun for N > 1: one line, from rank 0
+            return 0
+        print(json.dumps({"impl": "reference", "unavailable": "reference is TypeScript on tf.js/socket.io: no setup.py/pyproject "
+                          "(pip: 'not installable'), and node/npm/tfjs are absent offline; see DESIGN.md"}))
+        return 0
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:            # convenience: re-launch under torchrun
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+                   "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
+            return subprocess.call(cmd)
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); the CPU plumbing configuration is exercised by "
+                         "`pytest -m 'not gpu'` and `python -m distriflow_b200.train --device cpu`")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    r = run_arm(args, args.impl, rank, local_rank, world, device, host_seed=4321)
+    base = None
+    if args.impl == "ours" and args.baseline != "none":
+        try:
+            base = run_arm(args, "ddp", rank, local_rank, world, device, host_seed=4321)
+        except Exception as e:                      # the product number must not die with the comparison arm
+            base = {"error": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
-        gb = bs * world
-        value = gb * args.steps / (ms / 1e3)
+        gb = r["bs"] * world
+        value = gb * args.steps / (r["ms"] / 1e3)
         out = {"metric": "samples/sec sync DP" if args.mode == "sync" else "samples/sec async DP", "value": value,
                "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-               "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                "dtype": "bf16" if args.model.startswith(("gpt2", "resnet")) else "fp32", "data": "synthetic",
                "impl": args.impl,
-               "config": {**wcfg, "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
-                          "optimizer": args.optimizer, "bucket_mb": args.bucket_mb,
-                          "cuda_graph": bool(prep), "nvls": bool(args.nvls and world > 1), "graph_prep_steps": prep,
+               "config": {**r["wcfg"], "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
+                          "optimizer": args.optimizer, "bucket_mb": args.bucket_mb, "buckets": r["buckets"],
+                          "cuda_graph": r["graph"], "nvls": bool(args.nvls and world > 1), "graph_prep_steps": r["prep"],
+                          "fuse_allgather": bool(args.fuse_ag),
                           "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
-                          "loss": float(loss)},
-               "clocks": clocks, "gpu_launches": int(launches)}
-        if e2e:
-            out["e2e"] = {"value": gb * args.steps / (e2e_ms / 1e3), "unit": "samples/s", "h2d_bytes_per_step": e2e[1],
-                          "d2h_bytes_per_step": e2e[2], "ms_per_step": e2e_ms / args.steps}
+                          "loss": r["loss"]},
+               "clocks": r["clocks"], "gpu_launches": r["launches"], "replicas_identical": r["replicas_identical"],
+               "loss_first_steps": {"ours" if args.impl == "ours" else args.impl: r["first_losses"]}}
+        if r["e2e"]:
+            out["e2e"] = {"value": gb * args.steps / (r["e2e_ms"] / 1e3), "unit": "samples/s", "h2d_bytes_per_step": r["e2e"][1],
+                          "d2h_bytes_per_step": r["e2e"][2], "ms_per_step": r["e2e_ms"] / args.steps}
+        if r["trace"]:
+            out["trace"] = r["trace"]
+        if base is not None and "error" not in base:
+            bval = gb * args.steps / (base["ms"] / 1e3)
+            out["vs_baseline"] = value / bval
+            out["baseline"] = {"impl": "PyTorch DDP + NCCL + cuBLAS/cuDNN, eager" + (" + torch.compile" if args.ddp_compile else ""),
+                               "same_box_same_process": True, "value": bval, "unit": "samples/s",
+                               "ms_per_step": base["ms"] / args.steps, "clocks": base["clocks"],
+                               "config": {**base["wcfg"], "global_batch": base["bs"] * world, "optimizer": args.optimizer,
+                                          "bucket_mb": args.bucket_mb, "steps": args.steps, "warmup": args.warmup + base["prep"]},
+                               "loss": base["loss"]}
+            if base["e2e"]:
+                out["baseline"]["e2e_value"] = gb * args.steps / (base["e2e_ms"] / 1e3)
+                if r["e2e"]:
+                    out["e2e"]["vs_baseline"] = out["e2e"]["value"] / out["baseline"]["e2e_value"]
+            out["loss_first_steps"]["ddp"] = base["first_losses"]
+        elif base is not None:
+            out["baseline"] = base
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()

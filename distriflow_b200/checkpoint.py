@@ -66,9 +66,17 @@ def force_symlink(src: str, dest: str) -> None:
 # tf.js layers-model artifact
 
 def _named_weights(model: torch.nn.Module) -> List[Tuple[str, torch.Tensor]]:
+    """Everything a restart needs: trainable weights AND persistent buffers (BatchNorm moving_mean / moving_variance),
+    which Keras / tf.js list in the manifest as non-trainable weights of the layer."""
     if hasattr(model, "named_weights"):
         return model.named_weights()
-    return [(n.replace(".", "/"), p) for n, p in model.named_parameters()]
+    out = [(n.replace(".", "/"), p) for n, p in model.named_parameters()]
+    nonpersistent = set()
+    for mn, m in model.named_modules():
+        for bn in getattr(m, "_non_persistent_buffers_set", ()):
+            nonpersistent.add(f"{mn}.{bn}" if mn else bn)
+    out += [(n.replace(".", "/"), b) for n, b in model.named_buffers() if n not in nonpersistent and b.is_floating_point()]
+    return out
 
 
 def save_layers_model(model: torch.nn.Module, directory: str, topology: Optional[Dict[str, Any]] = None) -> str:
@@ -76,8 +84,14 @@ def save_layers_model(model: torch.nn.Module, directory: str, topology: Optional
     os.makedirs(directory, exist_ok=True)
     if topology is None:
         from .models.topology import SequentialModel, topology_from_model
-        topology = topology_from_model(model) if isinstance(model, SequentialModel) else \
-            {"class_name": model.__class__.__name__, "config": getattr(model, "config", {})}
+        if isinstance(model, SequentialModel):
+            topology = topology_from_model(model)
+        else:                                       # not rebuildable from JSON: class name + its config for the record
+            import dataclasses
+            cfg = getattr(model, "config", {})
+            if dataclasses.is_dataclass(cfg) and not isinstance(cfg, type):
+                cfg = dataclasses.asdict(cfg)
+            topology = {"class_name": model.__class__.__name__, "config": cfg if isinstance(cfg, dict) else {}}
     specs, blobs = [], []
     for name, t in _named_weights(model):
         t32 = t.detach().to("cpu", torch.float32).contiguous()     # weights.bin is float32
@@ -117,17 +131,21 @@ def read_manifest_weights(model_json: str, artifact: Dict[str, Any]) -> Dict[str
 
 
 def load_layers_model(path: str, builder: Optional[Callable[[Dict[str, Any]], torch.nn.Module]] = None,
-                      load_weights: bool = True, strict: bool = True) -> torch.nn.Module:
-    """`path` is a model.json or a directory holding one."""
+                      load_weights: bool = True, strict: bool = True, into: Optional[torch.nn.Module] = None) -> torch.nn.Module:
+    """`path` is a model.json or a directory holding one.  `into`: read the manifest into this existing module instead of
+    rebuilding one from the topology (needed for models that are not Sequential: ResNet, GPT-2, user modules)."""
     if os.path.isdir(path):
         path = os.path.join(path, "model.json")
     with open(path) as f:
         artifact = json.load(f)
     topo = artifact["modelTopology"]
-    if builder is None:
-        from .models.topology import model_from_topology
-        builder = model_from_topology
-    model = builder(topo)
+    if into is not None:
+        model = into
+    else:
+        if builder is None:
+            from .models.topology import model_from_topology
+            builder = model_from_topology
+        model = builder(topo)
     if load_weights:
         try:
             weights = read_manifest_weights(path, artifact)
@@ -238,7 +256,18 @@ class DistriServerTorchModel(DistriTorchModel):
     def load(self, version: str) -> None:
         path = os.path.join(self.saveDir, version, "model.json")
         self.version = version
-        self.model = load_layers_model(path)
+        with open(path) as f:
+            topo = json.load(f)["modelTopology"]
+        from .models.topology import is_sequential_topology
+        if is_sequential_topology(topo):
+            self.model = load_layers_model(path)
+        else:
+            # ResNet / GPT-2 / user modules are not rebuilt from JSON: the weights are read into the module the caller
+            # supplied (the reference can always rebuild because tf.js LayersModels are self-describing, models.ts:140-150)
+            self._resolve()
+            if self.model is None:
+                raise ValueError(f"{path}: topology {topo.get('class_name')!r} cannot be rebuilt; pass the module as initialModel")
+            load_layers_model(path, into=self.model)
         if self.device is not None:
             self.model.to(self.device)
         self._params = [p for p in self.model.parameters() if p.requires_grad]

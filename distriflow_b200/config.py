@@ -84,6 +84,7 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "trace": False,               # CUDA-event phase timers + NVTX ranges (forward / backward / collective tail); eager steps only
     "watchdogSeconds": 0.0,       # > 0: host thread reports a rank whose device-written step counter stops advancing
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
+    "debugPoison": False,         # race detector: NaN a bucket's weights the moment its last gradient is reported (tests)
 }
 
 _VALID = {

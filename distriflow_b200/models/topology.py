@@ -70,6 +70,12 @@ def sequential(layer_list: Sequence[nn.Module], input_shape: Sequence[int], name
     return SequentialModel(layer_list, input_shape, name)
 
 
+def is_sequential_topology(topology: Dict[str, Any]) -> bool:
+    """True when `model_from_topology` can rebuild the module from this JSON (Keras `Sequential`)."""
+    t = topology.get("model_config", topology)
+    return isinstance(t, dict) and t.get("class_name") == "Sequential"
+
+
 def _layer_entries(topology: Dict[str, Any]) -> Tuple[List[Dict[str, Any]], str]:
     t = topology
     if "model_config" in t:

@@ -125,16 +125,7 @@ class _ThinConvFn(torch.autograd.Function):
             dy2 = act_op(dy2, y, 2)
         kernel, bias = ctx.kernel_ref, ctx.bias_ref
         dx = dw = db = None
-        if ctx.needs_input_grad[1]:
-            patches = _im2col(x, ctx.geom, ctx.kpad)
-            dwm = gemm(patches, dy2, a_mn=True, b_mn=True, M=ctx.kpad, N=K, K=N * OH * OW, out_dtype=torch.float32)
-            dw_full = dwm[:kreal].reshape(kh, kw, C, K)
-            sink = getattr(kernel, "_dfb_grad_sink", None)
-            if sink is not None:
-                sink.view(kh, kw, C, K).copy_(dw_full)
-                kernel._dfb_grad_ready()
-            else:
-                dw = dw_full.to(kernel.dtype)
+        # data gradient first: it reads the live filter, and `_dfb_grad_ready()` below may start the bucket kernel that overwrites it
         if ctx.needs_input_grad[0]:
             if sh == 1 and sw == 1 and K % 8 == 0 and C % 8 == 0:
                 # data gradient = stride-1 correlation of dY with the flipped, transposed filter: same patch-matrix GEMM
@@ -155,6 +146,16 @@ class _ThinConvFn(torch.autograd.Function):
             else:
                 dx = torch.empty_like(x)
                 _conv_call(1, dy2.view(N, OH, OW, K), ctx.kernel_ref.to(x.dtype).contiguous(), dx, None, ctx.geom, None)
+        if ctx.needs_input_grad[1]:
+            patches = _im2col(x, ctx.geom, ctx.kpad)
+            dwm = gemm(patches, dy2, a_mn=True, b_mn=True, M=ctx.kpad, N=K, K=N * OH * OW, out_dtype=torch.float32)
+            dw_full = dwm[:kreal].reshape(kh, kw, C, K)
+            sink = getattr(kernel, "_dfb_grad_sink", None)
+            if sink is not None:
+                sink.view(kh, kw, C, K).copy_(dw_full)
+                kernel._dfb_grad_ready()
+            else:
+                dw = dw_full.to(kernel.dtype)
         if bias is not None and ctx.needs_input_grad[2]:
             db = colsum(dy2)
             sink = getattr(bias, "_dfb_grad_sink", None)

@@ -1021,7 +1021,7 @@ DFB_API int dfb_ag_gemm_bf16(const void* A, const void* W_local, void* D, const 
 // library and stays until the process exits.
 //
 // Sharing rules: every call on a device uses the same array.  Nothing in it has to start at zero — each split
-// writes its whole [ceil128(M) x N] partial tile grid with plain stores before the reduce kernel reads it, so
+// writes its whole [ceil256(M) x N] partial tile grid (rows padded to 256, as in dfb_gemm_workspace_bytes) with plain stores before the reduce kernel reads it, so
 // whatever the previous call left behind is overwritten, never accumulated into.  Two calls whose kernels can
 // overlap on the GPU (different streams without an ordering between them) race on the array and corrupt each
 // other; keep calls on one stream or order them with events.
@@ -1032,7 +1032,9 @@ DFB_API int dfb_ag_gemm_bf16(const void* A, const void* W_local, void* D, const 
 // before starting any stream capture.
 constexpr size_t kNoAllocScratchBytes = size_t(32) << 20;
 static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchBytes / sizeof(float)];
-static float* g_noalloc_scratch_addr[64];      // device address of the array, per device ordinal (0 = not resolved yet)
+// device address of the array, per device ordinal (0 = not resolved yet).  Filled without a lock: two host threads making
+// the first call on one device both resolve the same address and store the same value (a benign duplicate store).
+static float* g_noalloc_scratch_addr[64];
 
 DFB_API int dfb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N,
                                          int K, int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int out_dtype,

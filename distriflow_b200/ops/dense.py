@@ -307,14 +307,17 @@ class _MlpFn(torch.autograd.Function):
         dy2 = dy.reshape(M, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        # fc2: dW2 = h^T dy, db2 = colsum(dy), dpre = (dy W2^T) * gelu'(pre)   <- GELU backward in the dgrad epilogue
+        # Order matters under the overlapped engine: a parameter's `_dfb_grad_ready()` may launch its bucket's fused
+        # reduce-scatter + optimizer + all-gather kernel on the side stream, which OVERWRITES the working weights.  Every
+        # kernel that still reads a weight (the data-gradient GEMMs) is therefore enqueued before that weight is reported.
+        # fc2: dpre = (dy W2^T) * gelu'(pre)   <- GELU backward in the dgrad epilogue;  dW2 = h^T dy, db2 = colsum(dy)
+        dpre = gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2)
+        dx = gemm(dpre, w1d, a_mn=False, b_mn=False, M=M, N=K, K=H).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw2 = _wgrad(h, dy2, w2, H, N, M)
         db2 = _deliver(b2, colsum(dy2)) if b2 is not None else None
-        dpre = gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2)
         # fc1
         dw1 = _wgrad(x2, dpre, w1, K, H, M)
         db1 = _deliver(b1, colsum(dpre)) if b1 is not None else None
-        dx = gemm(dpre, w1d, a_mn=False, b_mn=False, M=M, N=K, K=H).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         return dx, dw1, db1, dw2, db2
 
 

@@ -595,19 +595,29 @@ __global__ void wq_init_kernel(uint32_t* wq, uint32_t batches, uint32_t epochs, 
   }
 }
 
+// The epoch word carries a "rolling" marker (top bit) while the completer that finished an epoch resets the queue, and all
+// completions are serialised by a spin lock (W_LOCK): check-epoch / set-bit / count / roll is one critical section, so a
+// duplicate completion of a re-issued batch can never land in the freshly cleared bitmap of the next epoch (which would
+// leave that batch "done" before it ran and the epoch counter one short for ever).  Completions are rare (one per batch) and
+// the section is a few dozen instructions of one thread; holders are always running kernels, so the lock cannot be held by
+// a kernel that is waiting to be scheduled.
+constexpr uint32_t kWqRolling = 0x80000000u;
+constexpr uint32_t kWqSpinLimit = 1u << 22;            // bounded waits: a wedged queue reports "exhausted" instead of hanging the GPU
+
 // One thread takes a ticket.  out[0] = batch index or 0xffffffff when the dataset is exhausted, out[1] = epoch.
 // FCFS in index order; when the fresh tickets of the epoch are gone, still-incomplete batches are re-issued
 // (round-robin scan of the bitmap) exactly like DistributedDataset.next() (dataset.ts:57-60).
 __global__ void wq_take_kernel(uint32_t* wq, uint32_t* out) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  while (true) {
-    if (ld_acquire_sys(wq + W_DONE)) { out[0] = 0xffffffffu; out[1] = ld_acquire_sys(wq + W_EPOCH); return; }
+  for (uint32_t spins = 0; spins < kWqSpinLimit; ++spins) {
+    if (ld_acquire_sys(wq + W_DONE)) { out[0] = 0xffffffffu; out[1] = ld_acquire_sys(wq + W_EPOCH) & ~kWqRolling; return; }
     const uint32_t batches = wq[W_BATCHES];
     const uint32_t epoch = ld_acquire_sys(wq + W_EPOCH);
+    if (epoch & kWqRolling) { __nanosleep(200); continue; }   // the queue is being reset for the next epoch
     const uint32_t t = atomicAdd_system(wq + W_TICKET, 1u);
     if (t < batches) {
       if (ld_acquire_sys(wq + W_EPOCH) == epoch) { out[0] = t; out[1] = epoch; return; }
-      continue;                                       // epoch rolled over under us: take again
+      continue;                                       // epoch rolled over under us: take again (the lost ticket is re-issued)
     }
     // fresh ones ran out: re-issue something still incomplete
     const uint32_t start = atomicAdd_system(wq + W_CURSOR, 1u);
@@ -615,12 +625,14 @@ __global__ void wq_take_kernel(uint32_t* wq, uint32_t* out) {
       const uint32_t b = (start + k) % batches;
       const uint32_t word = ld_acquire_sys(wq + W_BITMAP + (b >> 5));
       if (!((word >> (b & 31)) & 1u)) {
-        if (ld_acquire_sys(wq + W_EPOCH) != epoch) break;
+        if (ld_acquire_sys(wq + W_EPOCH) != epoch) break;     // includes the rolling marker: the zero we read is the reset
         out[0] = b; out[1] = epoch; return;
       }
     }
-    // everything complete (or epoch rolled): loop and look again
+    __nanosleep(500);                                 // everything complete (or epoch rolled): look again
   }
+  out[0] = 0xffffffffu;                               // gave up: see kWqSpinLimit
+  out[1] = ld_acquire_sys(wq + W_EPOCH) & ~kWqRolling;
 }
 
 // Mark `batch` of `epoch` complete (idempotent).  The completion that finishes the epoch advances it.
@@ -629,25 +641,37 @@ __global__ void wq_complete_kernel(uint32_t* wq, const uint32_t* ticket, const u
   if (accepted != nullptr && *accepted == 0) return;    // the gradient of this batch was refused: leave it incomplete -> re-issued
   const uint32_t b = ticket[0], epoch = ticket[1];
   if (b == 0xffffffffu) return;
-  if (ld_acquire_sys(wq + W_EPOCH) != epoch) return;    // stale completion from a previous epoch: ignored
-  const uint32_t bit = 1u << (b & 31);
-  const uint32_t old = atomicOr_system(wq + W_BITMAP + (b >> 5), bit);
-  if (old & bit) return;                                // duplicate
-  const uint32_t batches = wq[W_BATCHES];
-  const uint32_t done = atomicAdd_system(wq + W_COMPLETED, 1u) + 1;
-  if (done == batches) {                                // last one of the epoch: roll over
-    const int words = (batches + 31) / 32;
-    if (epoch + 1 >= wq[W_EPOCHS]) {
-      st_release_sys(wq + W_DONE, 1u);
-    } else {
-      for (int i = 0; i < words; ++i) atomicExch_system(wq + W_BITMAP + i, 0u);
-      atomicExch_system(wq + W_COMPLETED, 0u);
-      atomicExch_system(wq + W_CURSOR, 0u);
-      atomicExch_system(wq + W_TICKET, 0u);
-      __threadfence_system();
-      st_release_sys(wq + W_EPOCH, epoch + 1);
+  uint32_t spins = 0;
+  while (atomicCAS_system(wq + W_LOCK, 0u, 1u) != 0u) {
+    if (++spins > kWqSpinLimit) return;
+    __nanosleep(100);
+  }
+  __threadfence_system();
+  if (ld_acquire_sys(wq + W_EPOCH) == epoch) {          // else: stale completion from a previous epoch, ignored
+    const uint32_t bit = 1u << (b & 31);
+    const uint32_t old = atomicOr_system(wq + W_BITMAP + (b >> 5), bit);
+    if (!(old & bit)) {                                 // else: duplicate
+      const uint32_t batches = wq[W_BATCHES];
+      const uint32_t done = atomicAdd_system(wq + W_COMPLETED, 1u) + 1;
+      if (done == batches) {                            // last one of the epoch: roll over
+        const int words = (batches + 31) / 32;
+        if (epoch + 1 >= wq[W_EPOCHS]) {
+          st_release_sys(wq + W_DONE, 1u);
+        } else {
+          st_release_sys(wq + W_EPOCH, epoch | kWqRolling);     // publish "rolling" BEFORE anything is cleared
+          __threadfence_system();
+          for (int i = 0; i < words; ++i) atomicExch_system(wq + W_BITMAP + i, 0u);
+          atomicExch_system(wq + W_COMPLETED, 0u);
+          atomicExch_system(wq + W_CURSOR, 0u);
+          atomicExch_system(wq + W_TICKET, 0u);
+          __threadfence_system();
+          st_release_sys(wq + W_EPOCH, epoch + 1);
+        }
+      }
     }
   }
+  __threadfence_system();
+  atomicExch_system(wq + W_LOCK, 0u);
 }
 
 // Gather the rows of batch `ticket[0]` from a device-resident dataset: dst[r, :] = src[(b*bs + r) % rows, :].
@@ -913,23 +937,29 @@ DFB_API int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, cud
   return 0;
 }
 
-DFB_API int dfb_wq_init(unsigned* pad, unsigned batches, unsigned epochs, cudaStream_t stream) {
+// `wq` is the queue's control block in the home rank's heap (any rank's mapping of it): either the slot inside the signal
+// pad (`pad + dfb_wq_pad_offset_words()`, room for `dfb_wq_pad_capacity()` batches) or, for larger datasets, a block of
+// `dfb_wq_words(batches)` 32-bit words allocated from the heap.
+DFB_API int dfb_wq_init(unsigned* wq, unsigned batches, unsigned epochs, cudaStream_t stream) {
+  DFB_REQUIRE(batches >= 1 && epochs < kWqRolling, "wq_init: bad arguments");
   const int words = (int)((batches + 31) / 32);
-  wq_init_kernel<<<1, 256, 0, stream>>>(pad + kWqBase, batches, epochs, words);
+  wq_init_kernel<<<1, 256, 0, stream>>>(wq, batches, epochs, words);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
-DFB_API int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, cudaStream_t stream) {
-  wq_take_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket_out2);
+DFB_API int dfb_wq_take(unsigned* wq, unsigned* ticket_out2, cudaStream_t stream) {
+  wq_take_kernel<<<1, 32, 0, stream>>>(wq, ticket_out2);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
-DFB_API int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, const unsigned* accepted, cudaStream_t stream) {
-  wq_complete_kernel<<<1, 32, 0, stream>>>(home_pad + kWqBase, ticket2, accepted);
+DFB_API int dfb_wq_complete(unsigned* wq, const unsigned* ticket2, const unsigned* accepted, cudaStream_t stream) {
+  wq_complete_kernel<<<1, 32, 0, stream>>>(wq, ticket2, accepted);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
-DFB_API int dfb_wq_pad_words(unsigned batches) { return kWqBase + W_BITMAP + (int)((batches + 31) / 32); }
+DFB_API int dfb_wq_words(unsigned batches) { return W_BITMAP + (int)((batches + 31) / 32); }
+DFB_API int dfb_wq_pad_offset_words(void) { return kWqBase; }
+DFB_API int dfb_wq_pad_capacity(void) { return (4096 / 4 - kWqBase - W_BITMAP) * 32; }
 DFB_API int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                              cudaStream_t stream) {
   DFB_REQUIRE((row_bytes % 4) == 0, "gather_batch: row size must be a multiple of 4 bytes");

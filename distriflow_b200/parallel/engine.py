@@ -210,6 +210,15 @@ class DataParallelEngine:
 
     def _param_ready(self, b: Bucket) -> None:
         b.pending -= 1
+        if b.pending == 0 and self.cfg["debugPoison"]:
+            # Race detector: from the moment a bucket is reported complete its working weights may be overwritten by the
+            # fused kernel, so nothing enqueued later in this backward may read them.  Overwrite them with NaN right here
+            # (same stream, deterministic) and run the real kernel in the tail, which rewrites every element from the fp32
+            # masters; a kernel that read a weight after reporting it turns the next loss into NaN.
+            lo, hi = b.nopush
+            b.param_buf[:lo].fill_(float("nan"))
+            b.param_buf[hi:].fill_(float("nan"))
+            return
         if b.pending == 0 and self.cfg["overlap"]:
             self._launch_bucket(b)
 
@@ -429,8 +438,9 @@ class DataParallelEngine:
             for p, off in zip(b.params, b.offsets):
                 entry = {k: f[off:off + p.numel()].view(p.shape).cpu().clone() for k, f in flats.items() if f is not None}
                 params[names[id(p)]] = entry
+        buffers = {n: b.detach().cpu().clone() for n, b in self.model.named_buffers()}     # BatchNorm running statistics etc.
         return {"format": "distriflow_b200.engine/1", "version": int(self.version), "optimizer": self.cfg["optimizer"],
-                "learningRate": self.lr, "params": params}
+                "learningRate": self.lr, "params": params, "buffers": buffers}
 
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
         """Inverse of `state_dict` at ANY world size: every rank takes its slice of every bucket, the working copies are
@@ -455,6 +465,11 @@ class DataParallelEngine:
             for k, f in flats.items():
                 getattr(b, k).copy_(f[lo:hi])
             b.param_buf.copy_(flats["master"])
+        saved_buffers = sd.get("buffers", {})
+        with torch.no_grad():
+            for n, buf in self.model.named_buffers():
+                if n in saved_buffers:
+                    buf.copy_(saved_buffers[n].to(buf.device, buf.dtype))
         self.version = int(sd["version"])
         if self._graph_mode:
             self._step_dev.fill_(self.version)
@@ -578,8 +593,12 @@ def _comm_sigs():
         L.dfb_wq_take.argtypes = [c_void_p, c_void_p, c_void_p]
         L.dfb_wq_complete.restype = c_int
         L.dfb_wq_complete.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p]
-        L.dfb_wq_pad_words.restype = c_int
-        L.dfb_wq_pad_words.argtypes = [ctypes.c_uint]
+        L.dfb_wq_words.restype = c_int
+        L.dfb_wq_words.argtypes = [ctypes.c_uint]
+        L.dfb_wq_pad_offset_words.restype = c_int
+        L.dfb_wq_pad_offset_words.argtypes = []
+        L.dfb_wq_pad_capacity.restype = c_int
+        L.dfb_wq_pad_capacity.argtypes = []
         L.dfb_gather_batch.restype = c_int
         L.dfb_gather_batch.argtypes = [c_void_p, c_void_p, c_void_p, ctypes.c_long, c_int, ctypes.c_long, c_void_p]
         L._dfb_comm_sigs = True

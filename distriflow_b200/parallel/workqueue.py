@@ -18,7 +18,7 @@ import torch
 from ..ops import _lib
 from ..ops._lib import c_void_p, check, ptr
 from .engine import _comm_sigs
-from .symm import PAD_BYTES, SymmetricHeap
+from .symm import SymmetricHeap
 
 __all__ = ["DeviceWorkQueue", "Ticket"]
 
@@ -37,9 +37,13 @@ class DeviceWorkQueue:
     def __init__(self, heap: SymmetricHeap, batches: int, epochs: int, home_rank: int = 0, init: bool = True):
         self.L = _comm_sigs()
         self.heap, self.batches, self.epochs, self.home = heap, batches, epochs, home_rank
-        if self.L.dfb_wq_pad_words(batches) * 4 > PAD_BYTES:
-            raise ValueError(f"{batches} batches do not fit the signal pad bitmap ({PAD_BYTES} bytes)")
-        self.home_pad = c_void_p(heap.peer_bases[home_rank])
+        if batches <= self.L.dfb_wq_pad_capacity():
+            off = self.L.dfb_wq_pad_offset_words() * 4                 # small datasets: the slot inside the signal pad
+        else:
+            # the completion bitmap is sized from the dataset (60 000 examples at batch 1 = 7.5 KB): a block of the heap,
+            # allocated by every rank so that heap offsets stay identical across ranks
+            off = heap.alloc(self.L.dfb_wq_words(batches) * 4)
+        self.home_pad = c_void_p(heap.peer_bases[home_rank] + off)
         self.ticket = torch.zeros(2, dtype=torch.int32, device=heap.device)
         if init and heap.rank == home_rank:
             check(self.L.dfb_wq_init(self.home_pad, batches, epochs, _lib.stream()), "dfb_wq_init")
@@ -47,7 +51,7 @@ class DeviceWorkQueue:
 
     @classmethod
     def local(cls, batches: int, epochs: int, device=None) -> "DeviceWorkQueue":
-        return cls(SymmetricHeap(4096, 0, 1, None, device), batches, epochs)
+        return cls(SymmetricHeap(4096 + 4 * (32 + batches // 32), 0, 1, None, device), batches, epochs)
 
     def take_async(self) -> torch.Tensor:
         """Take a ticket into device memory (`[batch, epoch]`, batch = 0xffffffff when the dataset is exhausted)."""

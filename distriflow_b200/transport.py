@@ -27,7 +27,7 @@ import threading
 import time
 from typing import Any, Callable, Deque, Dict, List, Optional, Tuple
 
-from .messages import Events, decode, encode
+from .messages import MAX_FRAME_BYTES, Events, WireFormatError, decode, encode
 
 __all__ = ["LoopbackHub", "LoopbackPeer", "LoopbackClientEndpoint", "TcpServerEndpoint", "TcpClientEndpoint",
            "AckTimeout", "ConnectTimeout"]
@@ -199,10 +199,15 @@ def _recv_frame(sock: socket.socket) -> Optional[Tuple[int, int, Any]]:
     if hdr is None:
         return None
     n, mid, kind = _HDR.unpack(hdr)
+    if n > MAX_FRAME_BYTES or kind not in (0, 1):
+        return None                               # not our protocol (or an absurd length): drop the connection
     payload = _recv_exact(sock, n)
     if payload is None:
         return None
-    return mid, kind, decode(payload)
+    try:
+        return mid, kind, decode(payload)
+    except WireFormatError:
+        return None
 
 
 class _TcpPeer:
@@ -274,7 +279,10 @@ class TcpServerEndpoint:
                 frame = None
             if frame is None:
                 break
-            mid, kind, (event, msg) = frame
+            mid, kind, obj = frame
+            if kind != 0 or not (isinstance(obj, tuple) and len(obj) == 2 and isinstance(obj[0], str)):
+                break                             # not an event frame: protocol violation, drop the peer
+            event, msg = obj
 
             def ack(v: Any = True, mid=mid) -> None:
                 try:
@@ -365,6 +373,8 @@ class TcpClientEndpoint:
                     self._acks[mid] = obj
                     self._cv.notify_all()
                 continue
+            if not (isinstance(obj, tuple) and len(obj) == 2 and isinstance(obj[0], str)):
+                break
             event, msg = obj
             with self._cv:
                 hs = list(self.handlers.get(event, ()))

@@ -133,10 +133,14 @@ int dfb_async_pull(void* const* params, void* const* sig, void* dst, unsigned* s
                    int rank, int R, int ctas, void* stream);
 int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, void* stream);
 /* device work queue (dataset.ts:43-67) */
-int dfb_wq_init(unsigned* pad, unsigned batches, unsigned epochs, void* stream);
-int dfb_wq_take(unsigned* home_pad, unsigned* ticket_out2, void* stream);
-int dfb_wq_complete(unsigned* home_pad, const unsigned* ticket2, const unsigned* accepted /* nullable */, void* stream);
-int dfb_wq_pad_words(unsigned batches);
+/* `wq`: the queue's control block in the home rank's heap (through any rank's mapping): the slot inside the signal pad
+ * (pad + dfb_wq_pad_offset_words(), room for dfb_wq_pad_capacity() batches) or a heap block of dfb_wq_words(batches) words */
+int dfb_wq_init(unsigned* wq, unsigned batches, unsigned epochs, void* stream);
+int dfb_wq_take(unsigned* wq, unsigned* ticket_out2, void* stream);
+int dfb_wq_complete(unsigned* wq, const unsigned* ticket2, const unsigned* accepted /* nullable */, void* stream);
+int dfb_wq_words(unsigned batches);
+int dfb_wq_pad_offset_words(void);
+int dfb_wq_pad_capacity(void);
 int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                      void* stream);
 

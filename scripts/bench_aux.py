@@ -2,6 +2,8 @@ import sys, os
 sys.path.insert(0, os.getcwd())
 import torch
 from distriflow_b200.ops.dense import _init_sigs, gemm, gemm_aux, act_op
+from distriflow_b200.utils.clocks import ClockSampler
+sampler = ClockSampler(0).start()
 _init_sigs()
 dev = torch.device("cuda")
 M, K, H = 32768, 768, 3072
@@ -21,3 +23,5 @@ print("bwd fused (aux gelu')   us", t(lambda: gemm_aux(dy, w2, a_mn=False, b_mn=
 print("bwd gemm + act kernel   us", t(lambda: act_op(gemm(dy, w2, a_mn=False, b_mn=False, M=M, N=H, K=K), pre, 1)))
 print("bwd gemm only           us", t(lambda: gemm(dy, w2, a_mn=False, b_mn=False, M=M, N=H, K=K)))
 print("fwd gemm, no bias       us", t(lambda: gemm(x, w1, a_mn=False, b_mn=True, M=M, N=H, K=K)))
+import json
+print(json.dumps({"clocks": sampler.stop()}))

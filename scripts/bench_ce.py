@@ -9,6 +9,7 @@ import torch
 
 from distriflow_b200.ops import _lib, softmax_ce
 from distriflow_b200.ops._lib import check, ptr, stream
+from distriflow_b200.utils.clocks import ClockSampler
 
 dev = torch.device("cuda")
 rows, C = 8192, 50304
@@ -28,11 +29,15 @@ def run(i):
 for i in range(3):
     run(i)
 torch.cuda.synchronize()
+sampler = ClockSampler(0, period_ms=50).start()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-for i in range(12):
+for i in range(240):
     run(i)
 e1.record()
 torch.cuda.synchronize()
-us = e0.elapsed_time(e1) / 12 * 1e3
+us = e0.elapsed_time(e1) / 240 * 1e3
 print(f"softmax_ce fwd+bwd in place {rows}x{C} bf16: {us:.1f} us, {2 * rows * C * 2 / us / 1e3:.0f} GB/s of the 1R+1W minimum")
+import json
+print(json.dumps({"kernel": "softmax_ce_index", "rows": rows, "cols": C, "us": round(us, 1),
+                  "gbs_of_1r1w": round(2 * rows * C * 2 / us / 1e3), "clocks": sampler.stop()}))

@@ -19,6 +19,7 @@ from distriflow_b200.ops import _lib
 from distriflow_b200.ops._lib import check, ptr
 from distriflow_b200.parallel.engine import _OPT, _comm_sigs
 from distriflow_b200.parallel.symm import SymmetricHeap
+from distriflow_b200.utils.clocks import ClockSampler
 
 LINK_GBS = 770.0
 
@@ -47,6 +48,7 @@ def main():
         heap.view(po, (max_elems,), torch.bfloat16).normal_()
     epoch = [0]
     rows = []
+    sampler = ClockSampler(local).start() if rank == 0 else None
     for mb in sizes_mb:
         n = int(mb * (1 << 20)) // 2
         n = (n + world * 64 - 1) // (world * 64) * (world * 64)
@@ -111,6 +113,9 @@ def main():
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
+    if rank == 0:
+        rows.append({"clocks": sampler.stop()})
+        print(json.dumps(rows[-1]), flush=True)
     if rank == 0 and a.out:
         with open(a.out, "w") as f:
             for r in rows:

@@ -8,6 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
 from distriflow_b200.ops.dense import _init_sigs, gemm, pick_tile
+from distriflow_b200.utils.clocks import ClockSampler
 
 
 def timeit(fn, n=10, warm=3):
@@ -33,6 +34,7 @@ def main():
     tokens = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
     shapes = [("qkv", 768, 2304), ("proj", 768, 768), ("fc1", 768, 3072), ("fc2", 3072, 768), ("lm_head", 768, 50304)]
     rows = []
+    sampler = ClockSampler(0).start()
     for name, K, N in shapes:
         nbuf = max(2, int(200e6 // (tokens * max(K, N) * 2)) + 1)
         xs = [torch.randn(tokens, K, device=dev).bfloat16() for _ in range(nbuf)]
@@ -64,6 +66,7 @@ def main():
                          "cublas_tflops": round(flops / t_r / 1e9, 1), "ratio": round(t_r / t_o, 3)})
             print(json.dumps(rows[-1]), flush=True)
         del xs, dys
+    print(json.dumps({"clocks": sampler.stop()}), flush=True)        # clocks + throttle reasons while the rows above ran
     return rows
 
 

@@ -193,6 +193,41 @@ def test_device_work_queue_matches_host_dispatcher():
     assert wq.take().done
 
 
+def test_work_queue_stale_duplicate_completion_cannot_poison_the_next_epoch():
+    """A duplicate completion of a re-issued batch that arrives after its epoch has rolled over must not set a bit in the
+    next epoch's bitmap (the epoch then never completes and every taker spins)."""
+    from distriflow_b200.parallel.workqueue import DeviceWorkQueue
+    wq = DeviceWorkQueue.local(4, 3, device=dev())
+    first = [wq.take() for _ in range(4)]
+    dup = wq.take()                                     # fresh tickets are gone: batch 0 is re-issued
+    assert dup.batch == 0 and dup.epoch == 0
+    for t in first:
+        wq.complete(t)                                  # the fourth completion rolls the queue to epoch 1
+    wq.complete(dup)                                    # late duplicate from epoch 0: ignored
+    wq.complete(first[2])
+    second = [wq.take() for _ in range(4)]
+    assert [(t.batch, t.epoch) for t in second] == [(0, 1), (1, 1), (2, 1), (3, 1)]
+    for t in second:
+        wq.complete(t)
+    third = [wq.take() for _ in range(4)]
+    assert [(t.batch, t.epoch) for t in third] == [(0, 2), (1, 2), (2, 2), (3, 2)]
+    for t in third:
+        wq.complete(t)
+    assert wq.take().done
+
+
+def test_work_queue_bitmap_is_sized_from_the_dataset():
+    """60 000 examples at batch size 1 (a federated-style run over MNIST): the bitmap does not fit the 4 KiB signal pad and
+    moves to a heap block."""
+    from distriflow_b200.parallel.workqueue import DeviceWorkQueue
+    wq = DeviceWorkQueue.local(60000, 1, device=dev())
+    t0, t1 = wq.take(), wq.take()
+    assert (t0.batch, t1.batch) == (0, 1)
+    wq.complete(t0)
+    wq.complete(t1)
+    assert wq.take().batch == 2 and not wq.take().done
+
+
 def test_gather_batch_from_ticket():
     from distriflow_b200.parallel.workqueue import DeviceWorkQueue
     data = torch.arange(40 * 8, device=dev(), dtype=torch.float32).reshape(40, 8)

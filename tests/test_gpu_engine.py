@@ -334,3 +334,39 @@ def test_trainer_on_gpu_with_host_data_prefetch_and_resume(tmp_path):
     assert out2["resumed_from"] == 7 and out2["steps"] == 12 and out2["finished"]
     for a, b in zip(ref.full_precision_weights(), second.full_precision_weights()):
         assert float((a - b).abs().max()) < 1e-5
+
+
+@pytest.mark.parametrize("model_name", ["gpt2", "mnist_cnn", "resnet20"])
+def test_no_weight_is_read_after_its_bucket_is_reported(model_name):
+    """Every parameter in its own bucket + `debugPoison`: the engine overwrites a bucket's working weights with NaN the
+    moment its last gradient is reported (which is when the overlapped fused kernel may start rewriting them).  A backward
+    function that reports a weight and reads it afterwards (the round-1 `_MlpFn` / `_ThinConvFn` bug) yields NaN gradients,
+    which this test sees as a non-finite or diverging loss against the plain run."""
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    if model_name == "gpt2":
+        from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+        cfg = GPT2Config.tiny()
+        idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev())
+        batch = (idx[:, :-1].contiguous(), idx[:, 1:].contiguous())
+        make, loss_fn = (lambda: GPT2(cfg).to(dev())), gpt2_loss
+    elif model_name == "mnist_cnn":
+        from distriflow_b200.losses import get_loss
+        from distriflow_b200.models import mnist_cnn
+        ce = get_loss("softmaxCrossEntropy")
+        loss_fn = lambda m, a, b: ce(b, m(a))                                     # noqa: E731
+        make = lambda: mnist_cnn(5, dropout=False, softmax_output=False).to(dev())      # noqa: E731
+        batch = (torch.rand(32, 28, 28, 1, device=dev()), torch.randint(0, 5, (32,), device=dev()))
+    else:
+        from distriflow_b200.models.resnet import resnet20, resnet_loss as loss_fn
+        make = lambda: resnet20().to(dev())                                       # noqa: E731
+        batch = (torch.rand(64, 32, 32, 3, device=dev()), torch.randint(0, 10, (64,), device=dev()))
+    dt = "fp32" if model_name == "mnist_cnn" else "bf16"
+    out = {}
+    for poison in (False, True):
+        torch.manual_seed(0)
+        eng = DataParallelEngine(make(), loss_fn, {"optimizer": "sgd", "learningRate": 1e-2, "bucketBytes": 1, "dtype": dt,
+                                                   "gradDtype": dt, "debugPoison": poison, "fuseAllGather": False}, device=dev())
+        assert len(eng.buckets) == sum(1 for _ in eng.model.parameters())
+        out[poison] = [float(eng.step(*batch)) for _ in range(4)]
+    assert all(np.isfinite(v) for v in out[True]), out
+    assert max(abs(a - b) for a, b in zip(out[False], out[True])) < 2e-2 * max(1.0, abs(out[False][0])), out

@@ -48,6 +48,9 @@ def _sync_worker(rank, world, port, out, variants=("p2p", "nccl", "p2p-graph")):
             res["fused"] = getattr(model.first_dense_kernel(), "_dfb_ag", None) is not None
         w = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
         res[backend] = (losses, w.cpu())
+        if "w_init" not in res:
+            torch.manual_seed(0)
+            res["w_init"] = torch.cat([p.detach().float().reshape(-1) for p in GPT2(cfg).parameters() if p.requires_grad]).cpu()
         ws = [torch.empty_like(w) for _ in range(world)]
         dist.all_gather(ws, w)
         res[backend + "_same"] = all(torch.equal(ws[0], t) for t in ws)
@@ -69,7 +72,11 @@ def test_sync_engine_p2p_matches_nccl(world, tmp_path):
     ln, wn = res["nccl"]
     assert lp[-1] < lp[0]
     assert max(abs(a - b) for a, b in zip(lp, ln)) < 5e-2, (lp, ln)
-    assert float((wp - wn).abs().max()) < 2e-2          # bf16 gradients: fp32 pull-reduce vs NCCL's bf16 ring
+    # bf16 gradients, fp32 pull-reduce vs NCCL's bf16 ring: the two trajectories may differ by a fraction of the distance the
+    # weights actually moved, no more (an engine that applied no update at all fails this: its distance is the whole movement)
+    moved = float((wn - res["w_init"]).abs().max())
+    assert moved > 1e-3, moved
+    assert float((wp - wn).abs().max()) <= 0.2 * moved, (float((wp - wn).abs().max()), moved)
     assert res["fused"] and res["working_equals_master"], "a rank's working weights differ from the gathered masters"
     lg, wg = res["p2p-graph"]                                # same engine replayed from a CUDA graph (cross-rank barriers inside)
     assert res["p2p-graph_same"] and max(abs(a - b) for a, b in zip(lp, lg)) < 2e-2 and float((wp - wg).abs().max()) < 1e-2

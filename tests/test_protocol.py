@@ -150,6 +150,34 @@ def test_checkpoint_layout_and_resume(tmp_path):
         assert torch.equal(a, b)
 
 
+def test_checkpoint_resume_of_a_non_sequential_model_keeps_batchnorm_statistics(tmp_path):
+    """ResNet (not rebuildable from JSON, has BatchNorm buffers): save -> new process state -> `setup()` must come back with the
+    trained weights AND the moving statistics, read into the module the caller supplies."""
+    from distriflow_b200.models.resnet import resnet20
+    torch.manual_seed(0)
+    net = resnet20()
+    m = DistriServerTorchModel(str(tmp_path), net, {"loss": "softmaxCrossEntropy"})
+    m.setup()
+    net.train()
+    with torch.no_grad():
+        net(torch.randn(8, 32, 32, 3))                        # moves every moving_mean / moving_variance
+        for p in net.parameters():
+            p.add_(0.01)
+    m.save(force=True)
+    art = json.load(open(tmp_path / m.version / "model.json"))
+    names = [w["name"] for w in art["weightsManifest"][0]["weights"]]
+    assert any(n.endswith("moving_mean") for n in names) and any(n.endswith("moving_variance") for n in names)
+    torch.manual_seed(7)
+    m2 = DistriServerTorchModel(str(tmp_path), resnet20(), {"loss": "softmaxCrossEntropy"})
+    m2.setup()                                                 # resumes from the newest version directory
+    assert m2.version == m.version
+    sd1, sd2 = net.state_dict(), m2.model.state_dict()
+    assert set(sd1) == set(sd2)
+    for k in sd1:
+        assert torch.equal(sd1[k], sd2[k]), k
+    assert float(sd2["stem.bn.moving_mean"].abs().max()) > 0
+
+
 def test_reference_cnn_topology_loads_and_round_trips(tmp_path):
     ref = "/root/reference/experiment/mnist/model.json"
     if not os.path.exists(ref):

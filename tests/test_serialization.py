@@ -78,3 +78,36 @@ def test_serialize_round_trip_any_shape_and_dtype(shape, dtype, seed):
     data, meta = flat_serialize([t, t.reshape(-1)])
     a, b = flat_deserialize(data, meta)
     assert torch.equal(a, t) and torch.equal(b, t.reshape(-1))
+
+
+def test_wire_codec_is_data_only_and_round_trips_messages():
+    """The TCP frames carry a JSON header + raw blobs: every message type survives, nothing executable does."""
+    import pickle
+    import pytest as _pytest
+    import torch as _torch
+    from distriflow_b200.messages import (DataMsg, DownloadMsg, GradientMsg, ModelMsg, UploadMsg, WireFormatError, decode, encode)
+    from distriflow_b200.serialization import deserialize_var, serialize_var
+    w = _torch.arange(12, dtype=_torch.float32).reshape(3, 4)
+    g = _torch.randn(5).to(_torch.bfloat16)
+    down = DownloadMsg(ModelMsg("17", [serialize_var(w)]), {"learningRate": 0.5, "nested": {"a": [1, 2, (3, 4)]}},
+                       DataMsg(3, 1, serialize_var(w), serialize_var(_torch.tensor([1, 0, 2], dtype=_torch.int32)), "bid", "eid"))
+    up = UploadMsg("worker-1", GradientMsg("17", [serialize_var(g)]), batch=3, metrics=[0.25, float("inf")], epoch=1)
+    for msg in (("downloadVars", down), ("uploadVars", up), True, None, {"k": b"\x00\x01raw"}):
+        back = decode(encode(msg))
+        assert type(back) is type(msg)
+    ev, d2 = decode(encode(("downloadVars", down)))
+    assert ev == "downloadVars" and d2.model.version == "17" and d2.hyperparams["nested"]["a"][2] == (3, 4)
+    assert _torch.equal(deserialize_var(d2.model.vars[0]), w) and d2.data.batchId == "bid"
+    _, u2 = decode(encode(("uploadVars", up)))
+    assert _torch.equal(deserialize_var(u2.gradients.vars[0]), g) and u2.metrics[1] == float("inf")
+
+    class Evil:
+        def __reduce__(self):
+            return (print, ("pwned",))
+
+    with _pytest.raises(WireFormatError):
+        encode(("uploadVars", Evil()))                       # arbitrary objects cannot be sent ...
+    with _pytest.raises(WireFormatError):
+        decode(pickle.dumps(Evil()))                         # ... and a pickle is not a frame
+    with _pytest.raises(WireFormatError):
+        decode(encode({"a": 1})[:9])                         # truncated header
