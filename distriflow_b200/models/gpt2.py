@@ -3,8 +3,9 @@
 Not in the reference (it ships only the MNIST models); needed as a named workload.  All projections are Dense
 layers in the `[in, out]` layout (GPT-2's own Conv1D layout) running the tcgen05 GEMM, GELU and the bias are in
 the GEMM path, the tied LM head runs the same kernel on the `[vocab, d]` embedding table (K-major B operand), the
-loss is the fused softmax-CE kernel writing the logit gradient in place.  Attention, LayerNorm and the
-embedding gather stay on PyTorch ops (SURVEY §2.5 last paragraph).
+loss is the fused softmax-CE kernel writing the logit gradient in place, causal attention (forward and backward) is the
+tcgen05 kernel of `ops/csrc/attention_sm100.cu` on the packed QKV tensor, LayerNorm + residual adds are fused kernels; only
+the embedding gather stays on a PyTorch op.
 """
 from __future__ import annotations
 
@@ -35,7 +36,7 @@ class GPT2Config:
 
     @staticmethod
     def tiny() -> "GPT2Config":
-        return GPT2Config(vocab_size=500, n_positions=128, n_embd=128, n_layer=2, n_head=4, padded_vocab=512)
+        return GPT2Config(vocab_size=500, n_positions=128, n_embd=128, n_layer=2, n_head=2, padded_vocab=512)   # head dim 64: the tcgen05 attention kernel
 
 
 class Block(nn.Module):

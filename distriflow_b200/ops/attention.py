@@ -1,8 +1,9 @@
-"""Causal self-attention around the packed QKV projection.
+"""Causal self-attention on the packed QKV projection.
 
-The score/softmax/value product itself stays on `F.scaled_dot_product_attention` (attention is not one of the
-hand-written hot ops named in BASELINE.json).  What this module owns is the data movement around it, which the step
-profile showed to cost more than the attention forward itself.  `_PackedAttention` hands the library strided views of
+Head dimension 64 in bf16 (GPT-2) runs the hand-written tcgen05 kernels of `csrc/attention_sm100.cu`: forward and
+backward read `[B,T,3,H,D]` through 4-D TMA boxes and the backward writes `dqkv` in the same packed layout, so no head
+split, merge or gradient pack exists any more (`_FlashAttention`).  Other shapes fall back to the library SDPA wrappers
+below, kept from round 1: `_PackedAttention` hands the library strided views of
 the packed projection output `[B,T,3,H,D]` (measured on B200: the cuDNN kernels take them at the speed of contiguous
 operands and return the output in `[B,T,H,D]` memory order, so splitting and merging heads are views), and packs the
 three gradients, which come back as separate `[B,T,H,D]` tensors, into `[B,T,3,H,D]` with the hand-written row-copy
@@ -11,8 +12,14 @@ kept for operands the packed path does not cover.
 """
 from __future__ import annotations
 
+import ctypes
+import os
+
 import torch
 import torch.nn.functional as F
+
+from . import _lib
+from ._lib import c_int, c_void_p, check, ptr, stream
 
 
 def _bthd_dense(t: torch.Tensor, B: int, H: int, T: int, D: int) -> bool:
@@ -108,13 +115,79 @@ class _MergeHeads(torch.autograd.Function):
         return out
 
 
+class _FlashAttention(torch.autograd.Function):
+    """`qkv [B,T,3*H*64]` bf16 -> `[B,T,H*64]` through `dfb_attn_fwd` / `dfb_attn_bwd` (causal, scale 1/8)."""
+
+    @staticmethod
+    def forward(ctx, qkv, n_head):
+        L = _sigs()
+        B, T, C3 = qkv.shape
+        D = C3 // (3 * n_head)
+        q = qkv.detach()
+        if not q.is_contiguous():
+            q = q.contiguous()
+        out = torch.empty((B, T, n_head * D), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((B, n_head, T), dtype=torch.float32, device=qkv.device)
+        check(L.dfb_attn_fwd(ptr(q), ptr(out), ptr(lse), B, T, n_head, D, stream()), "dfb_attn_fwd")
+        ctx.dims = (B, T, n_head, D)
+        ctx.save_for_backward(q, out, lse)
+        return out
+
+    @staticmethod
+    def backward(ctx, do):
+        L = _sigs()
+        q, out, lse = ctx.saved_tensors
+        B, T, H, D = ctx.dims
+        do = do.contiguous()
+        if do.dtype != q.dtype:
+            do = do.to(q.dtype)
+        dqkv = torch.empty_like(q)
+        scratch = _bwd_scratch(q.device, int(L.dfb_attn_bwd_scratch_bytes(B, T, H, D)))
+        check(L.dfb_attn_bwd(ptr(q), ptr(out), ptr(do), ptr(lse), ptr(dqkv), ptr(scratch), ctypes.c_size_t(scratch.numel()),
+                             B, T, H, D, stream()), "dfb_attn_bwd")
+        return dqkv, None
+
+
+_SCRATCH = {}
+
+
+def _bwd_scratch(device: torch.device, nbytes: int) -> torch.Tensor:
+    """delta + the fp32 dQ accumulator of the backward kernel.  One zero-initialised buffer per device, shared by every
+    layer (the kernel leaves the accumulator at zero again); created during the eager warm-up steps, i.e. before a CUDA
+    graph capture of the step."""
+    key = (device.type, device.index)
+    buf = _SCRATCH.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _SCRATCH[key] = buf
+    return buf
+
+
+def _sigs():
+    L = _lib.lib()
+    if not getattr(L, "_dfb_attn_sigs", False):
+        L.dfb_attn_supported.restype = c_int
+        L.dfb_attn_supported.argtypes = [c_int] * 4
+        L.dfb_attn_fwd.restype = c_int
+        L.dfb_attn_fwd.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
+        L.dfb_attn_bwd_scratch_bytes.restype = ctypes.c_size_t
+        L.dfb_attn_bwd_scratch_bytes.argtypes = [c_int] * 4
+        L.dfb_attn_bwd.restype = c_int
+        L.dfb_attn_bwd.argtypes = [c_void_p] * 6 + [ctypes.c_size_t, c_int, c_int, c_int, c_int, c_void_p]
+        L._dfb_attn_sigs = True
+    return L
+
+
 PACKED = True     # strided-view path (one gradient pack per layer); False: explicit head permutations
+FLASH = os.environ.get("DFB_ATTN", "flash") == "flash"      # DFB_ATTN=sdpa: library attention for A/B runs
 
 
 def causal_self_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
     """`qkv` `[B, T, 3*H*D]` (q | k | v along the last axis) -> `[B, T, H*D]`."""
     B, T, C3 = qkv.shape
     D = C3 // (3 * n_head)
+    if qkv.is_cuda and FLASH and qkv.dtype == torch.bfloat16 and D == 64:
+        return _FlashAttention.apply(qkv, n_head)
     if qkv.is_cuda and PACKED and (n_head * D * qkv.element_size()) % 16 == 0:
         return _PackedAttention.apply(qkv, n_head)
     if qkv.is_cuda and (D * qkv.element_size()) % 16 == 0:

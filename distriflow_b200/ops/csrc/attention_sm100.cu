@@ -1,0 +1,677 @@
+// Causal self-attention for sm_100a, forward and backward, straight on the packed QKV projection.
+//
+//   qkv  [B, T, 3, H, 64] bf16   (the output of the c_attn Dense layer, untouched: no head split, no transpose)
+//   out  [B, T, H, 64]    bf16   (= [B, T, H*64], the input of the c_proj Dense layer)
+//   lse  [B, H, T]        fp32   (log-sum-exp of the scaled scores, kept for the backward pass)
+//   dqkv [B, T, 3, H, 64] bf16   (gradient in the same packed layout: the c_attn wgrad/dgrad GEMMs read it as is)
+//
+// Both products of the forward pass (S = Q K^T and O = P V) and all five of the backward pass run on tcgen05.mma with the
+// accumulators in TMEM; Q/K/V/dO tiles come in through 4-D TMA boxes cut directly out of the packed tensor (coordinates
+// {d, t, which*H + h, b}: rows beyond T are zero-filled and never bleed into the next sequence); the softmax runs in the
+// warps that drain TMEM (one query row per thread, so row max / row sum need no shuffles).
+// No counterpart in the reference (its models have no attention); it is on the hot path of BASELINE.json config 5 (GPT-2),
+// where the forward pass is `predictOnBatch` inside `tf.variableGrads` (/root/reference/src/common/models.ts:137-142).
+//
+// Operand layouts (all SWIZZLE_128B, 128-byte rows of 64 bf16):
+//   Q, K tiles   [128 rows x 64 d]         K-major A / B of S = Q K^T and dP = dO V^T
+//   V tile       [128 kv rows x 64 d]      MN-major B of O = P V (rows are the contraction index)
+//   P, dS tiles  two 64-column blocks of [128 rows x 128 B], written by the softmax threads with the same XOR swizzle the
+//                TMA would apply.  The same bytes are a K-major A operand (P V, dS K) and an MN-major A operand
+//                (P^T dO, dS^T Q): the transposes of the backward pass cost nothing.
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+namespace dfb {
+
+constexpr int kAttD = 64;                        // head dimension (one 128-byte swizzle row)
+constexpr int kAttTile = 128;                    // query rows and key rows per tile
+constexpr int kAttTileBytes = kAttTile * kAttD * 2;   // 16 KiB
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct AttnFwdParams {
+  float* lse;          // [B, H, T]
+  int B, T, H;
+  int n_qt;            // query tiles per sequence = ceil(T / 128)
+  float scale_log2;    // log2(e) / sqrt(D)
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// One 128-byte row of a SWIZZLE_128B tile: eight 16-byte pieces, piece j of row r lives at ((j ^ (r & 7)) << 4).
+__device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, int piece, uint4 q) {
+  *reinterpret_cast<uint4*>(tile + row * 128 + ((piece ^ (row & 7)) << 4)) = q;
+}
+
+// ============================================================================================== forward
+// One CTA per (128 query rows, head, batch); two CTAs share an SM (80 KiB of shared memory, 256 TMEM columns each), so one
+// CTA's softmax (MUFU-bound: 128 exp2 per thread and key tile) overlaps the other's MMAs.
+//   warp 0      TMA producer (Q once, then K_j / V_j, single-buffered: K_{j+1} is requested as soon as S_j has been issued)
+//   warp 1      TMEM allocation + MMA issue (one elected lane)
+//   warps 2..5  softmax: thread = query row.  Per key tile: row max over S_j in TMEM, P_j = exp2(S_j*c - m*c) -> bf16 ->
+//               shared memory, then O_j = P_j V_j is read back from TMEM and folded into the fp32 accumulator held in
+//               registers (acc = acc * alpha + O_j), so no rescaling pass over TMEM exists.
+constexpr int kFwdThreads = 192;
+constexpr int kFwdSmem = 5 * kAttTileBytes + 256 + 1024;      // Q, K, V, P (2 blocks) + barriers + alignment slack
+constexpr uint32_t kFwdTmemCols = 256;                        // S: columns [0,128), O_j: [128,192)
+
+__global__ void __launch_bounds__(kFwdThreads, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, const AttnFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kAttTileBytes;
+  uint8_t* sV = smem + 2 * kAttTileBytes;
+  uint8_t* sP = smem + 3 * kAttTileBytes;                     // 32 KiB: kv columns [0,64) then [64,128)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * kAttTileBytes);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;
+  uint64_t* k_empty = bars + 2;
+  uint64_t* v_full = bars + 3;
+  uint64_t* v_empty = bars + 4;
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_ready = bars + 6;
+  uint64_t* o_full = bars + 7;
+  uint64_t* o_empty = bars + 8;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp_idx = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // heaviest tiles (most key tiles) first: blockIdx.x = (n_qt - 1 - qt) * (B*H) + bh
+  const int bh_total = p.B * p.H;
+  const int qt = p.n_qt - 1 - (int)(blockIdx.x / bh_total);
+  const int bh = (int)(blockIdx.x % bh_total);
+  const int b = bh / p.H, h = bh % p.H;
+  const int q0 = qt * kAttTile;
+  const int n_kv = qt + 1;                                     // key tiles 0..qt; tile qt is the diagonal one
+
+  if (warp_idx == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmO);
+    mbar_init(q_full, 1);
+    mbar_init(k_full, 1);
+    mbar_init(k_empty, 1);
+    mbar_init(v_full, 1);
+    mbar_init(v_empty, 1);
+    mbar_init(s_full, 1);
+    mbar_init(p_ready, 4);      // one arrive per softmax warp
+    mbar_init(o_full, 1);
+    mbar_init(o_empty, 4);
+    fence_mbar_init();
+  }
+  if (warp_idx == 1) tmem_alloc<kFwdTmemCols>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_s = tmem_base;
+  const uint32_t tmem_o = tmem_base + 128;
+
+  if (warp_idx == 0) {
+    // ===================================================================== TMA producer
+    if (elect_one()) {
+      mbar_expect_tx(q_full, kAttTileBytes);
+      tma_load_4d(sQ, &tmQKV, q_full, 0, q0, h, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const uint32_t ph = j & 1;
+        mbar_wait(k_empty, ph ^ 1);
+        mbar_expect_tx(k_full, kAttTileBytes);
+        tma_load_4d(sK, &tmQKV, k_full, 0, j * kAttTile, p.H + h, b);
+        mbar_wait(v_empty, ph ^ 1);
+        mbar_expect_tx(v_full, kAttTileBytes);
+        tma_load_4d(sV, &tmQKV, v_full, 0, j * kAttTile, 2 * p.H + h, b);
+      }
+    }
+  } else if (warp_idx == 1) {
+    // ===================================================================== MMA issuer
+    if (elect_one()) {
+      const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);     // S[128 q x 128 kv]  = Q (K-major) x K (K-major)
+      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);      // O[128 q x 64 d]    = P (K-major) x V (MN-major)
+      const uint64_t dq = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
+      const uint64_t dk = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
+      const uint64_t dv = make_smem_desc_sw128(smem_u32(sV), kAttTileBytes, 1024);
+      const uint64_t dp0 = make_smem_desc_sw128(smem_u32(sP), 0, 1024);
+      const uint64_t dp1 = make_smem_desc_sw128(smem_u32(sP + kAttTileBytes), 0, 1024);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < n_kv; ++j) {
+        const uint32_t ph = j & 1;
+        // S_j: the S columns are free (the softmax warps signalled p_ready(j-1) after their last read of S_{j-1})
+        mbar_wait(k_full, ph);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(k_empty);
+        umma_commit(s_full);
+        // O_j = P_j V_j once the softmax warps have written P_j and have taken O_{j-1} out of TMEM
+        mbar_wait(p_ready, ph);
+        mbar_wait(v_full, ph);
+        if (j > 0) mbar_wait(o_empty, ph ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t a = (k < 4 ? dp0 : dp1) + (uint64_t)((k & 3) * 2);       // 32 bytes per 16-wide k step inside a block
+          umma_f16(tmem_o, a, dv + (uint64_t)(k * 128), idesc_o, k > 0 ? 1u : 0u);   // 16 kv rows x 128 B per k step
+        }
+        umma_commit(v_empty);
+        umma_commit(o_full);
+      }
+    }
+  } else {
+    // ===================================================================== softmax warps (2..5), thread = query row
+    const int quarter = warp_idx & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
+    const float c = p.scale_log2;
+    float m_prev = -INFINITY, l = 0.f;
+    float acc[kAttD];
+#pragma unroll
+    for (int i = 0; i < kAttD; ++i) acc[i] = 0.f;
+
+    for (int j = 0; j < n_kv; ++j) {
+      const uint32_t ph = j & 1;
+      const bool diag = (j == n_kv - 1);
+      mbar_wait(s_full, ph);
+      tc_fence_after();
+      // pass 1: row maximum
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int ch = 0; ch < 4; ++ch) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_s + lane_sel + ch * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float v = __uint_as_float(r[i]);
+          if (diag && ch * 32 + i > row) v = -INFINITY;
+          mx = fmaxf(mx, v);
+        }
+      }
+      const float m_new = fmaxf(m_prev, mx);
+      const float mc = m_new * c;
+      // pass 2: P = exp2(S*c - m*c), row sum, bf16 into the swizzled P tile
+      float sum = 0.f;
+#pragma unroll 1
+      for (int ch = 0; ch < 4; ++ch) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_s + lane_sel + ch * 32, r);
+        tmem_ld_wait();
+        float e[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float v = __uint_as_float(r[i]);
+          if (diag && ch * 32 + i > row) v = -INFINITY;
+          e[i] = exp2f(fmaf(v, c, -mc));
+          sum += e[i];
+        }
+        uint8_t* blk = sP + (ch >> 1) * kAttTileBytes;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 pk = {pack_bf16(e[8 * q4 + 0], e[8 * q4 + 1]), pack_bf16(e[8 * q4 + 2], e[8 * q4 + 3]),
+                      pack_bf16(e[8 * q4 + 4], e[8 * q4 + 5]), pack_bf16(e[8 * q4 + 6], e[8 * q4 + 7])};
+          st_swizzled_row_piece(blk, row, (ch & 1) * 4 + q4, pk);
+        }
+      }
+      tc_fence_before();            // our TMEM reads of S_j are done before the MMA thread may overwrite S
+      fence_proxy_async_smem();     // P_j (generic-proxy stores) visible to the tensor core (async proxy)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_ready);
+      const float alpha = exp2f((m_prev - m_new) * c);        // first tile: exp2(-inf) = 0
+      l = l * alpha + sum;
+      m_prev = m_new;
+      // fold O_j into the accumulator
+      mbar_wait(o_full, ph);
+      tc_fence_after();
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_o + lane_sel + hh * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[hh * 32 + i] = fmaf(acc[hh * 32 + i], alpha, __uint_as_float(r[i]));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_empty);
+    }
+
+    // epilogue: O = acc / l -> bf16 -> swizzled staging (the P buffer: every MMA that read it has completed) -> TMA store
+    const float inv_l = 1.f / l;
+    if (q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m_prev * c + log2f(l)) * kLn2;
+#pragma unroll
+    for (int q8 = 0; q8 < 8; ++q8) {
+      uint4 pk = {pack_bf16(acc[8 * q8 + 0] * inv_l, acc[8 * q8 + 1] * inv_l), pack_bf16(acc[8 * q8 + 2] * inv_l, acc[8 * q8 + 3] * inv_l),
+                  pack_bf16(acc[8 * q8 + 4] * inv_l, acc[8 * q8 + 5] * inv_l), pack_bf16(acc[8 * q8 + 6] * inv_l, acc[8 * q8 + 7] * inv_l)};
+      st_swizzled_row_piece(sP, row, q8, pk);
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1, 128);
+    if (threadIdx.x == 64) {
+      tma_store_4d(&tmO, sP, 0, q0, h, b);
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp_idx == 1) {
+    tc_fence_after();
+    tmem_dealloc<kFwdTmemCols>(tmem_base);
+  }
+}
+
+
+// ============================================================================================== backward
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (the row term of the softmax Jacobian), eight threads per row.
+__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                                         float* __restrict__ delta, int B, int T, int H) {
+  const long rows = (long)B * T * H;
+  const long gid = (long)blockIdx.x * 256 + threadIdx.x;
+  const long r = gid >> 3;
+  const int part = (int)(gid & 7);
+  float acc = 0.f;
+  if (r < rows) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(o + r * kAttD) + part);
+    const uint4 g = __ldg(reinterpret_cast<const uint4*>(d_o + r * kAttD) + part);
+    const __nv_bfloat162* ah = reinterpret_cast<const __nv_bfloat162*>(&a);
+    const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&g);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 x = __bfloat1622float2(ah[i]), y = __bfloat1622float2(gh[i]);
+      acc = fmaf(x.x, y.x, fmaf(x.y, y.y, acc));
+    }
+  }
+  acc += __shfl_xor_sync(0xffffffff, acc, 1);
+  acc += __shfl_xor_sync(0xffffffff, acc, 2);
+  acc += __shfl_xor_sync(0xffffffff, acc, 4);
+  if (r < rows && part == 0) {
+    const long h = r % H, bt = r / H, t = bt % T, b = bt / T;
+    delta[(b * H + h) * T + t] = acc;
+  }
+}
+
+// dq_acc [B,T,H,64] fp32 -> dqkv[b,t,0,h,:] bf16, and the accumulator is cleared for the next call (it must start at zero).
+__global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long rows_bt,
+                                                              int H) {
+  const long vec_per_bt = (long)H * kAttD / 8;                 // 8 elements per thread
+  const long total = rows_bt * vec_per_bt;
+  for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+    const long bt = i / vec_per_bt, c = i - bt * vec_per_bt;
+    float4* src = reinterpret_cast<float4*>(dq_acc + bt * H * kAttD + c * 8);
+    const float4 a = src[0], b = src[1];
+    uint4 pk = {pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w)};
+    *reinterpret_cast<uint4*>(dqkv + bt * 3 * H * kAttD + c * 8) = pk;
+    src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+__device__ __forceinline__ void tma_reduce_add_4d(const void* tmap, const void* smem_src, int32_t c0, int32_t c1, int32_t c2,
+                                                  int32_t c3) {
+  asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n" ::"l"(
+                   reinterpret_cast<uint64_t>(tmap)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+struct AttnBwdParams {
+  const float* lse;      // [B, H, T]
+  const float* delta;    // [B, H, T]
+  int B, T, H;
+  int n_qt;
+  float scale;           // 1 / sqrt(D)
+  float scale_log2;      // scale * log2(e)
+};
+
+// One CTA per (128 key rows, head, batch), one CTA per SM.  K_j and V_j stay in shared memory; the CTA walks the query
+// tiles i = j .. n-1 (causal) and per tile issues five products:
+//     S  = Q_i K_j^T          dP = dO_i V_j^T                      (fresh accumulators, TMEM columns [0,128) / [128,256))
+//     dV += P^T dO_i          dK += dS^T Q_i                        (accumulate over i, columns [256,320) / [320,384))
+//     dQ_i = dS K_j                                                  (fresh, columns [384,448); added to the fp32 dQ
+//                                                                     accumulator in global memory with a TMA reduce-add)
+// with P = exp2(S*c - lse*log2e) and dS = P * (dP - delta) / sqrt(D) computed by eight warps between the two groups
+// (thread = query row x half of the key columns).  P and dS are written once to shared memory and read by the tensor core
+// both as K-major (dS K) and as MN-major (P^T dO, dS^T Q) operands.
+//   warp 0      TMA producer: K_j, V_j, then a 2-stage ring of {Q_i, dO_i}
+//   warp 1      TMEM allocation + MMA issue
+//   warps 2..9  softmax / dS, dQ drain, final dK / dV epilogue
+constexpr int kBwdThreads = 320;
+constexpr int kBwdStageBytes = 2 * kAttTileBytes;             // Q_i + dO_i
+constexpr int kBwdSmem = 2 * kAttTileBytes + 2 * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 256 + 1024;
+constexpr uint32_t kBwdTmemCols = 512;
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ, const AttnBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = smem + kAttTileBytes;
+  uint8_t* sQdO = smem + 2 * kAttTileBytes;                                   // stage s: Q at +s*32K, dO at +s*32K+16K
+  uint8_t* sP = sQdO + 2 * kBwdStageBytes;                                    // 32 KiB
+  uint8_t* sdS = sP + 2 * kAttTileBytes;                                      // 32 KiB
+  uint8_t* sdQ = sdS + 2 * kAttTileBytes;                                     // 32 KiB fp32 staging: d columns [0,32) then [32,64)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdQ + 2 * kAttTileBytes);
+  uint64_t* kv_full = bars + 0;
+  uint64_t* qdo_full = bars + 1;      // [2]
+  uint64_t* qdo_empty = bars + 3;     // [2]
+  uint64_t* sdp_full = bars + 5;
+  uint64_t* pds_ready = bars + 6;
+  uint64_t* dq_full = bars + 7;
+  uint64_t* dq_empty = bars + 8;
+  uint64_t* dkv_full = bars + 9;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+
+  const int warp_idx = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // heaviest key tiles (lowest index: most query tiles) first
+  const int bh_total = p.B * p.H;
+  const int jt = (int)(blockIdx.x / bh_total);
+  const int bh = (int)(blockIdx.x % bh_total);
+  const int b = bh / p.H, h = bh % p.H;
+  const int kv0 = jt * kAttTile;
+  const int n_it = p.n_qt - jt;                                 // query tiles jt .. n_qt-1
+
+  if (warp_idx == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQKV);
+    tma_prefetch_desc(&tmDQ);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_ready, 8);      // one arrive per compute warp
+    mbar_init(dq_full, 1);
+    mbar_init(dq_empty, 8);
+    mbar_init(dkv_full, 1);
+    fence_mbar_init();
+  }
+  if (warp_idx == 1) tmem_alloc<kBwdTmemCols>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 128, tmem_dv = tmem_base + 256, tmem_dk = tmem_base + 320,
+                 tmem_dq = tmem_base + 384;
+
+  if (warp_idx == 0) {
+    // ===================================================================== TMA producer
+    if (elect_one()) {
+      mbar_expect_tx(kv_full, 2 * kAttTileBytes);
+      tma_load_4d(sK, &tmQKV, kv_full, 0, kv0, p.H + h, b);
+      tma_load_4d(sV, &tmQKV, kv_full, 0, kv0, 2 * p.H + h, b);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        mbar_wait(&qdo_empty[st], ph ^ 1);
+        mbar_expect_tx(&qdo_full[st], kBwdStageBytes);
+        const int q0 = (jt + it) * kAttTile;
+        tma_load_4d(sQdO + st * kBwdStageBytes, &tmQKV, &qdo_full[st], 0, q0, h, b);
+        tma_load_4d(sQdO + st * kBwdStageBytes + kAttTileBytes, &tmDO, &qdo_full[st], 0, q0, h, b);
+      }
+    }
+  } else if (warp_idx == 1) {
+    // ===================================================================== MMA issuer
+    if (elect_one()) {
+      const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);      // S, dP
+      const uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);       // dV = P^T dO, dK = dS^T Q  (both operands MN-major)
+      const uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);       // dQ = dS K
+      const uint64_t dk_kmaj = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
+      const uint64_t dv_kmaj = make_smem_desc_sw128(smem_u32(sV), 0, 1024);
+      const uint64_t dk_mn = make_smem_desc_sw128(smem_u32(sK), kAttTileBytes, 1024);
+      const uint64_t dp_mn = make_smem_desc_sw128(smem_u32(sP), kAttTileBytes, 1024);         // A MN-major: two 64-wide atoms
+      const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
+      const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
+      const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = it & 1, sph = (it >> 1) & 1;
+        const uint64_t dq_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), 0, 1024);
+        const uint64_t ddo_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), 0, 1024);
+        const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), kAttTileBytes, 1024);
+        const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
+        mbar_wait(&qdo_full[st], sph);
+        tc_fence_after();
+        // S and dP (their TMEM columns are free: pds_ready(it-1) was waited for below)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq_kmaj + (uint64_t)(k * 2), dk_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_f16(tmem_dp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(sdp_full);
+        mbar_wait(pds_ready, ph);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)         // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
+          umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)         // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
+          umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        if (it > 0) {
+          mbar_wait(dq_empty, ph ^ 1);      // the compute warps have taken dQ_{i-1} out of TMEM
+          tc_fence_after();
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k)         // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
+          umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
+        umma_commit(&qdo_empty[st]);
+        umma_commit(dq_full);               // also means: P / dS in shared memory have been consumed
+      }
+      umma_commit(dkv_full);
+    }
+  } else {
+    // ===================================================================== compute warps 2..9
+    const int quarter = warp_idx & 3;
+    const int half = (warp_idx - 2) >> 2;                       // key columns [64*half, 64*half + 64)
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
+    const int ctid = threadIdx.x - 64;                          // 0..255
+    for (int it = 0; it < n_it; ++it) {
+      const uint32_t ph = it & 1;
+      const int q0 = (jt + it) * kAttTile;
+      const bool diag = (it == 0);
+      float lse2 = 0.f, dl = 0.f;
+      if (q0 + row < p.T) {
+        lse2 = __ldg(p.lse + (size_t)bh * p.T + q0 + row) * kLog2e;
+        dl = __ldg(p.delta + (size_t)bh * p.T + q0 + row);
+      }
+      mbar_wait(sdp_full, ph);
+      tc_fence_after();
+      uint8_t* pblk = sP + half * kAttTileBytes;
+      uint8_t* dsblk = sdS + half * kAttTileBytes;
+#pragma unroll 1
+      for (int ch = 0; ch < 2; ++ch) {
+        const int col0 = half * 64 + ch * 32;
+        uint32_t rs[32], rp[32];
+        tmem_ld_32x32(tmem_s + lane_sel + col0, rs);
+        tmem_ld_32x32(tmem_dp + lane_sel + col0, rp);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          float pv[8], dv[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int i = 8 * q4 + e;
+            float pe = exp2f(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
+            if (diag && col0 + i > row) pe = 0.f;
+            pv[e] = pe;
+            dv[e] = pe * (__uint_as_float(rp[i]) - dl) * p.scale;
+          }
+          uint4 pk = {pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7])};
+          uint4 dk = {pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7])};
+          st_swizzled_row_piece(pblk, row, ch * 4 + q4, pk);
+          st_swizzled_row_piece(dsblk, row, ch * 4 + q4, dk);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_ready);
+
+      // dQ_i: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator
+      mbar_wait(dq_full, ph);
+      tc_fence_after();
+      {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_dq + lane_sel + half * 32, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dq_empty);
+        if (ctid == 0) tma_store_wait_read<0>();                // the previous reduce has finished reading the staging buffer
+        named_bar_sync(1, 256);
+        uint8_t* blk = sdQ + half * kAttTileBytes;
+#pragma unroll
+        for (int q8 = 0; q8 < 8; ++q8) {
+          uint4 pk = {r[4 * q8 + 0], r[4 * q8 + 1], r[4 * q8 + 2], r[4 * q8 + 3]};
+          st_swizzled_row_piece(blk, row, q8, pk);
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 256);
+        if (ctid == 0) {
+          tma_reduce_add_4d(&tmDQ, sdQ, 0, q0, h, b);
+          tma_reduce_add_4d(&tmDQ, sdQ + kAttTileBytes, 32, q0, h, b);
+          tma_store_commit();
+        }
+      }
+    }
+    // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) -> bf16 -> TMA store into dqkv
+    mbar_wait(dkv_full, 0);
+    tc_fence_after();
+    {
+      uint8_t* stage = half == 0 ? sP : sdS;                    // both free: every MMA has completed
+      const uint32_t src = (half == 0 ? tmem_dv : tmem_dk) + lane_sel;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        uint32_t r[32];
+        tmem_ld_32x32(src + hh * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint4 pk = {pack_bf16(__uint_as_float(r[8 * q4 + 0]), __uint_as_float(r[8 * q4 + 1])),
+                      pack_bf16(__uint_as_float(r[8 * q4 + 2]), __uint_as_float(r[8 * q4 + 3])),
+                      pack_bf16(__uint_as_float(r[8 * q4 + 4]), __uint_as_float(r[8 * q4 + 5])),
+                      pack_bf16(__uint_as_float(r[8 * q4 + 6]), __uint_as_float(r[8 * q4 + 7]))};
+          st_swizzled_row_piece(stage, row, hh * 4 + q4, pk);
+        }
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 256);
+      if (ctid == 0) {
+        tma_store_4d(&tmDQKV, sP, 0, kv0, 2 * p.H + h, b);      // dV
+        tma_store_4d(&tmDQKV, sdS, 0, kv0, p.H + h, b);         // dK
+        tma_store_commit();
+        tma_store_wait<0>();
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp_idx == 1) {
+    tc_fence_after();
+    tmem_dealloc<kBwdTmemCols>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- host side
+static int make_packed_map(CUtensorMap* tm, const void* base, int B, int T, int H, int which_count) {
+  // [B, T, which_count, H, 64] bf16 seen as {d, t, which*H + h, b}
+  const uint64_t row = (uint64_t)which_count * H * kAttD * 2;
+  uint64_t dims[4] = {(uint64_t)kAttD, (uint64_t)T, (uint64_t)which_count * H, (uint64_t)B};
+  uint64_t str[3] = {row, (uint64_t)kAttD * 2, (uint64_t)T * row};
+  uint32_t box[4] = {(uint32_t)kAttD, (uint32_t)kAttTile, 1, 1};
+  return encode_tmap(tm, base, 0, 4, dims, str, box, nullptr, 1);
+}
+
+}  // namespace dfb
+
+using namespace dfb;
+
+DFB_API int dfb_attn_supported(int B, int T, int H, int D) {
+  return (D == kAttD && B >= 1 && T >= 1 && H >= 1) ? 1 : 0;
+}
+
+// out [B,T,H,64] bf16, lse [B,H,T] fp32.  Causal, scale = 1/sqrt(64).
+DFB_API int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, cudaStream_t stream) {
+  DFB_REQUIRE(dfb_attn_supported(B, T, H, D), "attn_fwd: head dimension %d not supported (64 only)", D);
+  DFB_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attn_fwd: operands must be 16-byte aligned");
+  CUtensorMap tmQKV, tmO;
+  if (make_packed_map(&tmQKV, qkv, B, T, H, 3)) return 4;
+  if (make_packed_map(&tmO, out, B, T, H, 1)) return 4;
+  AttnFwdParams p;
+  p.lse = lse; p.B = B; p.T = T; p.H = H;
+  p.n_qt = ceil_div(T, kAttTile);
+  p.scale_log2 = kLog2e / sqrtf((float)D);
+  static bool attr_done[64] = {};
+  int dev = 0;
+  DFB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    DFB_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+    attr_done[dev & 63] = true;
+  }
+  const long grid = (long)p.n_qt * B * H;
+  attn_fwd_kernel<<<(unsigned)grid, kFwdThreads, kFwdSmem, stream>>>(tmQKV, tmO, p);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DFB_API size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D) {
+  // delta [B,H,T] fp32 (rounded to 256 B) + dQ accumulator [B,T,H,D] fp32
+  const size_t delta = (((size_t)B * H * T * 4) + 255) / 256 * 256;
+  return delta + (size_t)B * T * H * D * 4;
+}
+
+// dqkv [B,T,3,H,64] bf16 (fully written).  `scratch` holds delta and the fp32 dQ accumulator; the accumulator part
+// (everything after the first round256(B*H*T*4) bytes) must be ZERO on entry and is zero again on return.
+DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv, void* scratch,
+                         size_t scratch_bytes, int B, int T, int H, int D, cudaStream_t stream) {
+  DFB_REQUIRE(dfb_attn_supported(B, T, H, D), "attn_bwd: head dimension %d not supported (64 only)", D);
+  DFB_REQUIRE(scratch != nullptr && scratch_bytes >= dfb_attn_bwd_scratch_bytes(B, T, H, D), "attn_bwd: scratch of %zu bytes required",
+              dfb_attn_bwd_scratch_bytes(B, T, H, D));
+  const size_t delta_bytes = (((size_t)B * H * T * 4) + 255) / 256 * 256;
+  float* delta = reinterpret_cast<float*>(scratch);
+  float* dq_acc = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + delta_bytes);
+  CUtensorMap tmQKV, tmDO, tmDQKV, tmDQ;
+  if (make_packed_map(&tmQKV, qkv, B, T, H, 3)) return 4;
+  if (make_packed_map(&tmDO, d_out, B, T, H, 1)) return 4;
+  if (make_packed_map(&tmDQKV, dqkv, B, T, H, 3)) return 4;
+  {
+    const uint64_t row = (uint64_t)H * kAttD * 4;
+    uint64_t dims[4] = {(uint64_t)kAttD, (uint64_t)T, (uint64_t)H, (uint64_t)B};
+    uint64_t str[3] = {row, (uint64_t)kAttD * 4, (uint64_t)T * row};
+    uint32_t box[4] = {32, (uint32_t)kAttTile, 1, 1};
+    if (encode_tmap(&tmDQ, dq_acc, 1, 4, dims, str, box, nullptr, 1)) return 4;
+  }
+  AttnBwdParams p;
+  p.lse = lse; p.delta = delta; p.B = B; p.T = T; p.H = H;
+  p.n_qt = ceil_div(T, kAttTile);
+  p.scale = 1.f / sqrtf((float)D);
+  p.scale_log2 = p.scale * kLog2e;
+  static bool attr_done[64] = {};
+  int dev = 0;
+  DFB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    DFB_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+    attr_done[dev & 63] = true;
+  }
+  const long rows = (long)B * T * H;
+  attn_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H);
+  const long grid = (long)p.n_qt * B * H;
+  attn_bwd_kernel<<<(unsigned)grid, kBwdThreads, kBwdSmem, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, p);
+  const long vecs = (long)B * T * H * kAttD / 8;
+  long blocks = (vecs + 255) / 256;
+  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
+  attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}

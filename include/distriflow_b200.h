@@ -144,6 +144,17 @@ int dfb_wq_pad_capacity(void);
 int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long row_bytes, int batch_size, long rows,
                      void* stream);
 
+/* ---- causal self-attention on the packed QKV projection (no counterpart in the reference: its models have no attention;
+ * hot path of BASELINE.json config 5).  tcgen05 + TMEM + TMA, head dimension 64, bf16, scale 1/sqrt(D).
+ * qkv / dqkv: [B,T,3,H,D]; out / d_out: [B,T,H,D]; lse: [B,H,T] fp32.
+ * scratch (dfb_attn_bwd_scratch_bytes): delta [B,H,T] fp32 rounded to 256 B, then the fp32 dQ accumulator [B,T,H,D], which
+ * must be zero on entry and is zero again on return. */
+int dfb_attn_supported(int B, int T, int H, int D);
+int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
+size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D);
+int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv, void* scratch,
+                 size_t scratch_bytes, int B, int T, int H, int D, void* stream);
+
 /* ---- normalisation and layout kernels (no counterpart in the reference: its models are Dense / Conv2D / MaxPool) ------------
  * fused residual add + LayerNorm: s = x + r (r nullable), y = LN(s) * gamma + beta; mean / rstd: [rows] fp32 */
 int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamma, const void* beta, void* s_out, void* y, float* mean,

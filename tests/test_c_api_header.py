@@ -55,10 +55,10 @@ def test_ctypes_signatures_match_the_header():
     from distriflow_b200.ops import _lib
     if not _lib.available():
         pytest.skip("native library not built")
-    from distriflow_b200.ops import conv, dense, norm, softmax_ce
+    from distriflow_b200.ops import attention, conv, dense, norm, softmax_ce
     from distriflow_b200.parallel import engine, symm
     L = _lib.lib()
-    for init in (conv._sigs, dense._init_sigs, norm._sigs, softmax_ce._sigs, engine._comm_sigs, symm._sigs):
+    for init in (attention._sigs, conv._sigs, dense._init_sigs, norm._sigs, softmax_ce._sigs, engine._comm_sigs, symm._sigs):
         init()
     decl = _header_params()
     checked = 0
@@ -101,10 +101,10 @@ def test_ctypes_argument_kinds_match_the_header():
     from distriflow_b200.ops import _lib
     if not _lib.available():
         pytest.skip("native library not built")
-    from distriflow_b200.ops import conv, dense, norm, softmax_ce
+    from distriflow_b200.ops import attention, conv, dense, norm, softmax_ce
     from distriflow_b200.parallel import engine, symm
     L = _lib.lib()
-    for init in (conv._sigs, dense._init_sigs, norm._sigs, softmax_ce._sigs, engine._comm_sigs, symm._sigs):
+    for init in (attention._sigs, conv._sigs, dense._init_sigs, norm._sigs, softmax_ce._sigs, engine._comm_sigs, symm._sigs):
         init()
     hdr = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", "distriflow_b200.h")).read(), flags=re.S)
     bad = []
