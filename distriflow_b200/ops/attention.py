@@ -142,7 +142,7 @@ class _FlashAttention(torch.autograd.Function):
         if do.dtype != q.dtype:
             do = do.to(q.dtype)
         dqkv = torch.empty_like(q)
-        scratch = _bwd_scratch(q.device, int(L.dfb_attn_bwd_scratch_bytes(B, T, H, D)))
+        scratch = _bwd_scratch(q.device, (B, T, H, D), int(L.dfb_attn_bwd_scratch_bytes(B, T, H, D)))
         check(L.dfb_attn_bwd(ptr(q), ptr(out), ptr(do), ptr(lse), ptr(dqkv), ptr(scratch), ctypes.c_size_t(scratch.numel()),
                              B, T, H, D, stream()), "dfb_attn_bwd")
         return dqkv, None
@@ -151,13 +151,16 @@ class _FlashAttention(torch.autograd.Function):
 _SCRATCH = {}
 
 
-def _bwd_scratch(device: torch.device, nbytes: int) -> torch.Tensor:
-    """delta + the fp32 dQ accumulator of the backward kernel.  One zero-initialised buffer per device, shared by every
-    layer (the kernel leaves the accumulator at zero again); created during the eager warm-up steps, i.e. before a CUDA
-    graph capture of the step."""
-    key = (device.type, device.index)
+def _bwd_scratch(device: torch.device, shape, nbytes: int) -> torch.Tensor:
+    """delta + the fp32 dQ accumulator of the backward kernel.  One zero-initialised buffer per device AND problem shape,
+    shared by every layer of that shape (the kernel leaves the accumulator part at zero again, but where that part starts
+    depends on the shape, so a buffer is never reused across shapes); created during the eager warm-up steps, i.e. before a
+    CUDA graph capture of the step."""
+    key = (device.type, device.index, tuple(shape))
     buf = _SCRATCH.get(key)
-    if buf is None or buf.numel() < nbytes:
+    if buf is None:
+        if len(_SCRATCH) >= 8:                       # a handful of live shapes at most (training + evaluation)
+            _SCRATCH.pop(next(iter(_SCRATCH)))
         buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
         _SCRATCH[key] = buf
     return buf
