@@ -51,12 +51,79 @@ __device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, in
 // CTA's softmax (MUFU-bound: 128 exp2 per thread and key tile) overlaps the other's MMAs.
 //   warp 0      TMA producer (Q once, then K_j / V_j, single-buffered: K_{j+1} is requested as soon as S_j has been issued)
 //   warp 1      TMEM allocation + MMA issue (one elected lane)
-//   warps 2..5  softmax: thread = query row.  Per key tile: row max over S_j in TMEM, P_j = exp2(S_j*c - m*c) -> bf16 ->
-//               shared memory, then O_j = P_j V_j is read back from TMEM and folded into the fp32 accumulator held in
-//               registers (acc = acc * alpha + O_j), so no rescaling pass over TMEM exists.
+//   warps 2..5  softmax: thread = query row.  Per key tile ONE pass over S_j in TMEM (all 128 scores of the row sit in
+//               registers): row max, P_j = exp2(S_j*c - m*c) -> bf16 -> shared memory.
+// The output accumulator never leaves TMEM: O += P_j V_j accumulates across key tiles, and the reference maximum m of a
+// row is only moved (and O rescaled in place with tcgen05.ld / tcgen05.st) when the new row maximum exceeds it by more
+// than 2^8 in the exponent -- P stays <= 256, exact in bf16's range, and for all but the first tiles no rescale happens.
+// Rows are normalised by the running sum l (kept relative to the same m) once, in the epilogue.
 constexpr int kFwdThreads = 192;
 constexpr int kFwdSmem = 5 * kAttTileBytes + 256 + 1024;      // Q, K, V, P (2 blocks) + barriers + alignment slack
-constexpr uint32_t kFwdTmemCols = 256;                        // S: columns [0,128), O_j: [128,192)
+constexpr uint32_t kFwdTmemCols = 256;                        // S: columns [0,128), O: [128,192)
+constexpr float kRescaleThreshold = 8.0f;                     // log2 domain
+
+template <bool kDiag>
+__device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sP, int row, float c, bool first,
+                                                 float& m_ref, float& l, uint64_t* o_full, uint32_t o_parity) {
+  uint32_t s[128];
+  tmem_ld_32x32(tmem_s_lane, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+  tmem_ld_32x32(tmem_s_lane + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+  tmem_ld_32x32(tmem_s_lane + 64, *reinterpret_cast<uint32_t(*)[32]>(&s[64]));
+  tmem_ld_32x32(tmem_s_lane + 96, *reinterpret_cast<uint32_t(*)[32]>(&s[96]));
+  tmem_ld_wait();
+  if (kDiag) {                                                 // diagonal tile: key index > query index is masked
+#pragma unroll
+    for (int i = 0; i < 128; ++i)
+      if (i > row) s[i] = 0xff800000u;                         // -inf
+  }
+  float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < 128; i += 8) {
+    mx0 = fmaxf(mx0, fmaxf(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])));
+    mx1 = fmaxf(mx1, fmaxf(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])));
+    mx2 = fmaxf(mx2, fmaxf(__uint_as_float(s[i + 4]), __uint_as_float(s[i + 5])));
+    mx3 = fmaxf(mx3, fmaxf(__uint_as_float(s[i + 6]), __uint_as_float(s[i + 7])));
+  }
+  const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+  if (first) {
+    m_ref = mx;                                                // O is overwritten by the first P V (accumulate = 0)
+  } else {
+    const bool need = (mx - m_ref) * c > kRescaleThreshold;
+    if (__any_sync(0xffffffffu, need)) {                       // rare: move the reference maximum, rescale O and l
+      const float m_new = fmaxf(m_ref, mx);
+      const float alpha = exp2f((m_ref - m_new) * c);
+      mbar_wait(o_full, o_parity);                             // P_{j-1} V_{j-1} has landed (it has: S_j was issued after it)
+      tc_fence_after();
+#pragma unroll 1
+      for (int cc = 0; cc < kAttD; cc += 8) {                  // 8 columns at a time: the score tile stays in registers
+        uint32_t r[8];
+        tmem_ld_32x8(tmem_o_lane + cc, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+        tmem_st_32x8(tmem_o_lane + cc, r);
+      }
+      tmem_st_wait();
+      l *= alpha;
+      m_ref = m_new;
+    }
+  }
+  const float mc = m_ref * c;
+  float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+#pragma unroll
+  for (int q8 = 0; q8 < 16; ++q8) {
+    float e[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * q8 + i]), c, -mc));
+    sum0 += e[0] + e[1];
+    sum1 += e[2] + e[3];
+    sum2 += e[4] + e[5];
+    sum3 += e[6] + e[7];
+    uint4 pk = {pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7])};
+    st_swizzled_row_piece(sP + (q8 >> 3) * kAttTileBytes, row, q8 & 7, pk);
+  }
+  l += (sum0 + sum1) + (sum2 + sum3);
+}
 
 __global__ void __launch_bounds__(kFwdThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, const AttnFwdParams p) {
@@ -75,7 +142,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint64_t* s_full = bars + 5;
   uint64_t* p_ready = bars + 6;
   uint64_t* o_full = bars + 7;
-  uint64_t* o_empty = bars + 8;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp_idx = threadIdx.x >> 5;
@@ -100,7 +166,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(s_full, 1);
     mbar_init(p_ready, 4);      // one arrive per softmax warp
     mbar_init(o_full, 1);
-    mbar_init(o_empty, 4);
     fence_mbar_init();
   }
   if (warp_idx == 1) tmem_alloc<kFwdTmemCols>(tmem_ptr);
@@ -118,10 +183,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       tma_load_4d(sQ, &tmQKV, q_full, 0, q0, h, b);
       for (int j = 0; j < n_kv; ++j) {
         const uint32_t ph = j & 1;
-        mbar_wait(k_empty, ph ^ 1);
+        mbar_wait_backoff(k_empty, ph ^ 1, 128);
         mbar_expect_tx(k_full, kAttTileBytes);
         tma_load_4d(sK, &tmQKV, k_full, 0, j * kAttTile, p.H + h, b);
-        mbar_wait(v_empty, ph ^ 1);
+        mbar_wait_backoff(v_empty, ph ^ 1, 128);
         mbar_expect_tx(v_full, kAttTileBytes);
         tma_load_4d(sV, &tmQKV, v_full, 0, j * kAttTile, 2 * p.H + h, b);
       }
@@ -146,15 +211,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(k_empty);
         umma_commit(s_full);
-        // O_j = P_j V_j once the softmax warps have written P_j and have taken O_{j-1} out of TMEM
-        mbar_wait(p_ready, ph);
+        // O += P_j V_j once the softmax warps have written P_j (and, rarely, rescaled O)
+        mbar_wait_backoff(p_ready, ph, 32);
         mbar_wait(v_full, ph);
-        if (j > 0) mbar_wait(o_empty, ph ^ 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const uint64_t a = (k < 4 ? dp0 : dp1) + (uint64_t)((k & 3) * 2);       // 32 bytes per 16-wide k step inside a block
-          umma_f16(tmem_o, a, dv + (uint64_t)(k * 128), idesc_o, k > 0 ? 1u : 0u);   // 16 kv rows x 128 B per k step
+          umma_f16(tmem_o, a, dv + (uint64_t)(k * 128), idesc_o, (j > 0 || k > 0) ? 1u : 0u);   // 16 kv rows x 128 B per k step
         }
         umma_commit(v_empty);
         umma_commit(o_full);
@@ -166,86 +230,38 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const float c = p.scale_log2;
-    float m_prev = -INFINITY, l = 0.f;
-    float acc[kAttD];
-#pragma unroll
-    for (int i = 0; i < kAttD; ++i) acc[i] = 0.f;
+    float m_ref = -INFINITY, l = 0.f;
 
     for (int j = 0; j < n_kv; ++j) {
       const uint32_t ph = j & 1;
-      const bool diag = (j == n_kv - 1);
-      mbar_wait(s_full, ph);
+      mbar_wait(s_full, ph);       // S_j is complete, and so is every MMA issued before it: P_{j-1} V_{j-1} has read sP
       tc_fence_after();
-      // pass 1: row maximum
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_s + lane_sel + ch * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(r[i]);
-          if (diag && ch * 32 + i > row) v = -INFINITY;
-          mx = fmaxf(mx, v);
-        }
-      }
-      const float m_new = fmaxf(m_prev, mx);
-      const float mc = m_new * c;
-      // pass 2: P = exp2(S*c - m*c), row sum, bf16 into the swizzled P tile
-      float sum = 0.f;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_s + lane_sel + ch * 32, r);
-        tmem_ld_wait();
-        float e[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(r[i]);
-          if (diag && ch * 32 + i > row) v = -INFINITY;
-          e[i] = exp2f(fmaf(v, c, -mc));
-          sum += e[i];
-        }
-        uint8_t* blk = sP + (ch >> 1) * kAttTileBytes;
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 pk = {pack_bf16(e[8 * q4 + 0], e[8 * q4 + 1]), pack_bf16(e[8 * q4 + 2], e[8 * q4 + 3]),
-                      pack_bf16(e[8 * q4 + 4], e[8 * q4 + 5]), pack_bf16(e[8 * q4 + 6], e[8 * q4 + 7])};
-          st_swizzled_row_piece(blk, row, (ch & 1) * 4 + q4, pk);
-        }
-      }
-      tc_fence_before();            // our TMEM reads of S_j are done before the MMA thread may overwrite S
+      if (j == n_kv - 1) fwd_softmax_tile<true>(tmem_s + lane_sel, tmem_o + lane_sel, sP, row, c, j == 0, m_ref, l, o_full, ph ^ 1);
+      else fwd_softmax_tile<false>(tmem_s + lane_sel, tmem_o + lane_sel, sP, row, c, j == 0, m_ref, l, o_full, ph ^ 1);
+      tc_fence_before();            // our TMEM reads of S_j (and rescale stores to O) are ordered before the MMA thread's next issue
       fence_proxy_async_smem();     // P_j (generic-proxy stores) visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) mbar_arrive(p_ready);
-      const float alpha = exp2f((m_prev - m_new) * c);        // first tile: exp2(-inf) = 0
-      l = l * alpha + sum;
-      m_prev = m_new;
-      // fold O_j into the accumulator
-      mbar_wait(o_full, ph);
-      tc_fence_after();
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_o + lane_sel + hh * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[hh * 32 + i] = fmaf(acc[hh * 32 + i], alpha, __uint_as_float(r[i]));
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(o_empty);
     }
 
-    // epilogue: O = acc / l -> bf16 -> swizzled staging (the P buffer: every MMA that read it has completed) -> TMA store
+    // epilogue: O / l -> bf16 -> swizzled staging (the P buffer: every MMA that read it has completed) -> TMA store
+    mbar_wait(o_full, (n_kv - 1) & 1);
+    tc_fence_after();
     const float inv_l = 1.f / l;
-    if (q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m_prev * c + log2f(l)) * kLn2;
+    if (q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m_ref * c + log2f(l)) * kLn2;
 #pragma unroll
-    for (int q8 = 0; q8 < 8; ++q8) {
-      uint4 pk = {pack_bf16(acc[8 * q8 + 0] * inv_l, acc[8 * q8 + 1] * inv_l), pack_bf16(acc[8 * q8 + 2] * inv_l, acc[8 * q8 + 3] * inv_l),
-                  pack_bf16(acc[8 * q8 + 4] * inv_l, acc[8 * q8 + 5] * inv_l), pack_bf16(acc[8 * q8 + 6] * inv_l, acc[8 * q8 + 7] * inv_l)};
-      st_swizzled_row_piece(sP, row, q8, pk);
+    for (int hh = 0; hh < 2; ++hh) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_o + lane_sel + hh * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        uint4 pk = {pack_bf16(__uint_as_float(r[8 * q4 + 0]) * inv_l, __uint_as_float(r[8 * q4 + 1]) * inv_l),
+                    pack_bf16(__uint_as_float(r[8 * q4 + 2]) * inv_l, __uint_as_float(r[8 * q4 + 3]) * inv_l),
+                    pack_bf16(__uint_as_float(r[8 * q4 + 4]) * inv_l, __uint_as_float(r[8 * q4 + 5]) * inv_l),
+                    pack_bf16(__uint_as_float(r[8 * q4 + 6]) * inv_l, __uint_as_float(r[8 * q4 + 7]) * inv_l)};
+        st_swizzled_row_piece(sP, row, hh * 4 + q4, pk);
+      }
     }
     fence_proxy_async_smem();
     named_bar_sync(1, 128);
@@ -263,7 +279,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     tmem_dealloc<kFwdTmemCols>(tmem_base);
   }
 }
-
 
 // ============================================================================================== backward
 // delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (the row term of the softmax Jacobian), eight threads per row.
@@ -326,6 +341,36 @@ struct AttnBwdParams {
   float scale;           // 1 / sqrt(D)
   float scale_log2;      // scale * log2(e)
 };
+
+// P and dS for one query row and one half (64 key columns) of the tile: P = exp2(S*c - lse*log2e), dS = P (dP - delta) / sqrt(D).
+template <bool kDiag>
+__device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t tmem_dp_lane, uint8_t* pblk, uint8_t* dsblk, int row,
+                                                 int half, float lse2, float dl, float scale, float scale_log2) {
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    const int col0 = half * 64 + ch * 32;
+    uint32_t rs[32], rp[32];
+    tmem_ld_32x32(tmem_s_lane + col0, rs);
+    tmem_ld_32x32(tmem_dp_lane + col0, rp);
+    tmem_ld_wait();
+#pragma unroll
+    for (int q4 = 0; q4 < 4; ++q4) {
+      float pv[8], dv[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int i = 8 * q4 + e;
+        float pe = exp2f(fmaf(__uint_as_float(rs[i]), scale_log2, -lse2));
+        if (kDiag && col0 + i > row) pe = 0.f;
+        pv[e] = pe;
+        dv[e] = pe * (__uint_as_float(rp[i]) - dl) * scale;
+      }
+      uint4 pk = {pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7])};
+      uint4 dk = {pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7])};
+      st_swizzled_row_piece(pblk, row, ch * 4 + q4, pk);
+      st_swizzled_row_piece(dsblk, row, ch * 4 + q4, dk);
+    }
+  }
+}
 
 // One CTA per (128 key rows, head, batch), one CTA per SM.  K_j and V_j stay in shared memory; the CTA walks the query
 // tiles i = j .. n-1 (causal) and per tile issues five products:
@@ -411,7 +456,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       for (int it = 0; it < n_it; ++it) {
         const int st = it & 1;
         const uint32_t ph = (it >> 1) & 1;
-        mbar_wait(&qdo_empty[st], ph ^ 1);
+        mbar_wait_backoff(&qdo_empty[st], ph ^ 1, 128);
         mbar_expect_tx(&qdo_full[st], kBwdStageBytes);
         const int q0 = (jt + it) * kAttTile;
         tma_load_4d(sQdO + st * kBwdStageBytes, &tmQKV, &qdo_full[st], 0, q0, h, b);
@@ -447,7 +492,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_dp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(sdp_full);
-        mbar_wait(pds_ready, ph);
+        mbar_wait_backoff(pds_ready, ph, 32);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < 8; ++k)         // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
@@ -487,30 +532,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       tc_fence_after();
       uint8_t* pblk = sP + half * kAttTileBytes;
       uint8_t* dsblk = sdS + half * kAttTileBytes;
-#pragma unroll 1
-      for (int ch = 0; ch < 2; ++ch) {
-        const int col0 = half * 64 + ch * 32;
-        uint32_t rs[32], rp[32];
-        tmem_ld_32x32(tmem_s + lane_sel + col0, rs);
-        tmem_ld_32x32(tmem_dp + lane_sel + col0, rp);
-        tmem_ld_wait();
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          float pv[8], dv[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int i = 8 * q4 + e;
-            float pe = exp2f(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
-            if (diag && col0 + i > row) pe = 0.f;
-            pv[e] = pe;
-            dv[e] = pe * (__uint_as_float(rp[i]) - dl) * p.scale;
-          }
-          uint4 pk = {pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7])};
-          uint4 dk = {pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7])};
-          st_swizzled_row_piece(pblk, row, ch * 4 + q4, pk);
-          st_swizzled_row_piece(dsblk, row, ch * 4 + q4, dk);
-        }
-      }
+      if (diag) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2);
+      else bwd_softmax_half<false>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2);
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
