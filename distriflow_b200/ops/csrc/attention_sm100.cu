@@ -47,38 +47,46 @@ __device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, in
 }
 
 // ============================================================================================== forward
-// One CTA per (128 query rows, head, batch); two CTAs share an SM (80 KiB of shared memory, 256 TMEM columns each), so one
-// CTA's softmax (MUFU-bound: 128 exp2 per thread and key tile) overlaps the other's MMAs.
-//   warp 0      TMA producer (Q once, then K_j / V_j, single-buffered: K_{j+1} is requested as soon as S_j has been issued)
-//   warp 1      TMEM allocation + MMA issue (one elected lane)
-//   warps 2..5  softmax: thread = query row.  Per key tile ONE pass over S_j in TMEM (all 128 scores of the row sit in
-//               registers): row max, P_j = exp2(S_j*c - m*c) -> bf16 -> shared memory.
-// The output accumulator never leaves TMEM: O += P_j V_j accumulates across key tiles, and the reference maximum m of a
-// row is only moved (and O rescaled in place with tcgen05.ld / tcgen05.st) when the new row maximum exceeds it by more
-// than 2^8 in the exponent -- P stays <= 256, exact in bf16's range, and for all but the first tiles no rescale happens.
-// Rows are normalised by the running sum l (kept relative to the same m) once, in the epilogue.
-constexpr int kFwdThreads = 192;
-constexpr int kFwdSmem = 5 * kAttTileBytes + 256 + 1024;      // Q, K, V, P (2 blocks) + barriers + alignment slack
-constexpr uint32_t kFwdTmemCols = 256;                        // S: columns [0,128), O: [128,192)
+// One CTA per (128 query rows, head, batch); two CTAs share an SM (80 KiB of shared memory, 256 TMEM columns each).
+// Keys are walked in tiles of 64 so that everything between the tensor core and the softmax warps is double-buffered:
+//   TMEM   S slot 0 / 1 (64 columns each), O (64 columns, accumulated over all key tiles)
+//   smem   Q (16 KiB), K slot 0/1 and V slot 0/1 (8 KiB each), P slot 0/1 (16 KiB each)
+// Even key tiles belong to softmax warp set A (warps 2..5), odd ones to set B (warps 6..9): each set owns one S slot, one P
+// slot and its OWN output accumulator with its own running (m, l) per row, so the two sets never synchronise with each
+// other until the epilogue, where the two partial results are merged like two splits of a split-KV attention.  That puts
+// four softmax warps on every SM sub-partition (two CTAs per SM): the exp2 / FFMA streams of one warp hide the fixed
+// latencies of the others (with one warp set the kernel sat at 44 % issue and 46 % MUFU utilisation, ncu r2 v3).
+//   warp 0      TMA producer (Q once, then K_j / V_j into the 2-slot rings)
+//   warp 1      TMEM allocation + MMA issue (one elected lane): S_0, S_1, PV_0, S_2, PV_1, ...
+//   warps 2..9  softmax: thread = query row; the 64 scores of the row sit in registers (one TMEM pass): row max,
+//               P_j = exp2(S_j*c - m*c) -> bf16 -> shared memory.
+// An output accumulator never leaves TMEM: the reference maximum m of a row is only moved (and O rescaled in place with
+// tcgen05.ld / tcgen05.st) when the new row maximum exceeds it by more than 2^8 in the exponent -- P stays <= 256, and for
+// all but the first tiles no rescale happens.  Rows are normalised by the merged running sum once, in the epilogue.
+constexpr int kFwdThreads = 320;
+constexpr int kKvTile = 64;                                   // key rows per forward step
+constexpr int kKvTileBytes = kKvTile * kAttD * 2;             // 8 KiB
+constexpr int kFwdSmem = 5 * kAttTileBytes + 256 + 2048 + 1024;   // Q 16 + K 2x8 + V 2x8 + P 2x16 KiB + barriers + (m,l) exchange + slack
+constexpr uint32_t kFwdTmemCols = 256;                        // S slots: columns [0,64) [64,128), O_A: [128,192), O_B: [192,256)
 constexpr float kRescaleThreshold = 8.0f;                     // log2 domain
 
-template <bool kDiag>
-__device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sP, int row, float c, bool first,
-                                                 float& m_ref, float& l, uint64_t* o_full, uint32_t o_parity) {
-  uint32_t s[128];
+// `mask_from`: first key column (tile-relative) that is masked for query row 0 of the CTA, i.e. column i is masked for
+// `row` when i - mask_from > row - 0  <=>  i + kv0 > row + q0.  kMask = false: nothing is masked (tiles left of the diagonal).
+template <bool kMask>
+__device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sPslot, int row, int col_shift,
+                                                 float c, bool first, float& m_ref, float& l) {
+  uint32_t s[kKvTile];
   tmem_ld_32x32(tmem_s_lane, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
   tmem_ld_32x32(tmem_s_lane + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
-  tmem_ld_32x32(tmem_s_lane + 64, *reinterpret_cast<uint32_t(*)[32]>(&s[64]));
-  tmem_ld_32x32(tmem_s_lane + 96, *reinterpret_cast<uint32_t(*)[32]>(&s[96]));
   tmem_ld_wait();
-  if (kDiag) {                                                 // diagonal tile: key index > query index is masked
+  if (kMask) {                                                 // key index > query index is masked
 #pragma unroll
-    for (int i = 0; i < 128; ++i)
-      if (i > row) s[i] = 0xff800000u;                         // -inf
+    for (int i = 0; i < kKvTile; ++i)
+      if (i + col_shift > row) s[i] = 0xff800000u;             // -inf
   }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-  for (int i = 0; i < 128; i += 8) {
+  for (int i = 0; i < kKvTile; i += 8) {
     mx0 = fmaxf(mx0, fmaxf(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])));
     mx1 = fmaxf(mx1, fmaxf(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])));
     mx2 = fmaxf(mx2, fmaxf(__uint_as_float(s[i + 4]), __uint_as_float(s[i + 5])));
@@ -88,12 +96,11 @@ __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t 
   if (first) {
     m_ref = mx;                                                // O is overwritten by the first P V (accumulate = 0)
   } else {
-    const bool need = (mx - m_ref) * c > kRescaleThreshold;
+    const bool need = (mx - m_ref) * c > kRescaleThreshold;    // false for a fully masked row (mx = -inf)
     if (__any_sync(0xffffffffu, need)) {                       // rare: move the reference maximum, rescale O and l
       const float m_new = fmaxf(m_ref, mx);
       const float alpha = exp2f((m_ref - m_new) * c);
-      mbar_wait(o_full, o_parity);                             // P_{j-1} V_{j-1} has landed (it has: S_j was issued after it)
-      tc_fence_after();
+      // this set's previous P V has landed (the caller waited for pv_done) and the next is not issued before our p_ready
 #pragma unroll 1
       for (int cc = 0; cc < kAttD; cc += 8) {                  // 8 columns at a time: the score tile stays in registers
         uint32_t r[8];
@@ -108,10 +115,10 @@ __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t 
       m_ref = m_new;
     }
   }
-  const float mc = m_ref * c;
+  const float mc = (m_ref == -INFINITY) ? 0.f : m_ref * c;     // a fully masked row so far: every P is exp2(-inf) = 0
   float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
-  for (int q8 = 0; q8 < 16; ++q8) {
+  for (int q8 = 0; q8 < kKvTile / 8; ++q8) {
     float e[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * q8 + i]), c, -mc));
@@ -120,29 +127,31 @@ __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t 
     sum2 += e[4] + e[5];
     sum3 += e[6] + e[7];
     uint4 pk = {pack_bf16(e[0], e[1]), pack_bf16(e[2], e[3]), pack_bf16(e[4], e[5]), pack_bf16(e[6], e[7])};
-    st_swizzled_row_piece(sP + (q8 >> 3) * kAttTileBytes, row, q8 & 7, pk);
+    st_swizzled_row_piece(sPslot, row, q8, pk);
   }
   l += (sum0 + sum1) + (sum2 + sum3);
 }
 
 __global__ void __launch_bounds__(kFwdThreads, 2)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO, const AttnFwdParams p) {
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                const __grid_constant__ CUtensorMap tmO, const AttnFwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = smem + kAttTileBytes;
-  uint8_t* sV = smem + 2 * kAttTileBytes;
-  uint8_t* sP = smem + 3 * kAttTileBytes;                     // 32 KiB: kv columns [0,64) then [64,128)
+  uint8_t* sK = smem + kAttTileBytes;                         // 2 slots x 8 KiB
+  uint8_t* sV = smem + 2 * kAttTileBytes;                     // 2 slots x 8 KiB
+  uint8_t* sP = smem + 3 * kAttTileBytes;                     // 2 slots x 16 KiB
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * kAttTileBytes);
   uint64_t* q_full = bars + 0;
-  uint64_t* k_full = bars + 1;
-  uint64_t* k_empty = bars + 2;
-  uint64_t* v_full = bars + 3;
-  uint64_t* v_empty = bars + 4;
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_ready = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* k_full = bars + 1;      // [2]
+  uint64_t* k_empty = bars + 3;     // [2]
+  uint64_t* v_full = bars + 5;      // [2]
+  uint64_t* v_empty = bars + 7;     // [2]
+  uint64_t* s_full = bars + 9;      // [2]
+  uint64_t* p_ready = bars + 11;    // [2]
+  uint64_t* pv_done = bars + 13;    // [2]  P_j V_j complete: P slot free, O readable
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
+  float2* ml_xchg = reinterpret_cast<float2*>(smem + 5 * kAttTileBytes + 256);      // [2 sets][128 rows] (m, l)
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -153,19 +162,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   const int bh = (int)(blockIdx.x % bh_total);
   const int b = bh / p.H, h = bh % p.H;
   const int q0 = qt * kAttTile;
-  const int n_kv = qt + 1;                                     // key tiles 0..qt; tile qt is the diagonal one
+  const int n_kv = 2 * (qt + 1);                               // 64-row key tiles 0 .. 2qt+1; the last two straddle the diagonal
 
   if (warp_idx == 0 && lane == 0) {
-    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
     tma_prefetch_desc(&tmO);
     mbar_init(q_full, 1);
-    mbar_init(k_full, 1);
-    mbar_init(k_empty, 1);
-    mbar_init(v_full, 1);
-    mbar_init(v_empty, 1);
-    mbar_init(s_full, 1);
-    mbar_init(p_ready, 4);      // one arrive per softmax warp
-    mbar_init(o_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_ready[i], 4);      // one arrive per softmax warp of the set that owns slot i
+      mbar_init(&pv_done[i], 1);
+    }
     fence_mbar_init();
   }
   if (warp_idx == 1) tmem_alloc<kFwdTmemCols>(tmem_ptr);
@@ -173,98 +185,120 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tmem_s = tmem_base;
-  const uint32_t tmem_o = tmem_base + 128;
+  const uint32_t tmem_s = tmem_base;                           // + 64 * slot
+  const uint32_t tmem_o = tmem_base + 128;                     // + 64 * set
 
   if (warp_idx == 0) {
     // ===================================================================== TMA producer
     if (elect_one()) {
       mbar_expect_tx(q_full, kAttTileBytes);
-      tma_load_4d(sQ, &tmQKV, q_full, 0, q0, h, b);
+      tma_load_4d(sQ, &tmQ, q_full, 0, q0, h, b);
       for (int j = 0; j < n_kv; ++j) {
-        const uint32_t ph = j & 1;
-        mbar_wait_backoff(k_empty, ph ^ 1, 128);
-        mbar_expect_tx(k_full, kAttTileBytes);
-        tma_load_4d(sK, &tmQKV, k_full, 0, j * kAttTile, p.H + h, b);
-        mbar_wait_backoff(v_empty, ph ^ 1, 128);
-        mbar_expect_tx(v_full, kAttTileBytes);
-        tma_load_4d(sV, &tmQKV, v_full, 0, j * kAttTile, 2 * p.H + h, b);
+        const int slot = j & 1;
+        const uint32_t par = (j >> 1) & 1;
+        mbar_wait_backoff(&k_empty[slot], par ^ 1, 128);
+        mbar_expect_tx(&k_full[slot], kKvTileBytes);
+        tma_load_4d(sK + slot * kKvTileBytes, &tmKV, &k_full[slot], 0, j * kKvTile, p.H + h, b);
+        mbar_wait_backoff(&v_empty[slot], par ^ 1, 128);
+        mbar_expect_tx(&v_full[slot], kKvTileBytes);
+        tma_load_4d(sV + slot * kKvTileBytes, &tmKV, &v_full[slot], 0, j * kKvTile, 2 * p.H + h, b);
       }
     }
   } else if (warp_idx == 1) {
     // ===================================================================== MMA issuer
     if (elect_one()) {
-      const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);     // S[128 q x 128 kv]  = Q (K-major) x K (K-major)
-      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);      // O[128 q x 64 d]    = P (K-major) x V (MN-major)
+      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);      // S[128 q x 64 kv]  = Q (K-major) x K (K-major)
+      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);      // O[128 q x 64 d]   = P (K-major) x V (MN-major)
       const uint64_t dq = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
-      const uint64_t dk = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
-      const uint64_t dv = make_smem_desc_sw128(smem_u32(sV), kAttTileBytes, 1024);
-      const uint64_t dp0 = make_smem_desc_sw128(smem_u32(sP), 0, 1024);
-      const uint64_t dp1 = make_smem_desc_sw128(smem_u32(sP + kAttTileBytes), 0, 1024);
+      auto issue_s = [&](int j) {
+        const int slot = j & 1;
+        mbar_wait(&k_full[slot], (j >> 1) & 1);
+        tc_fence_after();
+        const uint64_t dk = make_smem_desc_sw128(smem_u32(sK + slot * kKvTileBytes), 0, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_f16(tmem_s + slot * kKvTile, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&k_empty[slot]);
+        umma_commit(&s_full[slot]);
+      };
       mbar_wait(q_full, 0);
+      issue_s(0);
       for (int j = 0; j < n_kv; ++j) {
-        const uint32_t ph = j & 1;
-        // S_j: the S columns are free (the softmax warps signalled p_ready(j-1) after their last read of S_{j-1})
-        mbar_wait(k_full, ph);
+        const int slot = j & 1;
+        const uint32_t par = (j >> 1) & 1;
+        // S runs one tile ahead of P V: slot (j+1)&1 was released by p_ready(j-1), waited for in the previous iteration
+        if (j + 1 < n_kv) issue_s(j + 1);
+        mbar_wait_backoff(&p_ready[slot], par, 32);
+        mbar_wait(&v_full[slot], par);
         tc_fence_after();
+        const uint64_t dp = make_smem_desc_sw128(smem_u32(sP + slot * kAttTileBytes), 0, 1024);
+        const uint64_t dv = make_smem_desc_sw128(smem_u32(sV + slot * kKvTileBytes), kKvTileBytes, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(k_empty);
-        umma_commit(s_full);
-        // O += P_j V_j once the softmax warps have written P_j (and, rarely, rescaled O)
-        mbar_wait_backoff(p_ready, ph, 32);
-        mbar_wait(v_full, ph);
-        tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint64_t a = (k < 4 ? dp0 : dp1) + (uint64_t)((k & 3) * 2);       // 32 bytes per 16-wide k step inside a block
-          umma_f16(tmem_o, a, dv + (uint64_t)(k * 128), idesc_o, (j > 0 || k > 0) ? 1u : 0u);   // 16 kv rows x 128 B per k step
-        }
-        umma_commit(v_empty);
-        umma_commit(o_full);
+        for (int k = 0; k < 4; ++k)      // A: 32 bytes per 16-wide k step; B: 16 key rows x 128 B per k step
+          umma_f16(tmem_o + slot * kAttD, dp + (uint64_t)(k * 2), dv + (uint64_t)(k * 128), idesc_o, (j > 1 || k > 0) ? 1u : 0u);
+        umma_commit(&v_empty[slot]);
+        umma_commit(&pv_done[slot]);
       }
     }
   } else {
-    // ===================================================================== softmax warps (2..5), thread = query row
+    // ===================================================================== softmax warps 2..9: set A = even key tiles, set B = odd
     const int quarter = warp_idx & 3;
+    const int set = (warp_idx - 2) >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const float c = p.scale_log2;
     float m_ref = -INFINITY, l = 0.f;
+    uint8_t* sPslot = sP + set * kAttTileBytes;
+    const uint32_t my_s = tmem_s + lane_sel + set * kKvTile;
+    const uint32_t my_o = tmem_o + lane_sel + set * kAttD;
+    const int n_t = n_kv >> 1;                                 // tiles of this set: j = 2t + set
 
-    for (int j = 0; j < n_kv; ++j) {
-      const uint32_t ph = j & 1;
-      mbar_wait(s_full, ph);       // S_j is complete, and so is every MMA issued before it: P_{j-1} V_{j-1} has read sP
+    for (int t = 0; t < n_t; ++t) {
+      const uint32_t par = t & 1;
+      mbar_wait(&s_full[set], par);
+      if (t >= 1) mbar_wait(&pv_done[set], par ^ 1);           // this set's previous P V is complete: P slot free, O_set at rest
       tc_fence_after();
-      if (j == n_kv - 1) fwd_softmax_tile<true>(tmem_s + lane_sel, tmem_o + lane_sel, sP, row, c, j == 0, m_ref, l, o_full, ph ^ 1);
-      else fwd_softmax_tile<false>(tmem_s + lane_sel, tmem_o + lane_sel, sP, row, c, j == 0, m_ref, l, o_full, ph ^ 1);
+      if (t == n_t - 1) fwd_softmax_tile<true>(my_s, my_o, sPslot, row, set * kKvTile, c, t == 0, m_ref, l);
+      else fwd_softmax_tile<false>(my_s, my_o, sPslot, row, 0, c, t == 0, m_ref, l);
       tc_fence_before();            // our TMEM reads of S_j (and rescale stores to O) are ordered before the MMA thread's next issue
       fence_proxy_async_smem();     // P_j (generic-proxy stores) visible to the tensor core (async proxy)
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_ready);
+      if (lane == 0) mbar_arrive(&p_ready[set]);
     }
 
-    // epilogue: O / l -> bf16 -> swizzled staging (the P buffer: every MMA that read it has completed) -> TMA store
-    mbar_wait(o_full, (n_kv - 1) & 1);
+    // epilogue: merge the two sets' partial results.  O = (O_A wA + O_B wB) / (l_A wA + l_B wB), w = 2^((m_set - m) c).
+    ml_xchg[set * kAttTile + row] = make_float2(m_ref, l);
+    mbar_wait(&pv_done[set], (n_t - 1) & 1);                   // this set's last P V is complete (a set only ever waits on its
+    tc_fence_after();                                          // own barrier: it is never more than one phase behind it)
+    tc_fence_before();
+    named_bar_sync(1, 256);                                    // ... and after this, so is the other set's
     tc_fence_after();
-    const float inv_l = 1.f / l;
-    if (q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m_ref * c + log2f(l)) * kLn2;
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_o + lane_sel + hh * 32, r);
+    const float2 other = ml_xchg[(set ^ 1) * kAttTile + row];
+    const float m_a = set == 0 ? m_ref : other.x, l_a = set == 0 ? l : other.y;
+    const float m_b = set == 0 ? other.x : m_ref, l_b = set == 0 ? other.y : l;
+    const float m = fmaxf(m_a, m_b);                           // finite: set A's first tile has an unmasked key for every row
+    const float w_a = exp2f((m_a - m) * c), w_b = exp2f((m_b - m) * c);      // exp2(-inf) = 0 for a set that saw only masked keys
+    const float l_tot = l_a * w_a + l_b * w_b;
+    const float inv_l = 1.f / l_tot;
+    if (set == 0 && q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m * c + log2f(l_tot)) * kLn2;
+    {
+      // this set merges output columns [32 set, 32 set + 32)
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32(tmem_o + lane_sel + set * 32, ra);
+      tmem_ld_32x32(tmem_o + lane_sel + kAttD + set * 32, rb);
       tmem_ld_wait();
+      const float fa = w_a * inv_l, fb = w_b * inv_l;
 #pragma unroll
       for (int q4 = 0; q4 < 4; ++q4) {
-        uint4 pk = {pack_bf16(__uint_as_float(r[8 * q4 + 0]) * inv_l, __uint_as_float(r[8 * q4 + 1]) * inv_l),
-                    pack_bf16(__uint_as_float(r[8 * q4 + 2]) * inv_l, __uint_as_float(r[8 * q4 + 3]) * inv_l),
-                    pack_bf16(__uint_as_float(r[8 * q4 + 4]) * inv_l, __uint_as_float(r[8 * q4 + 5]) * inv_l),
-                    pack_bf16(__uint_as_float(r[8 * q4 + 6]) * inv_l, __uint_as_float(r[8 * q4 + 7]) * inv_l)};
-        st_swizzled_row_piece(sP, row, hh * 4 + q4, pk);
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(ra[8 * q4 + i]) * fa + __uint_as_float(rb[8 * q4 + i]) * fb;
+        uint4 pk = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7])};
+        st_swizzled_row_piece(sP, row, set * 4 + q4, pk);        // staging = P slot 0: every MMA that read it has completed
       }
     }
     fence_proxy_async_smem();
-    named_bar_sync(1, 128);
+    named_bar_sync(1, 256);
     if (threadIdx.x == 64) {
       tma_store_4d(&tmO, sP, 0, q0, h, b);
       tma_store_commit();
@@ -606,12 +640,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
 }
 
 // ---------------------------------------------------------------------------------------------- host side
-static int make_packed_map(CUtensorMap* tm, const void* base, int B, int T, int H, int which_count) {
+static int make_packed_map(CUtensorMap* tm, const void* base, int B, int T, int H, int which_count, int box_rows = kAttTile) {
   // [B, T, which_count, H, 64] bf16 seen as {d, t, which*H + h, b}
   const uint64_t row = (uint64_t)which_count * H * kAttD * 2;
   uint64_t dims[4] = {(uint64_t)kAttD, (uint64_t)T, (uint64_t)which_count * H, (uint64_t)B};
   uint64_t str[3] = {row, (uint64_t)kAttD * 2, (uint64_t)T * row};
-  uint32_t box[4] = {(uint32_t)kAttD, (uint32_t)kAttTile, 1, 1};
+  uint32_t box[4] = {(uint32_t)kAttD, (uint32_t)box_rows, 1, 1};
   return encode_tmap(tm, base, 0, 4, dims, str, box, nullptr, 1);
 }
 
@@ -627,8 +661,9 @@ DFB_API int dfb_attn_supported(int B, int T, int H, int D) {
 DFB_API int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, cudaStream_t stream) {
   DFB_REQUIRE(dfb_attn_supported(B, T, H, D), "attn_fwd: head dimension %d not supported (64 only)", D);
   DFB_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attn_fwd: operands must be 16-byte aligned");
-  CUtensorMap tmQKV, tmO;
-  if (make_packed_map(&tmQKV, qkv, B, T, H, 3)) return 4;
+  CUtensorMap tmQ, tmKV, tmO;
+  if (make_packed_map(&tmQ, qkv, B, T, H, 3)) return 4;
+  if (make_packed_map(&tmKV, qkv, B, T, H, 3, kKvTile)) return 4;
   if (make_packed_map(&tmO, out, B, T, H, 1)) return 4;
   AttnFwdParams p;
   p.lse = lse; p.B = B; p.T = T; p.H = H;
@@ -642,7 +677,7 @@ DFB_API int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, i
     attr_done[dev & 63] = true;
   }
   const long grid = (long)p.n_qt * B * H;
-  attn_fwd_kernel<<<(unsigned)grid, kFwdThreads, kFwdSmem, stream>>>(tmQKV, tmO, p);
+  attn_fwd_kernel<<<(unsigned)grid, kFwdThreads, kFwdSmem, stream>>>(tmQ, tmKV, tmO, p);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
