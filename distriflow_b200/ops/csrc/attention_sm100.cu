@@ -47,7 +47,7 @@ __device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, in
 }
 
 // ============================================================================================== forward
-// One CTA per (128 query rows, head, batch); two CTAs share an SM (80 KiB of shared memory, 256 TMEM columns each).
+// Work item = (128 query rows, head, batch); two persistent CTAs share an SM (99 KiB of shared memory, 256 TMEM columns each).
 // Keys are walked in tiles of 64 so that everything between the tensor core and the softmax warps is double-buffered:
 //   TMEM   S slot 0 / 1 (64 columns each), O (64 columns, accumulated over all key tiles)
 //   smem   Q (16 KiB), K slot 0/1 and V slot 0/1 (8 KiB each), P slot 0/1 (16 KiB each)
@@ -66,7 +66,7 @@ __device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, in
 constexpr int kFwdThreads = 320;
 constexpr int kKvTile = 64;                                   // key rows per forward step
 constexpr int kKvTileBytes = kKvTile * kAttD * 2;             // 8 KiB
-constexpr int kFwdSmem = 5 * kAttTileBytes + 256 + 2048 + 1024;   // Q 16 + K 2x8 + V 2x8 + P 2x16 KiB + barriers + (m,l) exchange + slack
+constexpr int kFwdSmem = 6 * kAttTileBytes + 256 + 2048 + 1024;   // Q 16 + K 2x8 + V 2x8 + P 2x16 + O staging 16 KiB + barriers + (m,l) exchange + slack
 constexpr uint32_t kFwdTmemCols = 256;                        // S slots: columns [0,64) [64,128), O_A: [128,192), O_B: [192,256)
 constexpr float kRescaleThreshold = 8.0f;                     // log2 domain
 
@@ -132,6 +132,11 @@ __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t 
   l += (sum0 + sum1) + (sum2 + sum3);
 }
 
+// Persistent: the grid is two CTAs per SM; CTA c walks the work items c, c + grid, c + 2 grid, ... of the list
+// (query tile, head, batch) sorted heaviest first.  TMEM is allocated once, barrier phases run on across items, the TMA
+// producer and the MMA thread start on the next item (Q, first keys, S_0, S_1) while the softmax warps still merge and store
+// the previous one; the output store is asynchronous (its own 16 KiB staging buffer).  A one-CTA-per-item launch spent
+// ~5 us per CTA on allocation, first-load latency, store drain and relaunch: 41 % of the run at T = 1024 (r2 measurements).
 __global__ void __launch_bounds__(kFwdThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                 const __grid_constant__ CUtensorMap tmO, const AttnFwdParams p) {
@@ -141,7 +146,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sK = smem + kAttTileBytes;                         // 2 slots x 8 KiB
   uint8_t* sV = smem + 2 * kAttTileBytes;                     // 2 slots x 8 KiB
   uint8_t* sP = smem + 3 * kAttTileBytes;                     // 2 slots x 16 KiB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * kAttTileBytes);
+  uint8_t* sO = smem + 5 * kAttTileBytes;                     // 16 KiB output staging
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kAttTileBytes);
   uint64_t* q_full = bars + 0;
   uint64_t* k_full = bars + 1;      // [2]
   uint64_t* k_empty = bars + 3;     // [2]
@@ -149,26 +155,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* v_empty = bars + 7;     // [2]
   uint64_t* s_full = bars + 9;      // [2]
   uint64_t* p_ready = bars + 11;    // [2]
-  uint64_t* pv_done = bars + 13;    // [2]  P_j V_j complete: P slot free, O readable
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
-  float2* ml_xchg = reinterpret_cast<float2*>(smem + 5 * kAttTileBytes + 256);      // [2 sets][128 rows] (m, l)
+  uint64_t* pv_done = bars + 13;    // [2]  P_j V_j complete: P slot free, O_set at rest
+  uint64_t* q_empty = bars + 15;    // every S of the item has been issued and completed: Q may be overwritten
+  uint64_t* o_free = bars + 16;     // the epilogue has taken both accumulators out of TMEM
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 18);
+  float2* ml_xchg = reinterpret_cast<float2*>(smem + 6 * kAttTileBytes + 256);      // [2 sets][128 rows] (m, l)
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-
-  // heaviest tiles (most key tiles) first: blockIdx.x = (n_qt - 1 - qt) * (B*H) + bh
   const int bh_total = p.B * p.H;
-  const int qt = p.n_qt - 1 - (int)(blockIdx.x / bh_total);
-  const int bh = (int)(blockIdx.x % bh_total);
-  const int b = bh / p.H, h = bh % p.H;
-  const int q0 = qt * kAttTile;
-  const int n_kv = 2 * (qt + 1);                               // 64-row key tiles 0 .. 2qt+1; the last two straddle the diagonal
+  const int n_items = p.n_qt * bh_total;
 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmKV);
     tma_prefetch_desc(&tmO);
     mbar_init(q_full, 1);
+    mbar_init(q_empty, 1);
+    mbar_init(o_free, 8);             // one arrive per softmax warp
     for (int i = 0; i < 2; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
@@ -188,20 +192,31 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const uint32_t tmem_s = tmem_base;                           // + 64 * slot
   const uint32_t tmem_o = tmem_base + 128;                     // + 64 * set
 
+  // item w -> (query tile, batch*head): heaviest (most key tiles) first
+  // Every item has an even number of 64-row key tiles, so slot = j & 1 and the ring phases follow from `h0`, the number of
+  // tiles PER SET this CTA has processed before the item.
   if (warp_idx == 0) {
     // ===================================================================== TMA producer
     if (elect_one()) {
-      mbar_expect_tx(q_full, kAttTileBytes);
-      tma_load_4d(sQ, &tmQ, q_full, 0, q0, h, b);
-      for (int j = 0; j < n_kv; ++j) {
-        const int slot = j & 1;
-        const uint32_t par = (j >> 1) & 1;
-        mbar_wait_backoff(&k_empty[slot], par ^ 1, 128);
-        mbar_expect_tx(&k_full[slot], kKvTileBytes);
-        tma_load_4d(sK + slot * kKvTileBytes, &tmKV, &k_full[slot], 0, j * kKvTile, p.H + h, b);
-        mbar_wait_backoff(&v_empty[slot], par ^ 1, 128);
-        mbar_expect_tx(&v_full[slot], kKvTileBytes);
-        tma_load_4d(sV + slot * kKvTileBytes, &tmKV, &v_full[slot], 0, j * kKvTile, 2 * p.H + h, b);
+      int h0 = 0, it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int qt = p.n_qt - 1 - w / bh_total, bh = w % bh_total;
+        const int b = bh / p.H, h = bh % p.H;
+        const int n_kv = 2 * (qt + 1);
+        mbar_wait_backoff(q_empty, (it & 1) ^ 1, 128);
+        mbar_expect_tx(q_full, kAttTileBytes);
+        tma_load_4d(sQ, &tmQ, q_full, 0, qt * kAttTile, h, b);
+        for (int j = 0; j < n_kv; ++j) {
+          const int slot = j & 1;
+          const uint32_t par = (h0 + (j >> 1)) & 1;
+          mbar_wait_backoff(&k_empty[slot], par ^ 1, 128);
+          mbar_expect_tx(&k_full[slot], kKvTileBytes);
+          tma_load_4d(sK + slot * kKvTileBytes, &tmKV, &k_full[slot], 0, j * kKvTile, p.H + h, b);
+          mbar_wait_backoff(&v_empty[slot], par ^ 1, 128);
+          mbar_expect_tx(&v_full[slot], kKvTileBytes);
+          tma_load_4d(sV + slot * kKvTileBytes, &tmKV, &v_full[slot], 0, j * kKvTile, 2 * p.H + h, b);
+        }
+        h0 += n_kv >> 1;
       }
     }
   } else if (warp_idx == 1) {
@@ -210,34 +225,43 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);      // S[128 q x 64 kv]  = Q (K-major) x K (K-major)
       const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);      // O[128 q x 64 d]   = P (K-major) x V (MN-major)
       const uint64_t dq = make_smem_desc_sw128(smem_u32(sQ), 0, 1024);
-      auto issue_s = [&](int j) {
-        const int slot = j & 1;
-        mbar_wait(&k_full[slot], (j >> 1) & 1);
-        tc_fence_after();
-        const uint64_t dk = make_smem_desc_sw128(smem_u32(sK + slot * kKvTileBytes), 0, 1024);
+      int h0 = 0, it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int qt = p.n_qt - 1 - w / bh_total;
+        const int n_kv = 2 * (qt + 1);
+        auto issue_s = [&](int j) {
+          const int slot = j & 1;
+          mbar_wait(&k_full[slot], (h0 + (j >> 1)) & 1);
+          tc_fence_after();
+          const uint64_t dk = make_smem_desc_sw128(smem_u32(sK + slot * kKvTileBytes), 0, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          umma_f16(tmem_s + slot * kKvTile, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(&k_empty[slot]);
-        umma_commit(&s_full[slot]);
-      };
-      mbar_wait(q_full, 0);
-      issue_s(0);
-      for (int j = 0; j < n_kv; ++j) {
-        const int slot = j & 1;
-        const uint32_t par = (j >> 1) & 1;
-        // S runs one tile ahead of P V: slot (j+1)&1 was released by p_ready(j-1), waited for in the previous iteration
-        if (j + 1 < n_kv) issue_s(j + 1);
-        mbar_wait_backoff(&p_ready[slot], par, 32);
-        mbar_wait(&v_full[slot], par);
-        tc_fence_after();
-        const uint64_t dp = make_smem_desc_sw128(smem_u32(sP + slot * kAttTileBytes), 0, 1024);
-        const uint64_t dv = make_smem_desc_sw128(smem_u32(sV + slot * kKvTileBytes), kKvTileBytes, 1024);
+          for (int k = 0; k < 4; ++k)
+            umma_f16(tmem_s + slot * kKvTile, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+          umma_commit(&k_empty[slot]);
+          umma_commit(&s_full[slot]);
+          if (j == n_kv - 1) umma_commit(q_empty);               // last use of Q in this item
+        };
+        mbar_wait(q_full, it & 1);
+        issue_s(0);            // both S slots are free: the previous item's last two p_ready were waited for below
+        for (int j = 0; j < n_kv; ++j) {
+          const int slot = j & 1;
+          const uint32_t par = (h0 + (j >> 1)) & 1;
+          // S runs one tile ahead of P V.  (Issuing S_{j+2} BEFORE P_j V_j was measured slower, 0.143 vs 0.118 ms: the set that
+          // owns the slot needs P_j V_j complete too, to reuse its P buffer.)
+          if (j + 1 < n_kv) issue_s(j + 1);
+          mbar_wait_backoff(&p_ready[slot], par, 32);
+          mbar_wait(&v_full[slot], par);
+          if (j == 0 && it > 0) mbar_wait(o_free, (it - 1) & 1);  // the previous item's accumulators have been read out
+          tc_fence_after();
+          const uint64_t dp = make_smem_desc_sw128(smem_u32(sP + slot * kAttTileBytes), 0, 1024);
+          const uint64_t dv = make_smem_desc_sw128(smem_u32(sV + slot * kKvTileBytes), kKvTileBytes, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k)      // A: 32 bytes per 16-wide k step; B: 16 key rows x 128 B per k step
-          umma_f16(tmem_o + slot * kAttD, dp + (uint64_t)(k * 2), dv + (uint64_t)(k * 128), idesc_o, (j > 1 || k > 0) ? 1u : 0u);
-        umma_commit(&v_empty[slot]);
-        umma_commit(&pv_done[slot]);
+          for (int k = 0; k < 4; ++k)      // A: 32 bytes per 16-wide k step; B: 16 key rows x 128 B per k step
+            umma_f16(tmem_o + slot * kAttD, dp + (uint64_t)(k * 2), dv + (uint64_t)(k * 128), idesc_o, (j > 1 || k > 0) ? 1u : 0u);
+          umma_commit(&v_empty[slot]);
+          umma_commit(&pv_done[slot]);
+        }
+        h0 += n_kv >> 1;
       }
     }
   } else {
@@ -247,46 +271,55 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const float c = p.scale_log2;
-    float m_ref = -INFINITY, l = 0.f;
     uint8_t* sPslot = sP + set * kAttTileBytes;
     const uint32_t my_s = tmem_s + lane_sel + set * kKvTile;
     const uint32_t my_o = tmem_o + lane_sel + set * kAttD;
-    const int n_t = n_kv >> 1;                                 // tiles of this set: j = 2t + set
+    int h0 = 0;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int qt = p.n_qt - 1 - w / bh_total, bh = w % bh_total;
+      const int b = bh / p.H, h = bh % p.H;
+      const int q0 = qt * kAttTile;
+      const int n_t = qt + 1;                                  // tiles of this set: j = 2t + set
+      float m_ref = -INFINITY, l = 0.f;
 
-    for (int t = 0; t < n_t; ++t) {
-      const uint32_t par = t & 1;
-      mbar_wait(&s_full[set], par);
-      if (t >= 1) mbar_wait(&pv_done[set], par ^ 1);           // this set's previous P V is complete: P slot free, O_set at rest
+      for (int t = 0; t < n_t; ++t) {
+        const uint32_t par = (h0 + t) & 1;
+        mbar_wait(&s_full[set], par);
+        if (h0 + t >= 1) mbar_wait(&pv_done[set], par ^ 1);    // this set's previous P V is complete: P slot free, O_set at rest
+        tc_fence_after();
+        if (t == n_t - 1) fwd_softmax_tile<true>(my_s, my_o, sPslot, row, set * kKvTile, c, t == 0, m_ref, l);
+        else fwd_softmax_tile<false>(my_s, my_o, sPslot, row, 0, c, t == 0, m_ref, l);
+        tc_fence_before();          // our TMEM reads of S_j (and rescale stores to O) are ordered before the MMA thread's next issue
+        fence_proxy_async_smem();   // P_j (generic-proxy stores) visible to the tensor core (async proxy)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_ready[set]);
+      }
+      h0 += n_t;
+
+      // epilogue: merge the two sets' partial results.  O = (O_A wA + O_B wB) / (l_A wA + l_B wB), w = 2^((m_set - m) c).
+      ml_xchg[set * kAttTile + row] = make_float2(m_ref, l);
+      mbar_wait(&pv_done[set], (h0 - 1) & 1);                  // this set's last P V is complete (a set only ever waits on its
+      tc_fence_after();                                        // own barrier: it is never more than one phase behind it)
+      if (threadIdx.x == 64) tma_store_wait_read<0>();         // the previous item's store has finished reading the staging tile
+      tc_fence_before();
+      named_bar_sync(1, 256);                                  // ... and after this, so is the other set's
       tc_fence_after();
-      if (t == n_t - 1) fwd_softmax_tile<true>(my_s, my_o, sPslot, row, set * kKvTile, c, t == 0, m_ref, l);
-      else fwd_softmax_tile<false>(my_s, my_o, sPslot, row, 0, c, t == 0, m_ref, l);
-      tc_fence_before();            // our TMEM reads of S_j (and rescale stores to O) are ordered before the MMA thread's next issue
-      fence_proxy_async_smem();     // P_j (generic-proxy stores) visible to the tensor core (async proxy)
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&p_ready[set]);
-    }
-
-    // epilogue: merge the two sets' partial results.  O = (O_A wA + O_B wB) / (l_A wA + l_B wB), w = 2^((m_set - m) c).
-    ml_xchg[set * kAttTile + row] = make_float2(m_ref, l);
-    mbar_wait(&pv_done[set], (n_t - 1) & 1);                   // this set's last P V is complete (a set only ever waits on its
-    tc_fence_after();                                          // own barrier: it is never more than one phase behind it)
-    tc_fence_before();
-    named_bar_sync(1, 256);                                    // ... and after this, so is the other set's
-    tc_fence_after();
-    const float2 other = ml_xchg[(set ^ 1) * kAttTile + row];
-    const float m_a = set == 0 ? m_ref : other.x, l_a = set == 0 ? l : other.y;
-    const float m_b = set == 0 ? other.x : m_ref, l_b = set == 0 ? other.y : l;
-    const float m = fmaxf(m_a, m_b);                           // finite: set A's first tile has an unmasked key for every row
-    const float w_a = exp2f((m_a - m) * c), w_b = exp2f((m_b - m) * c);      // exp2(-inf) = 0 for a set that saw only masked keys
-    const float l_tot = l_a * w_a + l_b * w_b;
-    const float inv_l = 1.f / l_tot;
-    if (set == 0 && q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m * c + log2f(l_tot)) * kLn2;
-    {
+      const float2 other = ml_xchg[(set ^ 1) * kAttTile + row];
       // this set merges output columns [32 set, 32 set + 32)
       uint32_t ra[32], rb[32];
       tmem_ld_32x32(tmem_o + lane_sel + set * 32, ra);
       tmem_ld_32x32(tmem_o + lane_sel + kAttD + set * 32, rb);
       tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(o_free);                      // the next item's first P V may overwrite the accumulators
+      const float m_a = set == 0 ? m_ref : other.x, l_a = set == 0 ? l : other.y;
+      const float m_b = set == 0 ? other.x : m_ref, l_b = set == 0 ? other.y : l;
+      const float m = fmaxf(m_a, m_b);                         // finite: set A's first tile has an unmasked key for every row
+      const float w_a = exp2f((m_a - m) * c), w_b = exp2f((m_b - m) * c);    // exp2(-inf) = 0 for a set that saw only masked keys
+      const float l_tot = l_a * w_a + l_b * w_b;
+      const float inv_l = 1.f / l_tot;
+      if (set == 0 && q0 + row < p.T) p.lse[(size_t)bh * p.T + q0 + row] = (m * c + log2f(l_tot)) * kLn2;
       const float fa = w_a * inv_l, fb = w_b * inv_l;
 #pragma unroll
       for (int q4 = 0; q4 < 4; ++q4) {
@@ -294,16 +327,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(ra[8 * q4 + i]) * fa + __uint_as_float(rb[8 * q4 + i]) * fb;
         uint4 pk = {pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7])};
-        st_swizzled_row_piece(sP, row, set * 4 + q4, pk);        // staging = P slot 0: every MMA that read it has completed
+        st_swizzled_row_piece(sO, row, set * 4 + q4, pk);
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 256);         // staging complete; also: everybody has read ml_xchg before the next item rewrites it
+      if (threadIdx.x == 64) {
+        tma_store_4d(&tmO, sO, 0, q0, h, b);
+        tma_store_commit();
       }
     }
-    fence_proxy_async_smem();
-    named_bar_sync(1, 256);
-    if (threadIdx.x == 64) {
-      tma_store_4d(&tmO, sP, 0, q0, h, b);
-      tma_store_commit();
-      tma_store_wait<0>();
-    }
+    if (threadIdx.x == 64) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -676,7 +709,8 @@ DFB_API int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, i
     DFB_CUDA_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
     attr_done[dev & 63] = true;
   }
-  const long grid = (long)p.n_qt * B * H;
+  long grid = (long)p.n_qt * B * H;                           // persistent: at most two CTAs per SM, each walks a strided list
+  if (grid > 2L * num_sms()) grid = 2L * num_sms();
   attn_fwd_kernel<<<(unsigned)grid, kFwdThreads, kFwdSmem, stream>>>(tmQ, tmKV, tmO, p);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
