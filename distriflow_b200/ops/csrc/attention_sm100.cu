@@ -412,7 +412,8 @@ struct AttnBwdParams {
 // P and dS for one query row and one half (64 key columns) of the tile: P = exp2(S*c - lse*log2e), dS = P (dP - delta) / sqrt(D).
 template <bool kDiag>
 __device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t tmem_dp_lane, uint8_t* pblk, uint8_t* dsblk, int row,
-                                                 int half, float lse2, float dl, float scale, float scale_log2) {
+                                                 int half, float lse2, float dl, float scale, float scale_log2, uint64_t* smem_free,
+                                                 uint32_t smem_free_parity, bool wait_free) {
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
     const int col0 = half * 64 + ch * 32;
@@ -433,6 +434,8 @@ __device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t 
       }
       uint4 pk = {pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7])};
       uint4 dk = {pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7])};
+      // first store of the tile: the previous tile's dV / dK products must have finished reading P and dS
+      if (ch == 0 && q4 == 0 && wait_free) mbar_wait(smem_free, smem_free_parity);
       st_swizzled_row_piece(pblk, row, ch * 4 + q4, pk);
       st_swizzled_row_piece(dsblk, row, ch * 4 + q4, dk);
     }
@@ -476,7 +479,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint64_t* dq_full = bars + 7;
   uint64_t* dq_empty = bars + 8;
   uint64_t* dkv_full = bars + 9;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* pds_free = bars + 10;     // dV / dK of the tile have read P and dS: the shared-memory tiles may be rewritten
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -504,6 +508,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 8);
     mbar_init(dkv_full, 1);
+    mbar_init(pds_free, 1);
     fence_mbar_init();
   }
   if (warp_idx == 1) tmem_alloc<kBwdTmemCols>(tmem_ptr);
@@ -543,39 +548,45 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
       const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
       const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
-      mbar_wait(kv_full, 0);
-      for (int it = 0; it < n_it; ++it) {
+      // Issue order per query tile i (everything the compute warps wait for comes first):
+      //   [P_i, dS_i ready]  dQ_i  ->  S_{i+1}, dP_{i+1}  ->  dV += P_i^T dO_i, dK += dS_i^T Q_i
+      // so the dQ drain overlaps S/dP of the next tile and the next softmax overlaps dV/dK of this one (r2 ncu: with dV, dK
+      // first the compute warps spent 1700 cycles per tile waiting for dQ and 900 for the next S/dP).
+      auto issue_sdp = [&](int it) {
         const int st = it & 1;
-        const uint32_t ph = it & 1, sph = (it >> 1) & 1;
+        mbar_wait(&qdo_full[st], (it >> 1) & 1);
+        tc_fence_after();
         const uint64_t dq_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), 0, 1024);
         const uint64_t ddo_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), 0, 1024);
-        const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), kAttTileBytes, 1024);
-        const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
-        mbar_wait(&qdo_full[st], sph);
-        tc_fence_after();
-        // S and dP (their TMEM columns are free: pds_ready(it-1) was waited for below)
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq_kmaj + (uint64_t)(k * 2), dk_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_dp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(sdp_full);
-        mbar_wait_backoff(pds_ready, ph, 32);
+      };
+      mbar_wait(kv_full, 0);
+      issue_sdp(0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = it & 1;
+        const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), kAttTileBytes, 1024);
+        const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
+        mbar_wait_backoff(pds_ready, ph, 32);     // P_i, dS_i written; the compute warps are done with S_i / dP_i in TMEM
+        if (it > 0) mbar_wait(dq_empty, ph ^ 1);  // the compute warps have taken dQ_{i-1} out of TMEM
         tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)         // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
+          umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
+        umma_commit(dq_full);
+        if (it + 1 < n_it) issue_sdp(it + 1);
 #pragma unroll
         for (int k = 0; k < 8; ++k)         // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
           umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
         for (int k = 0; k < 8; ++k)         // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
           umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
-        if (it > 0) {
-          mbar_wait(dq_empty, ph ^ 1);      // the compute warps have taken dQ_{i-1} out of TMEM
-          tc_fence_after();
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k)         // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
-          umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
         umma_commit(&qdo_empty[st]);
-        umma_commit(dq_full);               // also means: P / dS in shared memory have been consumed
+        umma_commit(pds_free);
       }
       umma_commit(dkv_full);
     }
@@ -586,21 +597,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const int ctid = threadIdx.x - 64;                          // 0..255
+    // row statistics of the NEXT query tile are fetched while the current one is processed (the loads were 1200 exposed
+    // cycles per tile when issued at the top of the tile)
+    float lse_nx = 0.f, dl_nx = 0.f;
+    if (kv0 + row < p.T) {                                      // first query tile = the diagonal one: q0 = kv0
+      lse_nx = __ldg(p.lse + (size_t)bh * p.T + kv0 + row);
+      dl_nx = __ldg(p.delta + (size_t)bh * p.T + kv0 + row);
+    }
     for (int it = 0; it < n_it; ++it) {
       const uint32_t ph = it & 1;
       const int q0 = (jt + it) * kAttTile;
       const bool diag = (it == 0);
-      float lse2 = 0.f, dl = 0.f;
-      if (q0 + row < p.T) {
-        lse2 = __ldg(p.lse + (size_t)bh * p.T + q0 + row) * kLog2e;
-        dl = __ldg(p.delta + (size_t)bh * p.T + q0 + row);
+      const float lse2 = lse_nx * kLog2e, dl = dl_nx;
+      lse_nx = 0.f;
+      dl_nx = 0.f;
+      if (it + 1 < n_it && q0 + kAttTile + row < p.T) {
+        lse_nx = __ldg(p.lse + (size_t)bh * p.T + q0 + kAttTile + row);
+        dl_nx = __ldg(p.delta + (size_t)bh * p.T + q0 + kAttTile + row);
       }
       mbar_wait(sdp_full, ph);
       tc_fence_after();
       uint8_t* pblk = sP + half * kAttTileBytes;
       uint8_t* dsblk = sdS + half * kAttTileBytes;
-      if (diag) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2);
-      else bwd_softmax_half<false>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2);
+      if (diag) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
+                                       pds_free, ph ^ 1, it > 0);
+      else bwd_softmax_half<false>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
+                                   pds_free, ph ^ 1, it > 0);
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
