@@ -23,5 +23,6 @@ from .server import AbstractServer, AsynchronousSGDServer, DistriServer, Federat
 from .worker import (AbstractClient, AsynchronousSGDClient, DistriClientTorchModel, DistriWorker, FederatedClient,
                      is_distributed_client_model)
 from .trainer import Trainer
+from .b200 import B200Model, B200Server, B200Worker
 
 __version__ = "0.1.0"

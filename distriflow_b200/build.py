@@ -94,10 +94,15 @@ def build(force: bool = False, jobs: int = 8, verbose: bool = False) -> str:
     return OUT
 
 
-if __name__ == "__main__":
+def main(argv=None) -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("-j", type=int, default=8)
     ap.add_argument("-v", action="store_true")
-    a = ap.parse_args()
+    a = ap.parse_args(argv)
     print(build(a.force, a.j, a.v))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -19,7 +19,7 @@ from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-__all__ = ["MlpOracle", "log_softmax", "softmax", "ref_compat_loss_and_grad", "softmax_ce_loss_and_grad",
+__all__ = ["MlpOracle", "CnnOracle", "log_softmax", "softmax", "ref_compat_loss_and_grad", "softmax_ce_loss_and_grad",
            "simulate_async", "simulate_sync", "synthetic_mnist"]
 
 
@@ -88,21 +88,7 @@ class MlpOracle:
         w1, b1, w2, b2 = self.vars
         x2, h_pre, h, z, p = self.forward(x)
         y = y.astype(np.float32)
-        if self.loss in ("referenceCompat", "referenceCompatTrueGrad"):
-            loss, dp = ref_compat_loss_and_grad(p, y, "custom" if self.loss == "referenceCompat" else "true")
-            dz = p * (dp - (dp * p).sum(-1, keepdims=True))          # back through the model's own softmax layer
-        elif self.loss == "softmaxCrossEntropy":                     # standard CE on the logits
-            loss, dz = softmax_ce_loss_and_grad(z, y)
-        elif self.loss == "categoricalCrossentropy":
-            b = x2.shape[0]
-            loss = float((-(y * np.log(np.clip(p, 1e-7, 1 - 1e-7))).sum(-1)).mean())
-            dz = (p * y.sum(-1, keepdims=True) - y) / b
-        elif self.loss == "meanSquaredError":
-            loss = float(((y - p) ** 2).mean())
-            dp = 2 * (p - y) / p.size
-            dz = p * (dp - (dp * p).sum(-1, keepdims=True))
-        else:
-            raise ValueError(self.loss)
+        loss, dz = _loss_grad_wrt_logits(self.loss, z, p, y)
         dw2, db2 = h.T @ dz, dz.sum(0)
         dh = (dz @ w2.T) * (h_pre > 0)
         dw1, db1 = x2.T @ dh, dh.sum(0)
@@ -111,6 +97,110 @@ class MlpOracle:
     def update(self, grads: Sequence[np.ndarray], lr: Optional[float] = None) -> None:
         lr = self.lr if lr is None else lr
         self.vars = [v - np.float32(lr) * g for v, g in zip(self.vars, grads)]
+
+    def evaluate(self, x: np.ndarray, y: np.ndarray) -> List[float]:
+        p = self.predict(x)
+        return [float(((y - p) ** 2).mean()), float((p.argmax(-1) == y.argmax(-1)).mean())]
+
+
+def _loss_grad_wrt_logits(loss_name: str, z: np.ndarray, p: np.ndarray, y: np.ndarray) -> Tuple[float, np.ndarray]:
+    """Loss value and d loss / d logits for a model that ends in a softmax layer (shared by both oracles)."""
+    if loss_name in ("referenceCompat", "referenceCompatTrueGrad"):
+        loss, dp = ref_compat_loss_and_grad(p, y, "custom" if loss_name == "referenceCompat" else "true")
+        return loss, p * (dp - (dp * p).sum(-1, keepdims=True))      # back through the model's own softmax layer
+    if loss_name == "softmaxCrossEntropy":                           # standard CE on the logits
+        return softmax_ce_loss_and_grad(z, y)
+    if loss_name == "categoricalCrossentropy":
+        loss = float((-(y * np.log(np.clip(p, 1e-7, 1 - 1e-7))).sum(-1)).mean())
+        return loss, (p * y.sum(-1, keepdims=True) - y) / z.shape[0]
+    if loss_name == "meanSquaredError":
+        dp = 2 * (p - y) / p.size
+        return float(((y - p) ** 2).mean()), p * (dp - (dp * p).sum(-1, keepdims=True))
+    raise ValueError(loss_name)
+
+
+def _conv_valid(x: np.ndarray, w: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """NHWC x HWIO valid convolution, stride 1.  Returns (y, patch matrix) — K2 of SURVEY §2.5."""
+    kh, kw, c, k = w.shape
+    b, h, ww, _ = x.shape
+    oh, ow = h - kh + 1, ww - kw + 1
+    win = np.lib.stride_tricks.sliding_window_view(x, (kh, kw), axis=(1, 2))          # [B, OH, OW, C, kh, kw]
+    patches = np.ascontiguousarray(win.transpose(0, 1, 2, 4, 5, 3)).reshape(b * oh * ow, kh * kw * c)
+    return (patches @ w.reshape(kh * kw * c, k)).reshape(b, oh, ow, k), patches
+
+
+def _conv_valid_dx(dy: np.ndarray, w: np.ndarray) -> np.ndarray:
+    """Data gradient of `_conv_valid`: full correlation of dy with the flipped filter, channels swapped."""
+    kh, kw, c, k = w.shape
+    dyp = np.pad(dy, ((0, 0), (kh - 1, kh - 1), (kw - 1, kw - 1), (0, 0)))
+    wf = np.ascontiguousarray(w[::-1, ::-1].transpose(0, 1, 3, 2))                      # [kh, kw, K, C]
+    return _conv_valid(dyp, wf)[0]
+
+
+class CnnOracle:
+    """The Keras-converted MNIST CNN of `/root/reference/experiment/mnist/model.json`, NumPy fp32, NHWC / HWIO:
+    Conv2D(32,3x3,valid)-ReLU-Conv2D(32,3x3,valid)-ReLU-MaxPool 2x2-Flatten(H,W,C)-Dense(128)-ReLU-Dense(classes)-softmax.
+    Dropout is inactive, as in the reference's `predictOnBatch`.  K1-K6 for the CNN config."""
+
+    def __init__(self, classes: int = 5, seed: int = 0, loss: str = "referenceCompat", lr: float = 0.001):
+        rng = np.random.default_rng(seed)
+
+        def glorot(shape, fan_in, fan_out):
+            lim = np.sqrt(6.0 / (fan_in + fan_out))
+            return rng.uniform(-lim, lim, size=shape).astype(np.float32)
+
+        self.vars: List[np.ndarray] = [
+            glorot((3, 3, 1, 32), 9, 288), np.zeros(32, np.float32),
+            glorot((3, 3, 32, 32), 288, 288), np.zeros(32, np.float32),
+            glorot((4608, 128), 4608, 128), np.zeros(128, np.float32),
+            glorot((128, classes), 128, classes), np.zeros(classes, np.float32)]
+        self.loss, self.lr = loss, lr
+
+    get_vars, set_vars, update = MlpOracle.get_vars, MlpOracle.set_vars, MlpOracle.update
+
+    def forward(self, x: np.ndarray):
+        k1, b1, k2, b2, w3, b3, w4, b4 = self.vars
+        x = x.astype(np.float32).reshape(x.shape[0], 28, 28, 1)
+        a1_pre, p1 = _conv_valid(x, k1)
+        a1_pre = a1_pre + b1
+        a1 = np.maximum(a1_pre, 0)
+        a2_pre, p2 = _conv_valid(a1, k2)
+        a2_pre = a2_pre + b2
+        a2 = np.maximum(a2_pre, 0)
+        bsz = x.shape[0]
+        win = a2.reshape(bsz, 12, 2, 12, 2, 32)
+        pool = win.max(axis=(2, 4))                                                    # [B, 12, 12, 32]
+        flat = pool.reshape(bsz, 4608)                                                 # H, W, C order (SURVEY §5.1)
+        h_pre = flat @ w3 + b3
+        h = np.maximum(h_pre, 0)
+        z = h @ w4 + b4
+        return dict(x=x, p1=p1, a1_pre=a1_pre, a1=a1, p2=p2, a2_pre=a2_pre, a2=a2, pool=pool, flat=flat, h_pre=h_pre, h=h,
+                    z=z, p=softmax(z))
+
+    def predict(self, x: np.ndarray) -> np.ndarray:
+        return self.forward(x)["p"]
+
+    def fit(self, x: np.ndarray, y: np.ndarray) -> Tuple[float, List[np.ndarray]]:
+        k1, b1, k2, b2, w3, b3, w4, b4 = self.vars
+        f = self.forward(x)
+        loss, dz = _loss_grad_wrt_logits(self.loss, f["z"], f["p"], y.astype(np.float32))
+        dw4, db4 = f["h"].T @ dz, dz.sum(0)
+        dh = (dz @ w4.T) * (f["h_pre"] > 0)
+        dw3, db3 = f["flat"].T @ dh, dh.sum(0)
+        bsz = f["x"].shape[0]
+        dpool = (dh @ w3.T).reshape(bsz, 12, 12, 32)
+        # max-pool backward: the gradient goes to the window maximum (first one on a tie; ties are zeros behind a dead ReLU)
+        win = f["a2"].reshape(bsz, 12, 2, 12, 2, 32)
+        mask = win == f["pool"][:, :, None, :, None, :]
+        first = np.cumsum(np.cumsum(mask, axis=2), axis=4) == 1
+        da2 = ((mask & first) * dpool[:, :, None, :, None, :]).reshape(bsz, 24, 24, 32)
+        da2 = da2 * (f["a2_pre"] > 0)
+        dk2 = (f["p2"].T @ da2.reshape(-1, 32)).reshape(3, 3, 32, 32)
+        db2 = da2.sum((0, 1, 2))
+        da1 = _conv_valid_dx(da2, k2) * (f["a1_pre"] > 0)
+        dk1 = (f["p1"].T @ da1.reshape(-1, 32)).reshape(3, 3, 1, 32)
+        db1 = da1.sum((0, 1, 2))
+        return loss, [g.astype(np.float32) for g in (dk1, db1, dk2, db2, dw3, db3, dw4, db4)]
 
     def evaluate(self, x: np.ndarray, y: np.ndarray) -> List[float]:
         p = self.predict(x)
@@ -149,7 +239,7 @@ def simulate_async(model: MlpOracle, x: np.ndarray, y: np.ndarray, *, batch_size
         if qi < len(queue):
             hold[w] = (model.get_vars(), version, queue[qi])
             qi += 1
-    out = {"loss": [], "staleness": [], "dropped": 0, "versions": 0}
+    out = {"loss": [], "staleness": [], "dropped": 0, "versions": 0, "initial_vars": model.get_vars()}
     step = 0
     retry: List[Tuple[int, int]] = []
     while any(h is not None for h in hold):

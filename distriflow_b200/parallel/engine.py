@@ -101,6 +101,7 @@ class DataParallelEngine:
         if float(self.cfg["watchdogSeconds"]) > 0:
             self._start_watchdog(float(self.cfg["watchdogSeconds"]))
         self._graph, self._static_in, self._static_loss, self._warm, self._capturing, self._seq = None, None, None, 0, False, 0
+        self._accumulating, self._acc_count = False, 0
         if self._graph_mode:
             self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
             self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -210,6 +211,8 @@ class DataParallelEngine:
 
     def _param_ready(self, b: Bucket) -> None:
         b.pending -= 1
+        if self._accumulating:                                 # micro-batch of an unfinished version: nothing is launched
+            return
         if b.pending == 0 and self.cfg["debugPoison"]:
             # Race detector: from the moment a bucket is reported complete its working weights may be overwritten by the
             # fused kernel, so nothing enqueued later in this backward may read them.  Overwrite them with NaN right here
@@ -288,6 +291,7 @@ class DataParallelEngine:
             self._prog_pin.copy_(self._prog_dev, non_blocking=True)
         if self._graph_mode and self.world > 1:
             self._epoch_dev.add_(len(self.buckets))            # next step's barrier generations start after this step's
+        self._acc_count = 0
         if _count:
             old = self.version
             self.version += 1
@@ -295,8 +299,48 @@ class DataParallelEngine:
                 cb(old, self.version)
         return loss.detach()
 
+    def accumulate(self, *batch: Any) -> torch.Tensor:
+        """Forward + backward of one more micro-batch of the CURRENT version: its gradient is added to the bucket-shaped
+        `savedGradient` (fp32) and nothing is communicated or applied.  The next `step()` folds the saved sum into its own
+        gradient, divides by the number of contributions and runs the fused reduce-scatter + optimizer + all-gather once.
+        This is `minUpdatesPerVersion = K x workers` of the reference (`/root/reference/src/server/federated_server.ts:73-90`:
+        K uploads are buffered and averaged before one update) with the buffer kept on the GPU (README `savedGradient`)."""
+        if self._graph is not None:
+            raise RuntimeError("accumulate() after the step has been captured into a CUDA graph: build the engine with cudaGraph=False")
+        self._graph_mode = False
+        self.zero_pending()
+        self._accumulating = True
+        try:
+            loss = self.loss_fn(self.model, *batch)
+            loss.backward()
+        finally:
+            self._accumulating = False
+        for b in self.buckets:
+            if getattr(b, "acc", None) is None:
+                b.acc = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
+            if self._acc_count == 0:
+                b.acc.copy_(b.grad_buf)
+            else:
+                b.acc.add_(b.grad_buf)
+        self._acc_count += 1
+        return loss.detach()
+
+    @property
+    def savedGradient(self) -> Optional[List[torch.Tensor]]:
+        """The aggregated gradient of the micro-batches accumulated so far (one flat fp32 tensor per bucket), or None."""
+        if self._acc_count == 0:
+            return None
+        return [b.acc for b in self.buckets]
+
+    @property
+    def savedCount(self) -> int:
+        return self._acc_count
+
     def _launch_bucket(self, b: Bucket) -> None:
         b.launched = True
+        if self._acc_count:                                     # fold the saved micro-batch gradients in: mean over all of them
+            k = float(self._acc_count + 1)
+            b.grad_buf.copy_((b.acc + b.grad_buf.float()) / k)
         if self.backend == "p2p":
             self._launch_bucket_p2p(b)
         else:

@@ -323,8 +323,12 @@ class FederatedClient(AbstractClient):
         num_examples_remaining
 
 
-def DistriWorker(server, model, config: Optional[Dict[str, Any]] = None, mode: str = "async") -> AbstractClient:
-    """README facade (`/root/reference/README.md:16-21`): 'async'/'sync' -> dispatched batches, 'federated' -> own data."""
+def DistriWorker(server, model=None, config: Optional[Dict[str, Any]] = None, mode: str = "async", backend: str = "host"):
+    """README facade (`/root/reference/README.md:16-21`): 'async'/'sync' -> dispatched batches, 'federated' -> own data.
+    `backend="b200"`: `server` is this process's `DistriServer(..., backend="b200")`; the worker is this GPU rank's handle."""
+    if backend == "b200":
+        from .b200 import B200Worker
+        return B200Worker(server, config)
     if mode in ("async", "sync"):
         return AsynchronousSGDClient(server, model, config)
     if mode == "federated":

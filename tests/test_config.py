@@ -37,3 +37,15 @@ def test_validation():
     with pytest.raises(ConfigError):
         engine_config({"optimizer": "lamb"})
     assert engine_config({"maximumStaleness": 4})["maximumStaleness"] == 4
+
+
+def test_packaging_metadata_builds_and_ships_the_native_library():
+    """`pip install .` runs the nvcc build (setup.py hook) and the wheel carries the .so (reference: src/*/package.json)."""
+    import os
+    import tomllib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    meta = tomllib.load(open(os.path.join(root, "pyproject.toml"), "rb"))
+    assert meta["project"]["name"] == "distriflow-b200"
+    assert "ops/*.so" in meta["tool"]["setuptools"]["package-data"]["distriflow_b200"]
+    src = open(os.path.join(root, "setup.py")).read()
+    assert "native.build(" in src and "build_py" in src
