@@ -55,6 +55,8 @@ def parse():
     ap.add_argument("--baseline", default="auto", choices=["auto", "none", "ddp"],
                     help="same-box comparison arm run after the product arm (auto: DDP for --impl ours)")
     ap.add_argument("--ddp-compile", action="store_true", help="DDP arm under torch.compile (slow to start; stronger baseline)")
+    ap.add_argument("--close-barrier", default="step", choices=["step", "bucket"],
+                    help="one closing cross-rank barrier per step (default) or per bucket kernel (round-1 protocol)")
     ap.add_argument("--trace", action="store_true", help="eager steps with device-timed forward/backward/collective_tail phases")
     return ap.parse_args()
 
@@ -140,7 +142,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
                                                          "bucketBytes": int(args.bucket_mb * (1 << 20)),
                                                          "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
                                                          "cudaGraph": args.graph and not args.trace, "trace": args.trace,
-                                                         "fuseAllGather": args.fuse_ag,
+                                                         "fuseAllGather": args.fuse_ag, "closeBarrier": args.close_barrier,
                                                          "nvls": bool(args.nvls and world > 1)},
                                         rank=rank, world=world, device=device)
         step = engine.step
@@ -284,7 +286,7 @@ def main():
                "config": {**r["wcfg"], "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
                           "optimizer": args.optimizer, "bucket_mb": args.bucket_mb, "buckets": r["buckets"],
                           "cuda_graph": r["graph"], "nvls": bool(args.nvls and world > 1), "graph_prep_steps": r["prep"],
-                          "fuse_allgather": bool(args.fuse_ag),
+                          "fuse_allgather": bool(args.fuse_ag), "close_barrier": args.close_barrier,
                           "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
                           "loss": r["loss"]},
                "clocks": r["clocks"], "gpu_launches": r["launches"], "replicas_identical": r["replicas_identical"],

@@ -84,6 +84,7 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "trace": False,               # CUDA-event phase timers + NVTX ranges (forward / backward / collective tail); eager steps only
     "watchdogSeconds": 0.0,       # > 0: host thread reports a rank whose device-written step counter stops advancing
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
+    "closeBarrier": "step",       # "step": one closing cross-rank barrier per step; "bucket": one per bucket kernel (round 1)
     "debugPoison": False,         # race detector: NaN a bucket's weights the moment its last gradient is reported (tests)
 }
 
@@ -95,6 +96,7 @@ _VALID = {
     "dtype": {"bf16", "fp32"},
     "gradDtype": {"bf16", "fp32"},
     "backend": {"p2p", "nccl", "gloo"},
+    "closeBarrier": {"step", "bucket"},
 }
 
 

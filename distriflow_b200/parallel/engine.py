@@ -90,6 +90,9 @@ class DataParallelEngine:
                 self.fuse_allgather(w)
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.device)
+        self._close_per_step = self.backend == "p2p" and self.world > 1 and self.cfg["closeBarrier"] == "step"
+        if self.backend == "p2p" and self.device.type == "cuda":
+            _comm_sigs().dfb_sync_close_per_bucket(0 if self._close_per_step else 1)     # process-wide switch of the bucket kernels
         self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.backend == "p2p"
         self.tracer = None
         if self.cfg["trace"]:
@@ -282,6 +285,8 @@ class DataParallelEngine:
             for b in self.buckets:                             # anything not launched from a hook (unused params, overlap off)
                 if not getattr(b, "launched", False):
                     self._launch_bucket(b)
+            if self._close_per_step:
+                self._close_step()
             if self.device.type == "cuda":
                 torch.cuda.current_stream().wait_stream(self.comm_stream)
                 from ..ops import dense as _lin
@@ -345,6 +350,21 @@ class DataParallelEngine:
             self._launch_bucket_p2p(b)
         else:
             self._launch_bucket_torch(b)
+
+    def _close_step(self) -> None:
+        """The step's ONE closing barrier, behind the last bucket kernel on the side stream: when it completes every peer has
+        pushed all its refreshed slices into this rank's weight buffers (and stopped reading this rank's gradients)."""
+        from ..ops import _lib
+        from ..ops._lib import check, ptr
+        L = _comm_sigs()
+        graph = self._graph_mode
+        epoch = self._seq if graph else self._epoch
+        if epoch == 0:
+            return
+        with torch.cuda.stream(self.comm_stream):
+            check(L.dfb_step_close(self.heap.ptrs(0), self.rank, self.world, epoch, ptr(self._epoch_dev) if graph else None,
+                                   _lib.stream()), "dfb_step_close")
+        self._launches += 1
 
     def _launch_bucket_p2p(self, b: Bucket) -> None:
         from ..ops import _lib
@@ -616,6 +636,10 @@ def _comm_sigs():
         L.dfb_sync_nvls.argtypes = [c_void_p, c_void_p, P, P, c_void_p, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int,
                                     ctypes.c_uint, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int,
                                     ctypes.c_long, ctypes.c_long, c_void_p, c_void_p, c_void_p, c_void_p]
+        L.dfb_sync_close_per_bucket.restype = c_int
+        L.dfb_sync_close_per_bucket.argtypes = [c_int]
+        L.dfb_step_close.restype = c_int
+        L.dfb_step_close.argtypes = [P, c_int, c_int, ctypes.c_uint, c_void_p, c_void_p]
         L.dfb_allgather_push.restype = c_int
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int

@@ -119,6 +119,11 @@ int dfb_sync_rs_opt_ag_replayable(void* const* grads, void* const* params, void*
                                   float lr, float momentum, float beta1, float beta2, float eps, float weight_decay, int ctas,
                                   long nopush_lo, long nopush_hi, const unsigned* epoch_base, const int* step_ptr,
                                   const float* lr_ptr /* nullable: learning rate read on the device */, void* stream);
+/* 1 (default): every bucket kernel ends with its own cross-rank barrier; 0: bucket kernels skip it and the step is closed
+ * ONCE by dfb_step_close behind its last bucket kernel (federated_server.ts:92-116: mean -> update -> broadcast is one step).
+ * epoch_base nullable (device word added to `epoch` for CUDA-graph replay). */
+int dfb_sync_close_per_bucket(int on);
+int dfb_step_close(void* const* sig, int rank, int R, unsigned epoch, const unsigned* epoch_base, void* stream);
 int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
                        int ctas, void* stream);
 int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
