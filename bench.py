@@ -220,6 +220,12 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
             identical = all(int(c) == int(allcs[0]) for c in allcs)
         else:
             identical = True
+    async_counters = None
+    if impl == "ours" and args.mode == "async" and engine is not None:
+        engine.drain()
+        c = engine.counters()                      # this rank's shard: every gradient is counted once on every shard
+        async_counters = {"applied": int(c["applied"]), "dropped": int(c["dropped"]), "updates": int(c["version"]),
+                          "max_staleness_seen": int(c["max_staleness_seen"])}
     trace = None
     if args.trace and engine is not None and getattr(engine, "tracer", None) is not None:
         trace = engine.trace_summary()
@@ -229,7 +235,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     out = {"ms": float(t[0]), "e2e_ms": float(t[1]), "e2e": e2e, "loss": float(loss), "launches": int(launches),
            "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "graph": graph, "first_losses": first_losses,
-           "replicas_identical": identical, "trace": trace,
+           "replicas_identical": identical, "trace": trace, "async": async_counters,
            "buckets": len(engine.buckets) if engine is not None and hasattr(engine, "buckets") else None}
     close()
     del step, engine, model, dev
@@ -296,6 +302,11 @@ def main():
                           "d2h_bytes_per_step": r["e2e"][2], "ms_per_step": r["e2e_ms"] / args.steps}
         if r["trace"]:
             out["trace"] = r["trace"]
+        if r["async"]:
+            a = r["async"]
+            frac = a["applied"] / max(a["applied"] + a["dropped"], 1)
+            out["async"] = {**a, "applied_fraction": frac, "value_applied": value * frac,
+                            "note": "value counts every gradient computed; value_applied only those the staleness guard let through"}
         if base is not None and "error" not in base:
             bval = gb * args.steps / (base["ms"] / 1e3)
             out["vs_baseline"] = value / bval

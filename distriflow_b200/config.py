@@ -84,6 +84,9 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "trace": False,               # CUDA-event phase timers + NVTX ranges (forward / backward / collective tail); eager steps only
     "watchdogSeconds": 0.0,       # > 0: host thread reports a rank whose device-written step counter stops advancing
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)
+    "stalenessPolicy": "drop",    # async: "drop" a gradient older than maximumStaleness, or "scale" it by 1/(1+staleness) up to the bound
+    "versionCounts": "updates",   # async: a shard version = one optimizer update (all gradients that met in the accumulation
+                                  # buffer are ONE step on their sum) | "gradients": +1 per gradient (reference's literal rule)
     "closeBarrier": "step",       # "step": one closing cross-rank barrier per step; "bucket": one per bucket kernel (round 1)
     "debugPoison": False,         # race detector: NaN a bucket's weights the moment its last gradient is reported (tests)
 }
@@ -97,6 +100,7 @@ _VALID = {
     "gradDtype": {"bf16", "fp32"},
     "backend": {"p2p", "nccl", "gloo"},
     "closeBarrier": {"step", "bucket"},
+    "versionCounts": {"updates", "gradients"},
 }
 
 

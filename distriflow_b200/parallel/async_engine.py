@@ -39,7 +39,7 @@ class _Local:
 class AsyncShardState:
     def __init__(self, heaps: List[SymmetricHeap], ranks: List[int], world: int, n: int, grad_dtype, param_dtype, lr: float,
                  max_staleness: int, optimizer: str = "sgd", policy: str = "drop", cfg: Optional[Dict[str, Any]] = None,
-                 ctas: int = 32):
+                 ctas: int = 32, version_per_apply: bool = False):
         self.L = _comm_sigs()
         self.heaps, self.ranks, self.world = heaps, ranks, world
         self.n = _round_up(n, world * 64)
@@ -49,6 +49,10 @@ class AsyncShardState:
         self.cfg = cfg or {"momentum": 0.9, "beta1": 0.9, "beta2": 0.999, "eps": 1e-8, "weightDecay": 0.0}
         self.ctas = ctas
         self.steps = 0
+        # True: a shard's version counts optimizer UPDATES (all gradients that met in one accumulation buffer = one update);
+        # False: it counts gradients (the literal "every upload is a version" of asynchronousSGD_server.ts:95-108)
+        self.version_per_apply = bool(version_per_apply)
+        self.step_dev: Optional[torch.Tensor] = None          # device step counter (Adam under CUDA-graph replay)
         psz = torch.empty((), dtype=param_dtype).element_size()
         self.psz = psz
         self.loc: Dict[int, _Local] = {}
@@ -116,7 +120,7 @@ class AsyncShardState:
         check(self.L.dfb_async_apply(ptr(lo.acc0), ptr(lo.acc1), lo.heap.pad_ptr(r), ptr(lo.master), ptr(lo.m), ptr(lo.v),
                                      ptr(shard_view), ptr(lo.scratch), self.shard, dt(lo.params), _OPT[self.optimizer], self.lr,
                                      c["momentum"], c["beta1"], c["beta2"], c["eps"], c["weightDecay"], self.steps, self.ctas,
-                                     _lib.stream()), "dfb_async_apply")
+                                     ptr(self.step_dev), int(self.version_per_apply), _lib.stream()), "dfb_async_apply")
 
     def read_ctl(self, rank: Optional[int] = None) -> Dict[str, Any]:
         r = self._one(rank)
@@ -169,7 +173,8 @@ class AsyncEngine:
         heap = SymmetricHeap(npad * psz + 8 * (npad // world) + 65536, rank, world, group, self.device)
         self.state = AsyncShardState([heap], [rank], world, n, grad_dtype=self.grad_dtype, param_dtype=self.param_dtype,
                                      lr=float(self.cfg["learningRate"]), max_staleness=int(self.cfg["maximumStaleness"]),
-                                     optimizer=self.cfg["optimizer"], policy="drop", cfg=self.cfg)
+                                     optimizer=self.cfg["optimizer"], policy=self.cfg["stalenessPolicy"], cfg=self.cfg,
+                                     version_per_apply=self.cfg["versionCounts"] == "updates")
         flat = torch.zeros(self.state.n, device=self.device)
         for p, off in zip(self.params, self.offsets):
             flat[off:off + p.numel()] = p.data.reshape(-1).float()
@@ -195,13 +200,17 @@ class AsyncEngine:
         self.version = 0
         # whole-step CUDA graph (pull -> fit -> push -> apply): every argument of the async kernels is constant from step to
         # step (versions, buffer choice and the staleness decision live in device memory), except Adam's step count
-        self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.cfg["optimizer"] != "adam"
+        self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda"
+        if self._graph_mode and self.cfg["optimizer"] == "adam":
+            self.state.step_dev = torch.zeros(1, dtype=torch.int32, device=self.device)    # advanced by a captured add_
         self._graph, self._static_in, self._static_loss, self._warm, self._graph_native = None, None, None, 0, 0
         if world > 1:
             import torch.distributed as dist
             dist.barrier(group=group)
 
     def _step_body(self, *batch: Any) -> torch.Tensor:
+        if self.state.step_dev is not None:
+            self.state.step_dev.add_(1)
         self.state.pull()
         loss = self.loss_fn(self.model, *batch)
         loss.backward()

@@ -520,6 +520,8 @@ struct AsyncApplyArgs {
   void* param_shard;     // this rank's slice inside its own working-weight buffer (TP)
   uint32_t* scratch;     // [2] device scratch: {buffer to drain, count}
   long shard_elems;
+  const int* step_ptr;   // nullable: optimizer step count in device memory (Adam bias correction under CUDA-graph replay)
+  int version_per_apply; // 1: the shard version counts optimizer UPDATES (+1 per apply round), 0: gradients applied (+count)
   OptParams opt;
 };
 
@@ -546,14 +548,20 @@ __global__ void __launch_bounds__(512) async_apply_data_kernel(const AsyncApplyA
   const uint32_t cnt = a.scratch[1];
   if (cnt == 0) return;
   float* acc = a.scratch[0] ? a.acc1 : a.acc0;
+  OptParams opt = a.opt;
+  if (a.step_ptr != nullptr && opt.kind == OPT_ADAM) {
+    const float t = (float)max(*a.step_ptr, 1);
+    opt.bias_c1 = 1.f - powf(opt.beta1, t);
+    opt.bias_c2 = 1.f - powf(opt.beta2, t);
+  }
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < a.shard_elems; i += (long)gridDim.x * blockDim.x) {
     float g = acc[i];
     acc[i] = 0.f;
     float mm = a.m ? a.m[i] : 0.f, vv = a.v ? a.v[i] : 0.f;
-    float w = opt_step(a.master[i], g, &mm, &vv, a.opt);
+    float w = opt_step(a.master[i], g, &mm, &vv, opt);
     a.master[i] = w;
-    if (a.m && a.opt.kind != OPT_SGD) a.m[i] = mm;
-    if (a.v && a.opt.kind == OPT_ADAM) a.v[i] = vv;
+    if (a.m && opt.kind != OPT_SGD) a.m[i] = mm;
+    if (a.v && opt.kind == OPT_ADAM) a.v[i] = vv;
     reinterpret_cast<TP*>(a.param_shard)[i] = from_f32<TP>(w);
   }
 }
@@ -567,7 +575,10 @@ __global__ void async_apply_end_kernel(const AsyncApplyArgs a) {
   atomicExch_system(a.ctl + A_ARRIVED + b, 0u);
   atomicAdd_system(a.ctl + A_APPLIED, cnt);
   __threadfence_system();
-  atomicAdd_system(a.ctl + A_VERSION, cnt);             // publish last: a reader that sees the version sees the weights
+  // publish last: a reader that sees the version sees the weights.  All gradients that met in the buffer were applied as ONE
+  // optimizer step on their sum, i.e. one model update: `version_per_apply` counts it as one version, so `maximumStaleness`
+  // bounds the number of UPDATES a gradient may lag behind (with +count, 8 lock-step workers are 7 "versions" stale each).
+  atomicAdd_system(a.ctl + A_VERSION, a.version_per_apply ? 1u : cnt);
 }
 
 struct AsyncPullArgs {
@@ -925,8 +936,10 @@ DFB_API int dfb_async_push(const void* grad, void* const* acc0, void* const* acc
 
 DFB_API int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
                             unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum,
-                            float beta1, float beta2, float eps, float weight_decay, int step, int ctas, cudaStream_t stream) {
+                            float beta1, float beta2, float eps, float weight_decay, int step, int ctas, const int* step_ptr,
+                            int version_per_apply, cudaStream_t stream) {
   AsyncApplyArgs a;
+  a.step_ptr = step_ptr; a.version_per_apply = version_per_apply;
   a.acc0 = acc0; a.acc1 = acc1; a.ctl = ctl_pad + kAsyncBase; a.master = master; a.m = m; a.v = v; a.param_shard = param_shard;
   a.scratch = scratch; a.shard_elems = shard_elems;
   a.opt.kind = opt_kind; a.opt.lr = lr; a.opt.momentum = momentum; a.opt.beta1 = beta1; a.opt.beta2 = beta2; a.opt.eps = eps;

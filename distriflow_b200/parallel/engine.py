@@ -650,7 +650,7 @@ def _comm_sigs():
         L.dfb_async_apply.restype = c_int
         L.dfb_async_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       ctypes.c_long, c_int, c_int, c_float, c_float, c_float, c_float, c_float, c_float, c_int,
-                                      c_int, c_void_p]
+                                      c_int, c_void_p, c_int, c_void_p]
         L.dfb_async_pull.restype = c_int
         L.dfb_async_pull.argtypes = [P, P, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int, c_int, c_void_p]
         L.dfb_async_read_ctl.restype = c_int

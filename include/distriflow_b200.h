@@ -133,7 +133,9 @@ int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void*
                    int grad_dtype, int ctas, const unsigned* ticket, void* stream);
 int dfb_async_apply(float* acc0, float* acc1, unsigned* ctl_pad, float* master, float* m, float* v, void* param_shard,
                     unsigned* scratch, long shard_elems, int param_dtype, int opt_kind, float lr, float momentum, float beta1,
-                    float beta2, float eps, float weight_decay, int step, int ctas, void* stream);
+                    float beta2, float eps, float weight_decay, int step, int ctas,
+                    const int* step_ptr /* nullable: Adam step count on the device (graph replay) */,
+                    int version_per_apply /* 1: version counts optimizer updates, 0: gradients applied */, void* stream);
 int dfb_async_pull(void* const* params, void* const* sig, void* dst, unsigned* seen_version, long n_bytes, long shard_bytes,
                    int rank, int R, int ctas, void* stream);
 int dfb_async_read_ctl(const unsigned* ctl_pad, unsigned* host_out9, void* stream);
