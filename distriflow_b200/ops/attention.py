@@ -143,8 +143,13 @@ class _FlashAttention(torch.autograd.Function):
             do = do.to(q.dtype)
         dqkv = torch.empty_like(q)
         scratch = _bwd_scratch(q.device, (B, T, H, D), int(L.dfb_attn_bwd_scratch_bytes(B, T, H, D)))
-        check(L.dfb_attn_bwd(ptr(q), ptr(out), ptr(do), ptr(lse), ptr(dqkv), ptr(scratch), ctypes.c_size_t(scratch.numel()),
-                             B, T, H, D, stream()), "dfb_attn_bwd")
+        from .norm import FUSE_BIAS_GRAD
+        # the column sums of dqkv (= bias gradient of the QKV projection) come out of the same kernels: no pass over dqkv
+        dbias = torch.empty(3 * H * D, dtype=torch.float32, device=q.device) if FUSE_BIAS_GRAD else None
+        check(L.dfb_attn_bwd(ptr(q), ptr(out), ptr(do), ptr(lse), ptr(dqkv), ptr(dbias), ptr(scratch),
+                             ctypes.c_size_t(scratch.numel()), B, T, H, D, stream()), "dfb_attn_bwd")
+        if dbias is not None:
+            dqkv._dfb_colsum = dbias
         return dqkv, None
 
 
@@ -176,7 +181,7 @@ def _sigs():
         L.dfb_attn_bwd_scratch_bytes.restype = ctypes.c_size_t
         L.dfb_attn_bwd_scratch_bytes.argtypes = [c_int] * 4
         L.dfb_attn_bwd.restype = c_int
-        L.dfb_attn_bwd.argtypes = [c_void_p] * 6 + [ctypes.c_size_t, c_int, c_int, c_int, c_int, c_void_p]
+        L.dfb_attn_bwd.argtypes = [c_void_p] * 7 + [ctypes.c_size_t, c_int, c_int, c_int, c_int, c_void_p]
         L._dfb_attn_sigs = True
     return L
 

@@ -377,18 +377,37 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 }
 
 // dq_acc [B,T,H,64] fp32 -> dqkv[b,t,0,h,:] bf16, and the accumulator is cleared for the next call (it must start at zero).
+// A thread keeps ONE 8-column vector of the row and walks down the rows, so it can also sum its columns of dQ (the values as
+// stored) for the bias gradient of the QKV projection: `dbias` (nullable) fp32 [3*H*64], part [0, H*64) is added to.
 __global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long rows_bt,
-                                                              int H) {
-  const long vec_per_bt = (long)H * kAttD / 8;                 // 8 elements per thread
-  const long total = rows_bt * vec_per_bt;
-  for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
-    const long bt = i / vec_per_bt, c = i - bt * vec_per_bt;
+                                                              int H, float* __restrict__ dbias) {
+  const int vpr = H * kAttD / 8;                               // 8-element vectors per (b, t) row
+  const int rows_per_iter = blockDim.x / vpr;
+  const int c = threadIdx.x % vpr, rl = threadIdx.x / vpr;
+  if (rl >= rows_per_iter) return;
+  float sum[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+  for (long bt = (long)blockIdx.x * rows_per_iter + rl; bt < rows_bt; bt += (long)gridDim.x * rows_per_iter) {
     float4* src = reinterpret_cast<float4*>(dq_acc + bt * H * kAttD + c * 8);
     const float4 a = src[0], b = src[1];
     uint4 pk = {pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w)};
     *reinterpret_cast<uint4*>(dqkv + bt * 3 * H * kAttD + c * 8) = pk;
     src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
     src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (dbias != nullptr) {
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __bfloat1622float2(h2[j]);
+        sum[2 * j] += f.x;
+        sum[2 * j + 1] += f.y;
+      }
+    }
+  }
+  if (dbias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(dbias + c * 8 + j, sum[j]);
   }
 }
 
@@ -403,6 +422,7 @@ __device__ __forceinline__ void tma_reduce_add_4d(const void* tmap, const void* 
 struct AttnBwdParams {
   const float* lse;      // [B, H, T]
   const float* delta;    // [B, H, T]
+  float* dbias;          // nullable: fp32 [3*H*64], += column sums of dqkv (the bias gradient of the QKV projection)
   int B, T, H;
   int n_qt;
   float scale;           // 1 / sqrt(D)
@@ -677,6 +697,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
       fence_proxy_async_smem();
       named_bar_sync(1, 256);
+      if (p.dbias != nullptr) {
+        // column sums of the two bf16 tiles just staged (the values as stored): thread = (tile, half of the rows, column)
+        const int tile = ctid >> 7, rh = (ctid >> 6) & 1, col = ctid & 63;
+        const uint8_t* src8 = tile == 0 ? sP : sdS;
+        float acc = 0.f;
+#pragma unroll 8
+        for (int r0 = 0; r0 < 64; ++r0) {
+          const int rr = rh * 64 + r0;
+          const __nv_bfloat16 v = *reinterpret_cast<const __nv_bfloat16*>(src8 + rr * 128 + (((col >> 3) ^ (rr & 7)) << 4) + (col & 7) * 2);
+          acc += __bfloat162float(v);
+        }
+        atomicAdd(p.dbias + ((tile == 0 ? 2 : 1) * p.H + h) * kAttD + col, acc);
+      }
       if (ctid == 0) {
         tma_store_4d(&tmDQKV, sP, 0, kv0, 2 * p.H + h, b);      // dV
         tma_store_4d(&tmDQKV, sdS, 0, kv0, p.H + h, b);         // dK
@@ -746,8 +779,8 @@ DFB_API size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D) {
 
 // dqkv [B,T,3,H,64] bf16 (fully written).  `scratch` holds delta and the fp32 dQ accumulator; the accumulator part
 // (everything after the first round256(B*H*T*4) bytes) must be ZERO on entry and is zero again on return.
-DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv, void* scratch,
-                         size_t scratch_bytes, int B, int T, int H, int D, cudaStream_t stream) {
+DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv, float* dbias,
+                         void* scratch, size_t scratch_bytes, int B, int T, int H, int D, cudaStream_t stream) {
   DFB_REQUIRE(dfb_attn_supported(B, T, H, D), "attn_bwd: head dimension %d not supported (64 only)", D);
   DFB_REQUIRE(scratch != nullptr && scratch_bytes >= dfb_attn_bwd_scratch_bytes(B, T, H, D), "attn_bwd: scratch of %zu bytes required",
               dfb_attn_bwd_scratch_bytes(B, T, H, D));
@@ -766,7 +799,7 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
     if (encode_tmap(&tmDQ, dq_acc, 1, 4, dims, str, box, nullptr, 1)) return 4;
   }
   AttnBwdParams p;
-  p.lse = lse; p.delta = delta; p.B = B; p.T = T; p.H = H;
+  p.lse = lse; p.delta = delta; p.dbias = dbias; p.B = B; p.T = T; p.H = H;
   p.n_qt = ceil_div(T, kAttTile);
   p.scale = 1.f / sqrtf((float)D);
   p.scale_log2 = p.scale * kLog2e;
@@ -777,15 +810,18 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
     DFB_CUDA_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
     attr_done[dev & 63] = true;
   }
+  const int vpr = H * kAttD / 8;
+  DFB_REQUIRE(vpr <= 256, "attn_bwd: H * 64 = %d columns exceed the convert kernel's block (2048)", H * kAttD);
+  if (dbias != nullptr) DFB_CUDA_CHECK(cudaMemsetAsync(dbias, 0, (size_t)3 * H * kAttD * sizeof(float), stream));
   const long rows = (long)B * T * H;
   attn_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H);
   const long grid = (long)p.n_qt * B * H;
   attn_bwd_kernel<<<(unsigned)grid, kBwdThreads, kBwdSmem, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, p);
-  const long vecs = (long)B * T * H * kAttD / 8;
-  long blocks = (vecs + 255) / 256;
-  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
-  attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H);
+  const int cthreads = vpr * (256 / vpr);                      // whole rows per block iteration
+  long blocks = ((long)B * T + (256 / vpr) - 1) / (256 / vpr);
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  attn_dq_convert_kernel<<<(unsigned)blocks, cthreads, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H, dbias);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

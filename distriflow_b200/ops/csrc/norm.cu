@@ -83,16 +83,19 @@ __global__ void __launch_bounds__(128) add_ln_fwd_kernel(const T* __restrict__ x
 // are combined across the 4 warps through shared memory, then written to part[blockIdx.x][2][D].
 // All three row operands (dy, s, ds) are fetched up front as packed 16-byte vectors (9 loads in flight per lane at
 // D = 768) and unpacked twice, which keeps the register count low enough for 4 blocks per SM.
-template <typename T, int NV>
+template <typename T, int NV, bool kSum>
 __global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
                                                             const T* __restrict__ gamma, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, T* __restrict__ dx,
                                                             float* __restrict__ part, int rows, int D) {
   using V = Vec16<T>;
   constexpr int VN = V::kN;
-  extern __shared__ float sh[];              // [4 warps][2][D]
+  // kSum: a third partial, the column sums of dx.  dx is also the gradient of the residual branch `r` (s = x + r), i.e. of
+  // the Dense layer that produced r, so its column sums ARE that layer's bias gradient: no separate pass over dx (K4).
+  constexpr int kW = kSum ? 3 : 2;
+  extern __shared__ float sh[];              // [4 warps][kW][D]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float dg[NV][VN], db[NV][VN];
+  float dg[NV][VN], db[NV][VN], dxs[kSum ? NV : 1][VN];
   V gam[NV];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
@@ -103,6 +106,7 @@ __global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict_
     for (int j = 0; j < VN; ++j) {
       dg[i][j] = 0.f;
       db[i][j] = 0.f;
+      if (kSum) dxs[i][j] = 0.f;
     }
   }
   for (int row = blockIdx.x * 4 + warp; row < rows; row += gridDim.x * 4) {
@@ -146,6 +150,7 @@ __global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict_
           float val = rs * (b[i].get(j) * gam[i].get(j) - s1 - xhat * s2);
           if (ds != nullptr) val += r[i].get(j);
           o.set(j, val);
+          if (kSum) dxs[i][j] += o.get(j);             // the value as stored (rounded to T): equals a column sum over dx
         }
         *reinterpret_cast<uint4*>(dx + (long)row * D + c) = o.raw;
       }
@@ -157,39 +162,43 @@ __global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict_
     if (c < D) {
 #pragma unroll
       for (int j = 0; j < VN; ++j) {
-        sh[(warp * 2 + 0) * D + c + j] = dg[i][j];
-        sh[(warp * 2 + 1) * D + c + j] = db[i][j];
+        sh[(warp * kW + 0) * D + c + j] = dg[i][j];
+        sh[(warp * kW + 1) * D + c + j] = db[i][j];
+        if (kSum) sh[(warp * kW + 2) * D + c + j] = dxs[i][j];
       }
     }
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < 2 * D; c += 128) {
+  for (int c = threadIdx.x; c < kW * D; c += 128) {
     const int which = c / D, col = c - which * D;
     float t = 0.f;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) t += sh[(w * 2 + which) * D + col];
-    part[((long)blockIdx.x * 2 + which) * D + col] = t;
+    for (int w = 0; w < 4; ++w) t += sh[(w * kW + which) * D + col];
+    part[((long)blockIdx.x * kW + which) * D + col] = t;
   }
 }
 
 // out[which][col] = sum_b part[b][which][col]: 32 columns x 32 partial-groups per block, fixed order (deterministic).
 template <typename T>
 __global__ void __launch_bounds__(1024) ln_param_grad_reduce_kernel(const float* __restrict__ part, T* __restrict__ dgamma,
-                                                                    T* __restrict__ dbeta, int nblocks, int D) {
+                                                                    T* __restrict__ dbeta, float* __restrict__ dx_colsum, int nblocks,
+                                                                    int D) {
+  const int kW = dx_colsum != nullptr ? 3 : 2;          // partial kinds per block: dgamma, dbeta [, column sums of dx]
   __shared__ float sh[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
   float t = 0.f;
-  if (c < 2 * D)
-    for (int b = ty; b < nblocks; b += 32) t += part[(long)b * 2 * D + c];
+  if (c < kW * D)
+    for (int b = ty; b < nblocks; b += 32) t += part[(long)b * kW * D + c];
   sh[ty][tx] = t;
   __syncthreads();
-  if (ty == 0 && c < 2 * D) {
+  if (ty == 0 && c < kW * D) {
     float tot = 0.f;
 #pragma unroll
     for (int k = 0; k < 32; ++k) tot += sh[k][tx];
     const int which = c / D, col = c - which * D;
-    (which ? dbeta : dgamma)[col] = from_f32<T>(tot);
+    if (which == 2) dx_colsum[col] = tot;
+    else (which ? dbeta : dgamma)[col] = from_f32<T>(tot);
   }
 }
 
@@ -225,9 +234,9 @@ static int launch_ln_fwd(const void* x, const void* r, const void* gamma, const 
 }
 template <typename T, int NV>
 static int launch_ln_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
-                         void* dx, float* part, int nblocks, int rows, int D, cudaStream_t st) {
-  auto kern = add_ln_bwd_kernel<T, NV>;
-  const int smem = 4 * 2 * D * (int)sizeof(float);
+                         void* dx, float* part, int nblocks, int rows, int D, bool want_sum, cudaStream_t st) {
+  auto kern = want_sum ? add_ln_bwd_kernel<T, NV, true> : add_ln_bwd_kernel<T, NV, false>;
+  const int smem = 4 * (want_sum ? 3 : 2) * D * (int)sizeof(float);
   if (smem > 48 * 1024) DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   kern<<<nblocks, 128, smem, st>>>((const T*)dy, (const T*)ds, (const T*)s, (const T*)gamma, mean, rstd, (T*)dx, part, rows, D);
   DFB_CUDA_CHECK(cudaGetLastError());
@@ -264,11 +273,13 @@ DFB_API int dfb_layernorm_bwd_blocks(int rows) {
   return b < need ? b : need;
 }
 
-// dx = ds + LayerNorm-backward(dy); dgamma/dbeta in the parameter dtype.  `part` is fp32 scratch of
-// dfb_layernorm_bwd_blocks(rows) * 2 * D floats supplied by the caller.
+// dx = ds + LayerNorm-backward(dy); dgamma/dbeta in the parameter dtype.  `dx_colsum` (nullable, fp32 [D]): column sums of
+// dx, i.e. the bias gradient of the Dense layer whose output was the residual branch.  `part` is fp32 scratch of
+// dfb_layernorm_bwd_blocks(rows) * (dx_colsum ? 3 : 2) * D floats supplied by the caller.
 DFB_API int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean,
-                                  const float* rstd, void* dx, void* dgamma, void* dbeta, float* part, int rows, int D, int dtype,
-                                  cudaStream_t stream) {
+                                  const float* rstd, void* dx, void* dgamma, void* dbeta, float* dx_colsum, float* part, int rows,
+                                  int D, int dtype, cudaStream_t stream) {
+  const bool want_sum = dx_colsum != nullptr;
   DFB_REQUIRE(rows > 0 && D > 0, "layernorm_bwd: empty");
   const int vn = dtype == DT_BF16 ? 8 : 4;
   DFB_REQUIRE(dtype == DT_BF16 || dtype == DT_F32, "layernorm_bwd: dtype");
@@ -278,16 +289,17 @@ DFB_API int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s,
   int rc = 2;
 #define DFB_LN_BWD(NV)                                                                                                          \
   if (rc == 2 && nv <= NV)                                                                                                      \
-    rc = dtype == DT_BF16 ? launch_ln_bwd<__nv_bfloat16, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, stream)    \
-                          : launch_ln_bwd<float, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, stream);
+    rc = dtype == DT_BF16 ? launch_ln_bwd<__nv_bfloat16, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, want_sum, stream) \
+                          : launch_ln_bwd<float, NV>(dy, ds, s, gamma, mean, rstd, dx, part, nblocks, rows, D, want_sum, stream);
   DFB_LN_BWD(1) DFB_LN_BWD(2) DFB_LN_BWD(3) DFB_LN_BWD(4) DFB_LN_BWD(8)
 #undef DFB_LN_BWD
   if (rc) return rc;
   if (dtype == DT_BF16)
-    ln_param_grad_reduce_kernel<__nv_bfloat16><<<ceil_div(2 * D, 32), 1024, 0, stream>>>(part, (__nv_bfloat16*)dgamma,
-                                                                                         (__nv_bfloat16*)dbeta, nblocks, D);
+    ln_param_grad_reduce_kernel<__nv_bfloat16><<<ceil_div((want_sum ? 3 : 2) * D, 32), 1024, 0, stream>>>(
+        part, (__nv_bfloat16*)dgamma, (__nv_bfloat16*)dbeta, dx_colsum, nblocks, D);
   else
-    ln_param_grad_reduce_kernel<float><<<ceil_div(2 * D, 32), 1024, 0, stream>>>(part, (float*)dgamma, (float*)dbeta, nblocks, D);
+    ln_param_grad_reduce_kernel<float><<<ceil_div((want_sum ? 3 : 2) * D, 32), 1024, 0, stream>>>(part, (float*)dgamma, (float*)dbeta,
+                                                                                                 dx_colsum, nblocks, D);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -123,6 +123,15 @@ def gemm_aux(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int
     return out
 
 
+def take_colsum(dy: torch.Tensor, N: int) -> Optional[torch.Tensor]:
+    """Column sums of `dy` that its producer already computed (fp32 `[N]`), or None.  The producer (LayerNorm backward for
+    the residual branch, attention backward for the packed QKV gradient) hangs them on the gradient tensor it returns."""
+    cs = getattr(dy, "_dfb_colsum", None)
+    if cs is not None and cs.numel() == N and cs.device == dy.device:
+        return cs
+    return None
+
+
 def colsum(x2d: torch.Tensor) -> torch.Tensor:
     L = _lib.lib()
     M, N = x2d.shape
@@ -221,6 +230,7 @@ class _LinearFn(torch.autograd.Function):
         x2, w, saved_act = ctx.saved_tensors
         M, N, K = ctx.dims
         tr = ctx.transposed
+        pre_colsum = take_colsum(dy, N) if ctx.activation is None else None
         dy2 = dy.reshape(M, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
@@ -249,7 +259,7 @@ class _LinearFn(torch.autograd.Function):
                 dw = gemm(args["a"], args["b"], a_mn=True, b_mn=True, M=args["M"], N=args["N"], K=M, out_dtype=weight.dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             bias = ctx.bias_ref
-            db = colsum(dy2)
+            db = pre_colsum if pre_colsum is not None else colsum(dy2)
             sink = getattr(bias, "_dfb_grad_sink", None)
             if sink is not None:
                 sink.copy_(db)
@@ -304,6 +314,7 @@ class _MlpFn(torch.autograd.Function):
         w1, b1, w2, b2 = ctx.refs
         M, K = x2.shape
         H, N = w2d.shape
+        pre_colsum = take_colsum(dy, N)
         dy2 = dy.reshape(M, N)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
@@ -314,7 +325,7 @@ class _MlpFn(torch.autograd.Function):
         dpre = gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2)
         dx = gemm(dpre, w1d, a_mn=False, b_mn=False, M=M, N=K, K=H).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw2 = _wgrad(h, dy2, w2, H, N, M)
-        db2 = _deliver(b2, colsum(dy2)) if b2 is not None else None
+        db2 = _deliver(b2, pre_colsum if pre_colsum is not None else colsum(dy2)) if b2 is not None else None
         # fc1
         dw1 = _wgrad(x2, dpre, w1, K, H, M)
         db1 = _deliver(b1, colsum(dpre)) if b1 is not None else None

@@ -25,7 +25,7 @@ def _sigs():
         L.dfb_layernorm_bwd_blocks.restype = c_int
         L.dfb_layernorm_bwd_blocks.argtypes = [c_int]
         L.dfb_add_layernorm_bwd.restype = c_int
-        L.dfb_add_layernorm_bwd.argtypes = [c_void_p] * 10 + [c_int, c_int, c_int, c_void_p]
+        L.dfb_add_layernorm_bwd.argtypes = [c_void_p] * 11 + [c_int, c_int, c_int, c_void_p]
         L.dfb_permute_rows.restype = c_int
         L.dfb_permute_rows.argtypes = [c_void_p, c_void_p] + [c_int] * 4 + [ctypes.c_long] * 8 + [c_int, c_void_p]
         L.dfb_bn_partial_blocks.restype = c_int
@@ -38,6 +38,13 @@ def _sigs():
         L.dfb_bn_bwd.argtypes = [c_void_p] * 12 + [ctypes.c_long, c_int, c_int, c_int, c_int, c_void_p]
         L._dfb_norm_sigs = True
     return L
+
+
+import os as _os
+
+# bias gradients produced by the kernel that produces dY (LayerNorm backward, attention backward) instead of a separate
+# column-sum pass over dY; DFB_FUSE_BIAS_GRAD=0 restores the separate kernel for A/B runs
+FUSE_BIAS_GRAD = _os.environ.get("DFB_FUSE_BIAS_GRAD", "1") == "1"
 
 
 def _supported(x: torch.Tensor) -> bool:
@@ -86,13 +93,16 @@ class _AddLN(torch.autograd.Function):
         ds2 = ds.reshape(rows, D).contiguous() if ds is not None else None
         dx = torch.empty_like(s)
         nblocks = int(L.dfb_layernorm_bwd_blocks(rows))
-        part = torch.empty(nblocks * 2 * D, dtype=torch.float32, device=s.device)
+        # with a residual branch, dx is also the gradient of the Dense layer that produced the branch: its column sums are
+        # that layer's bias gradient, produced here for free and handed over on the tensor (`ops.dense.take_colsum`)
+        colsum = torch.empty(D, dtype=torch.float32, device=s.device) if (ctx.has_r and FUSE_BIAS_GRAD) else None
+        part = torch.empty(nblocks * (3 if colsum is not None else 2) * D, dtype=torch.float32, device=s.device)
         sg, sb = getattr(gamma, "_dfb_grad_sink", None), getattr(beta, "_dfb_grad_sink", None)
         direct = sg is not None and sb is not None and sg.dtype == s.dtype and sb.dtype == s.dtype
         dgamma = sg if direct else torch.empty(D, dtype=s.dtype, device=s.device)
         dbeta = sb if direct else torch.empty(D, dtype=s.dtype, device=s.device)
         check(L.dfb_add_layernorm_bwd(ptr(dy2), ptr(ds2), ptr(s), ptr(g), ptr(mean), ptr(rstd), ptr(dx), ptr(dgamma), ptr(dbeta),
-                                      ptr(part), rows, D, dt(s), stream()), "dfb_add_layernorm_bwd")
+                                      ptr(colsum), ptr(part), rows, D, dt(s), stream()), "dfb_add_layernorm_bwd")
         if direct:
             gamma._dfb_grad_ready()
             beta._dfb_grad_ready()
@@ -100,7 +110,12 @@ class _AddLN(torch.autograd.Function):
         else:
             dgamma, dbeta = dgamma.to(gamma.dtype), dbeta.to(beta.dtype)
         dxv = dx.view(ctx.shape)
-        return dxv, (dxv if ctx.has_r else None), dgamma, dbeta, None
+        if not ctx.has_r:
+            return dxv, None, dgamma, dbeta, None
+        dr = dx.view(ctx.shape)                     # a second view object for the branch: it carries the column sums
+        if colsum is not None:
+            dr._dfb_colsum = colsum
+        return dxv, dr, dgamma, dbeta, None
 
 
 def layer_norm_cuda(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float) -> torch.Tensor:

@@ -159,8 +159,9 @@ int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long ro
 int dfb_attn_supported(int B, int T, int H, int D);
 int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
 size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D);
-int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv, void* scratch,
-                 size_t scratch_bytes, int B, int T, int H, int D, void* stream);
+int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv,
+                 float* dbias /* nullable, fp32 [3*H*D]: receives the column sums of dqkv = bias gradient of the QKV projection */,
+                 void* scratch, size_t scratch_bytes, int B, int T, int H, int D, void* stream);
 
 /* ---- normalisation and layout kernels (no counterpart in the reference: its models are Dense / Conv2D / MaxPool) ------------
  * fused residual add + LayerNorm: s = x + r (r nullable), y = LN(s) * gamma + beta; mean / rstd: [rows] fp32 */
@@ -168,7 +169,9 @@ int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamma, const
                           float* rstd, int rows, int D, float eps, int dtype, void* stream);
 int dfb_layernorm_bwd_blocks(int rows);                     /* row blocks of the `part` scratch: 2 * D * blocks floats */
 int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
-                          void* dx, void* dgamma, void* dbeta, float* part, int rows, int D, int dtype, void* stream);
+                          void* dx, void* dgamma, void* dbeta,
+                          float* dx_colsum /* nullable, fp32 [D]: column sums of dx = bias gradient of the layer that fed the residual */,
+                          float* part /* blocks * (dx_colsum ? 3 : 2) * D floats */, int rows, int D, int dtype, void* stream);
 /* strided copy of rows of `row_bytes` (multiple of 16): src + sum(i_k * s_k) -> dst + sum(i_k * d_k), strides in bytes */
 int dfb_permute_rows(const void* src, void* dst, int n0, int n1, int n2, int n3, long s0, long s1, long s2, long s3, long d0,
                      long d1, long d2, long d3, int row_bytes, void* stream);

@@ -80,3 +80,33 @@ def test_gpt2_block_uses_the_native_attention_kernel():
     x = torch.randn(2, 128, 3 * 2 * 64, device=dev()).to(torch.bfloat16).requires_grad_(True)
     y = attention.causal_self_attention(x, 2)
     assert type(y.grad_fn).__name__ == "_FlashAttentionBackward"
+
+
+def test_attention_backward_emits_the_qkv_bias_gradient():
+    """`dbias` of dfb_attn_bwd = column sums of the packed dqkv it writes (bias gradient of the QKV projection, K4: bias-grad
+    in the producer), and the Dense backward picks it up from the gradient tensor instead of running a column-sum pass."""
+    import ctypes
+    from distriflow_b200.ops._lib import check, ptr, stream
+    from distriflow_b200.ops.attention import _bwd_scratch, _sigs
+    from distriflow_b200.ops.dense import take_colsum
+    L = _sigs()
+    B, H, T, D = 2, 3, 200, 64
+    qkv = torch.randn(B, T, 3 * H * D, device=dev()).to(torch.bfloat16)
+    do = torch.randn(B, T, H * D, device=dev()).to(torch.bfloat16)
+    out = torch.empty(B, T, H * D, device=dev(), dtype=torch.bfloat16)
+    lse = torch.empty(B, H, T, device=dev(), dtype=torch.float32)
+    check(L.dfb_attn_fwd(ptr(qkv), ptr(out), ptr(lse), B, T, H, D, stream()), "fwd")
+    dqkv = torch.empty_like(qkv)
+    dbias = torch.full((3 * H * D,), 7.0, device=dev())            # the entry point clears it itself
+    scratch = _bwd_scratch(dev(), (B, T, H, D), int(L.dfb_attn_bwd_scratch_bytes(B, T, H, D)))
+    for _ in range(2):
+        check(L.dfb_attn_bwd(ptr(qkv), ptr(out), ptr(do), ptr(lse), ptr(dqkv), ptr(dbias), ptr(scratch),
+                             ctypes.c_size_t(scratch.numel()), B, T, H, D, stream()), "bwd")
+    ref = dqkv.float().sum((0, 1))
+    assert float((dbias - ref).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
+    # through autograd the sums ride on the gradient tensor
+    x = qkv.clone().requires_grad_(True)
+    from distriflow_b200.ops.attention import _FlashAttention
+    _FlashAttention.apply(x, H).backward(do)
+    cs = take_colsum(x.grad, 3 * H * D)
+    assert cs is not None and float((cs - x.grad.float().sum((0, 1))).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3

@@ -321,6 +321,10 @@ def test_add_layer_norm(dtype, D, with_res):
         yr = F.layer_norm(sr, (D,), gr, br, 1e-5)
         torch.autograd.backward([sr, yr], [gs.float(), gy.float()])
         assert rel_err(s, sr) < 1e-2 and rel_err(r.grad, rr.grad) < 2e-2
+        # the branch gradient carries its own column sums (the bias gradient of the layer that produced the branch)
+        from distriflow_b200.ops.dense import take_colsum
+        cs = take_colsum(r.grad, D)
+        assert cs is not None and rel_err(cs, r.grad.float().reshape(-1, D).sum(0)) < (1e-5 if dtype == torch.float32 else 2e-3)
     else:
         yr = F.layer_norm(xr, (D,), gr, br, 1e-5)
         yr.backward(gy.float())
