@@ -381,33 +381,55 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // stored) for the bias gradient of the QKV projection: `dbias` (nullable) fp32 [3*H*64], part [0, H*64) is added to.
 __global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long rows_bt,
                                                               int H, float* __restrict__ dbias) {
+  __shared__ float sh_sum[2048];                               // [H*64] block-level column sums (H*64 <= 2048)
   const int vpr = H * kAttD / 8;                               // 8-element vectors per (b, t) row
-  const int rows_per_iter = blockDim.x / vpr;
+  const int rows_per_iter = blockDim.x / vpr;                  // blockDim is a multiple of vpr: a thread's columns never change
   const int c = threadIdx.x % vpr, rl = threadIdx.x / vpr;
-  if (rl >= rows_per_iter) return;
+  if (dbias != nullptr) {
+    for (int i = threadIdx.x; i < H * kAttD; i += blockDim.x) sh_sum[i] = 0.f;
+    __syncthreads();
+  }
   float sum[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) sum[j] = 0.f;
-  for (long bt = (long)blockIdx.x * rows_per_iter + rl; bt < rows_bt; bt += (long)gridDim.x * rows_per_iter) {
-    float4* src = reinterpret_cast<float4*>(dq_acc + bt * H * kAttD + c * 8);
-    const float4 a = src[0], b = src[1];
-    uint4 pk = {pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w)};
-    *reinterpret_cast<uint4*>(dqkv + bt * 3 * H * kAttD + c * 8) = pk;
-    src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-    src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (dbias != nullptr) {
-      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+  constexpr int U = 4;                                         // rows in flight per thread
+  const long step = (long)gridDim.x * rows_per_iter;
+  for (long bt0 = (long)blockIdx.x * rows_per_iter + rl; bt0 < rows_bt; bt0 += step * U) {
+    float4 a[U], b[U];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 f = __bfloat1622float2(h2[j]);
-        sum[2 * j] += f.x;
-        sum[2 * j + 1] += f.y;
+    for (int u = 0; u < U; ++u) {
+      const long bt = bt0 + u * step;
+      if (bt < rows_bt) {
+        const float4* src = reinterpret_cast<const float4*>(dq_acc + bt * H * kAttD + c * 8);
+        a[u] = src[0];
+        b[u] = src[1];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long bt = bt0 + u * step;
+      if (bt >= rows_bt) continue;
+      uint4 pk = {pack_bf16(a[u].x, a[u].y), pack_bf16(a[u].z, a[u].w), pack_bf16(b[u].x, b[u].y), pack_bf16(b[u].z, b[u].w)};
+      *reinterpret_cast<uint4*>(dqkv + bt * 3 * H * kAttD + c * 8) = pk;
+      float4* dst = reinterpret_cast<float4*>(dq_acc + bt * H * kAttD + c * 8);
+      dst[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+      dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dbias != nullptr) {
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = __bfloat1622float2(h2[j]);
+          sum[2 * j] += f.x;
+          sum[2 * j + 1] += f.y;
+        }
       }
     }
   }
-  if (dbias != nullptr) {
+  if (dbias != nullptr) {                                      // block-level sums first: one global atomic per column and block
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(dbias + c * 8 + j, sum[j]);
+    for (int j = 0; j < 8; ++j) atomicAdd(&sh_sum[c * 8 + j], sum[j]);
+    __syncthreads();
+    for (int i = threadIdx.x; i < H * kAttD; i += blockDim.x) atomicAdd(dbias + i, sh_sum[i]);
   }
 }
 
@@ -820,7 +842,7 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
   attn_bwd_kernel<<<(unsigned)grid, kBwdThreads, kBwdSmem, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, p);
   const int cthreads = vpr * (256 / vpr);                      // whole rows per block iteration
   long blocks = ((long)B * T + (256 / vpr) - 1) / (256 / vpr);
-  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
   attn_dq_convert_kernel<<<(unsigned)blocks, cthreads, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H, dbias);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(128) add_ln_fwd_kernel(const T* __restrict__ x
 // All three row operands (dy, s, ds) are fetched up front as packed 16-byte vectors (9 loads in flight per lane at
 // D = 768) and unpacked twice, which keeps the register count low enough for 4 blocks per SM.
 template <typename T, int NV, bool kSum>
-__global__ void __launch_bounds__(128, 4) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
+__global__ void __launch_bounds__(128, kSum ? 3 : 4) add_ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ ds, const T* __restrict__ s,
                                                             const T* __restrict__ gamma, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, T* __restrict__ dx,
                                                             float* __restrict__ part, int rows, int D) {
@@ -285,7 +285,8 @@ DFB_API int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s,
   DFB_REQUIRE(dtype == DT_BF16 || dtype == DT_F32, "layernorm_bwd: dtype");
   DFB_REQUIRE(D % vn == 0 && ln_nv(D, vn) <= kLnMaxVec, "layernorm_bwd: D=%d unsupported", D);
   const int nv = ln_nv(D, vn);
-  const int nblocks = dfb_layernorm_bwd_blocks(rows);
+  int nblocks = dfb_layernorm_bwd_blocks(rows);
+  if (want_sum && nblocks > num_sms() * 3) nblocks = num_sms() * 3;      // the column-sum variant keeps 3 blocks per SM resident: one wave
   int rc = 2;
 #define DFB_LN_BWD(NV)                                                                                                          \
   if (rc == 2 && nv <= NV)                                                                                                      \

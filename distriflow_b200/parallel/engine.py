@@ -90,7 +90,8 @@ class DataParallelEngine:
                 self.fuse_allgather(w)
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.device)
-        self._close_per_step = self.backend == "p2p" and self.world > 1 and self.cfg["closeBarrier"] == "step"
+        # one bucket: its own closing barrier is cheaper than a second launch (MNIST-sized models are one 32 KB bucket)
+        self._close_per_step = self.backend == "p2p" and self.world > 1 and self.cfg["closeBarrier"] == "step" and len(self.buckets) > 1
         if self.backend == "p2p" and self.device.type == "cuda":
             _comm_sigs().dfb_sync_close_per_bucket(0 if self._close_per_step else 1)     # process-wide switch of the bucket kernels
         self._graph_mode = bool(self.cfg["cudaGraph"]) and self.device.type == "cuda" and self.backend == "p2p"

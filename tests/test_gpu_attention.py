@@ -104,9 +104,21 @@ def test_attention_backward_emits_the_qkv_bias_gradient():
                              ctypes.c_size_t(scratch.numel()), B, T, H, D, stream()), "bwd")
     ref = dqkv.float().sum((0, 1))
     assert float((dbias - ref).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
-    # through autograd the sums ride on the gradient tensor
-    x = qkv.clone().requires_grad_(True)
+    # through autograd the sums ride on the gradient tensor that reaches the producer of qkv (the QKV Dense layer's backward)
     from distriflow_b200.ops.attention import _FlashAttention
-    _FlashAttention.apply(x, H).backward(do)
-    cs = take_colsum(x.grad, 3 * H * D)
-    assert cs is not None and float((cs - x.grad.float().sum((0, 1))).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
+    seen = []
+
+    class Probe(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, t):
+            return t.view_as(t)
+
+        @staticmethod
+        def backward(ctx, g):
+            seen.append(g)
+            return g
+
+    x = qkv.clone().requires_grad_(True)
+    _FlashAttention.apply(Probe.apply(x), H).backward(do)
+    cs = take_colsum(seen[0], 3 * H * D)
+    assert cs is not None and float((cs - seen[0].float().sum((0, 1))).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
