@@ -42,7 +42,11 @@ def parse():
     ap.add_argument("--mode", default="sync", choices=["sync", "async"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU micro-batch (0 = model default)")
     ap.add_argument("--seq", type=int, default=1024)
-    ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--bucket-mb", type=float, default=0.0,
+                    help="gradient bucket size; 0 = auto: 32 MB on one GPU, one bucket for the whole model (256 MB cap) on several "
+                         "(measured r2: at 2 and 8 GPUs one late bucket beats overlapped 32 MB buckets by 0.35-0.6 ms per GPT-2 "
+                         "step: the bucket kernels slow the backward GEMMs they overlap by more than the NVLink time they hide)")
+    ap.add_argument("--ddp-bucket-mb", type=float, default=32.0, help="bucket_cap_mb of the DDP comparison arm")
     ap.add_argument("--optimizer", default="adam")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--comm-ctas", type=int, default=148)
@@ -129,6 +133,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
 
     model, loss_fn, make_batch, bs, wcfg = build_workload(args, device, torch)
     engine = None
+    bucket_mb = args.bucket_mb if args.bucket_mb > 0 else (32.0 if world == 1 else 256.0)
     if impl == "ours":
         if args.mode == "async":
             from distriflow_b200.parallel.async_engine import AsyncEngine
@@ -139,7 +144,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
         else:
             from distriflow_b200.parallel.engine import DataParallelEngine
             engine = DataParallelEngine(model, loss_fn, {"optimizer": args.optimizer, "learningRate": 3e-4,
-                                                         "bucketBytes": int(args.bucket_mb * (1 << 20)),
+                                                         "bucketBytes": int(bucket_mb * (1 << 20)),
                                                          "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
                                                          "cudaGraph": args.graph and not args.trace, "trace": args.trace,
                                                          "fuseAllGather": args.fuse_ag, "closeBarrier": args.close_barrier,
@@ -149,7 +154,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
         close = lambda: None                                                      # noqa: E731
     else:   # PyTorch DDP + NCCL + cuBLAS baseline, identical model and schedule (bf16 weights and gradients)
         from baseline.ddp_baseline import make_ddp_step
-        step, close = make_ddp_step(model, loss_fn, args.optimizer, 3e-4, world, device, int(args.bucket_mb),
+        step, close = make_ddp_step(model, loss_fn, args.optimizer, 3e-4, world, device, int(args.ddp_bucket_mb),
                                     compile_model=args.ddp_compile)
 
     g = torch.Generator().manual_seed(host_seed + rank)
@@ -234,7 +239,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     out = {"ms": float(t[0]), "e2e_ms": float(t[1]), "e2e": e2e, "loss": float(loss), "launches": int(launches),
-           "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "graph": graph, "first_losses": first_losses,
+           "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "bucket_mb": bucket_mb if impl == "ours" else args.ddp_bucket_mb, "graph": graph, "first_losses": first_losses,
            "replicas_identical": identical, "trace": trace, "async": async_counters,
            "buckets": len(engine.buckets) if engine is not None and hasattr(engine, "buckets") else None}
     close()
@@ -290,7 +295,7 @@ def main():
                "dtype": "bf16" if args.model.startswith(("gpt2", "resnet")) else "fp32", "data": "synthetic",
                "impl": args.impl,
                "config": {**r["wcfg"], "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
-                          "optimizer": args.optimizer, "bucket_mb": args.bucket_mb, "buckets": r["buckets"],
+                          "optimizer": args.optimizer, "bucket_mb": r["bucket_mb"], "buckets": r["buckets"],
                           "cuda_graph": r["graph"], "nvls": bool(args.nvls and world > 1), "graph_prep_steps": r["prep"],
                           "fuse_allgather": bool(args.fuse_ag), "close_barrier": args.close_barrier,
                           "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
@@ -314,7 +319,7 @@ def main():
                                "same_box_same_process": True, "value": bval, "unit": "samples/s",
                                "ms_per_step": base["ms"] / args.steps, "clocks": base["clocks"],
                                "config": {**base["wcfg"], "global_batch": base["bs"] * world, "optimizer": args.optimizer,
-                                          "bucket_mb": args.bucket_mb, "steps": args.steps, "warmup": args.warmup + base["prep"]},
+                                          "bucket_mb": base["bucket_mb"], "steps": args.steps, "warmup": args.warmup + base["prep"]},
                                "loss": base["loss"]}
             if base["e2e"]:
                 out["baseline"]["e2e_value"] = gb * args.steps / (base["e2e_ms"] / 1e3)
