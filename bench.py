@@ -53,9 +53,14 @@ def parse():
     ap.add_argument("--reserve-sms", type=int, default=0)
     ap.add_argument("--graph", dest="graph", action="store_true", default=True,
                     help="capture the whole step into a CUDA graph after 3 eager steps (default)")
-    ap.add_argument("--nvls", action="store_true", help="reduce gradients / broadcast weights inside the NVSwitch (multicast heap)")
+    ap.add_argument("--nvls", nargs="?", const="on", default="auto", choices=["auto", "on", "off"],
+                    help="reduce gradients / broadcast weights inside the NVSwitch (multicast heap).  auto: on from 4 GPUs when every "
+                         "rank's device supports multicast objects (r2 at 8 GPUs: 34.70 vs 34.91 ms per step)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches every step")
-    ap.add_argument("--no-fuse-allgather", dest="fuse_ag", action="store_false", default=True)
+    ap.add_argument("--fuse-allgather", dest="fuse_ag", action="store_true", default=False,
+                    help="fuse the all-gather of the first Dense kernel into its forward GEMM (off by default: the r2 A/B at 8 GPUs "
+                         "measured 34.69 ms without it against 34.91 ms with it)")
+    ap.add_argument("--no-fuse-allgather", dest="fuse_ag", action="store_false")
     ap.add_argument("--baseline", default="auto", choices=["auto", "none", "ddp"],
                     help="same-box comparison arm run after the product arm (auto: DDP for --impl ours)")
     ap.add_argument("--ddp-compile", action="store_true", help="DDP arm under torch.compile (slow to start; stronger baseline)")
@@ -134,6 +139,15 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
     model, loss_fn, make_batch, bs, wcfg = build_workload(args, device, torch)
     engine = None
     bucket_mb = args.bucket_mb if args.bucket_mb > 0 else (32.0 if world == 1 else 256.0)
+    use_nvls = False
+    if impl == "ours" and world > 1 and args.mode == "sync" and args.nvls != "off" and args.model.startswith(("gpt2", "resnet")):
+        # (the in-switch path reduces bf16 gradients; the fp32 MNIST models stay on the P2P kernel)
+        from distriflow_b200.parallel.symm import multicast_supported
+        ok = torch.tensor([1 if multicast_supported(device) else 0], device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)                 # every rank takes the same decision
+        use_nvls = bool(int(ok)) and (args.nvls == "on" or world >= 4)
+        if args.nvls == "on" and not use_nvls:
+            raise SystemExit("--nvls on: a device of this job cannot join an NVSwitch multicast object")
     if impl == "ours":
         if args.mode == "async":
             from distriflow_b200.parallel.async_engine import AsyncEngine
@@ -148,7 +162,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
                                                          "commCtas": args.comm_ctas, "reserveSMs": args.reserve_sms,
                                                          "cudaGraph": args.graph and not args.trace, "trace": args.trace,
                                                          "fuseAllGather": args.fuse_ag, "closeBarrier": args.close_barrier,
-                                                         "nvls": bool(args.nvls and world > 1)},
+                                                         "nvls": use_nvls},
                                         rank=rank, world=world, device=device)
         step = engine.step
         close = lambda: None                                                      # noqa: E731
@@ -239,7 +253,7 @@ def run_arm(args, impl, rank, local_rank, world, device, host_seed):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     out = {"ms": float(t[0]), "e2e_ms": float(t[1]), "e2e": e2e, "loss": float(loss), "launches": int(launches),
-           "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "bucket_mb": bucket_mb if impl == "ours" else args.ddp_bucket_mb, "graph": graph, "first_losses": first_losses,
+           "clocks": clocks, "bs": bs, "wcfg": wcfg, "prep": prep, "nvls": use_nvls, "bucket_mb": bucket_mb if impl == "ours" else args.ddp_bucket_mb, "graph": graph, "first_losses": first_losses,
            "replicas_identical": identical, "trace": trace, "async": async_counters,
            "buckets": len(engine.buckets) if engine is not None and hasattr(engine, "buckets") else None}
     close()
@@ -296,7 +310,7 @@ def main():
                "impl": args.impl,
                "config": {**r["wcfg"], "global_batch": gb, "parallelism": f"dp{world}", "mode": args.mode,
                           "optimizer": args.optimizer, "bucket_mb": r["bucket_mb"], "buckets": r["buckets"],
-                          "cuda_graph": r["graph"], "nvls": bool(args.nvls and world > 1), "graph_prep_steps": r["prep"],
+                          "cuda_graph": r["graph"], "nvls": r["nvls"], "graph_prep_steps": r["prep"],
                           "fuse_allgather": bool(args.fuse_ag), "close_barrier": args.close_barrier,
                           "l2": "inputs+activations per step (GBs) far exceed the 126 MB L2; no explicit flush",
                           "loss": r["loss"]},

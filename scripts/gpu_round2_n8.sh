@@ -16,7 +16,7 @@ if [ "${TESTS:-1}" = "1" ]; then
 fi
 run gpt2_default --steps 20 --warmup 5
 run gpt2_trace --steps 10 --warmup 3 --trace --baseline none --no-e2e
-run gpt2_nvls --steps 20 --warmup 5 --nvls --baseline none --no-e2e
+run gpt2_nvls --steps 20 --warmup 5 --nvls on --baseline none --no-e2e
 run gpt2_bucketclose --steps 20 --warmup 5 --close-barrier bucket --baseline none --no-e2e
 run gpt2_nofuseag --steps 20 --warmup 5 --no-fuse-allgather --baseline none --no-e2e
 for mb in 4 16 64; do run gpt2_bucket${mb} --steps 15 --warmup 3 --bucket-mb $mb --baseline none --no-e2e; done
