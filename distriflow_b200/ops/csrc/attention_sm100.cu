@@ -42,8 +42,10 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 // One 128-byte row of a SWIZZLE_128B tile: eight 16-byte pieces, piece j of row r lives at ((j ^ (r & 7)) << 4).
+// (st.shared on a 32-bit shared-window address: as a generic store the same line showed up as ST.E.128 with "lg" stalls)
 __device__ __forceinline__ void st_swizzled_row_piece(uint8_t* tile, int row, int piece, uint4 q) {
-  *reinterpret_cast<uint4*>(tile + row * 128 + ((piece ^ (row & 7)) << 4)) = q;
+  const uint32_t addr = smem_u32(tile) + row * 128 + ((piece ^ (row & 7)) << 4);
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(q.x), "r"(q.y), "r"(q.z), "r"(q.w) : "memory");
 }
 
 // ============================================================================================== forward
@@ -451,36 +453,47 @@ struct AttnBwdParams {
   float scale_log2;      // scale * log2(e)
 };
 
-// P and dS for one query row and one half (64 key columns) of the tile: P = exp2(S*c - lse*log2e), dS = P (dP - delta) / sqrt(D).
+// P and dS for one query row and one half (64 key columns) of the tile, in two passes so that each shared-memory tile is
+// written as late as its previous reader allows:
+//   pass A   P  = exp2(S*c - lse*log2e)            -> sP   (first store waits for dV of the previous tile: `p_free`)
+//   pass B   dS = P (dP - delta) / sqrt(D)         -> sdS  (first store waits for dQ, dK of the previous tile: `ds_free`)
 template <bool kDiag>
 __device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t tmem_dp_lane, uint8_t* pblk, uint8_t* dsblk, int row,
-                                                 int half, float lse2, float dl, float scale, float scale_log2, uint64_t* smem_free,
-                                                 uint32_t smem_free_parity, bool wait_free) {
-#pragma unroll
-  for (int ch = 0; ch < 2; ++ch) {
-    const int col0 = half * 64 + ch * 32;
-    uint32_t rs[32], rp[32];
-    tmem_ld_32x32(tmem_s_lane + col0, rs);
-    tmem_ld_32x32(tmem_dp_lane + col0, rp);
+                                                 int half, float lse2, float dl, float scale, float scale_log2, uint64_t* p_free,
+                                                 uint64_t* ds_free, uint32_t free_parity, bool wait_free) {
+  const int col0 = half * 64;
+  float pv[64];
+  {
+    uint32_t rs[64];
+    tmem_ld_32x32(tmem_s_lane + col0, *reinterpret_cast<uint32_t(*)[32]>(&rs[0]));
+    tmem_ld_32x32(tmem_s_lane + col0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rs[32]));
     tmem_ld_wait();
 #pragma unroll
-    for (int q4 = 0; q4 < 4; ++q4) {
-      float pv[8], dv[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int i = 8 * q4 + e;
-        float pe = exp2f(fmaf(__uint_as_float(rs[i]), scale_log2, -lse2));
-        if (kDiag && col0 + i > row) pe = 0.f;
-        pv[e] = pe;
-        dv[e] = pe * (__uint_as_float(rp[i]) - dl) * scale;
-      }
-      uint4 pk = {pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7])};
-      uint4 dk = {pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7])};
-      // first store of the tile: the previous tile's dV / dK products must have finished reading P and dS
-      if (ch == 0 && q4 == 0 && wait_free) mbar_wait(smem_free, smem_free_parity);
-      st_swizzled_row_piece(pblk, row, ch * 4 + q4, pk);
-      st_swizzled_row_piece(dsblk, row, ch * 4 + q4, dk);
+    for (int i = 0; i < 64; ++i) {
+      float pe = exp2f(fmaf(__uint_as_float(rs[i]), scale_log2, -lse2));
+      if (kDiag && col0 + i > row) pe = 0.f;
+      pv[i] = pe;
     }
+  }
+  uint32_t rp[64];                                   // dP: in flight while P is packed and stored
+  tmem_ld_32x32(tmem_dp_lane + col0, *reinterpret_cast<uint32_t(*)[32]>(&rp[0]));
+  tmem_ld_32x32(tmem_dp_lane + col0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rp[32]));
+  if (wait_free) mbar_wait(p_free, free_parity);
+#pragma unroll
+  for (int q8 = 0; q8 < 8; ++q8) {
+    uint4 pk = {pack_bf16(pv[8 * q8 + 0], pv[8 * q8 + 1]), pack_bf16(pv[8 * q8 + 2], pv[8 * q8 + 3]),
+                pack_bf16(pv[8 * q8 + 4], pv[8 * q8 + 5]), pack_bf16(pv[8 * q8 + 6], pv[8 * q8 + 7])};
+    st_swizzled_row_piece(pblk, row, q8, pk);
+  }
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 64; ++i) pv[i] = pv[i] * (__uint_as_float(rp[i]) - dl) * scale;
+  if (wait_free) mbar_wait(ds_free, free_parity);
+#pragma unroll
+  for (int q8 = 0; q8 < 8; ++q8) {
+    uint4 dk = {pack_bf16(pv[8 * q8 + 0], pv[8 * q8 + 1]), pack_bf16(pv[8 * q8 + 2], pv[8 * q8 + 3]),
+                pack_bf16(pv[8 * q8 + 4], pv[8 * q8 + 5]), pack_bf16(pv[8 * q8 + 6], pv[8 * q8 + 7])};
+    st_swizzled_row_piece(dsblk, row, q8, dk);
   }
 }
 
@@ -521,8 +534,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint64_t* dq_full = bars + 7;
   uint64_t* dq_empty = bars + 8;
   uint64_t* dkv_full = bars + 9;
-  uint64_t* pds_free = bars + 10;     // dV / dK of the tile have read P and dS: the shared-memory tiles may be rewritten
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* p_free = bars + 10;       // dV of the tile has read P: sP may be rewritten
+  uint64_t* ds_free = bars + 11;      // dQ and dK of the tile have read dS: sdS may be rewritten
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -550,7 +564,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 8);
     mbar_init(dkv_full, 1);
-    mbar_init(pds_free, 1);
+    mbar_init(p_free, 1);
+    mbar_init(ds_free, 1);
     fence_mbar_init();
   }
   if (warp_idx == 1) tmem_alloc<kBwdTmemCols>(tmem_ptr);
@@ -590,10 +605,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
       const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
       const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
-      // Issue order per query tile i (everything the compute warps wait for comes first):
-      //   [P_i, dS_i ready]  dQ_i  ->  S_{i+1}, dP_{i+1}  ->  dV += P_i^T dO_i, dK += dS_i^T Q_i
-      // so the dQ drain overlaps S/dP of the next tile and the next softmax overlaps dV/dK of this one (r2 ncu: with dV, dK
-      // first the compute warps spent 1700 cycles per tile waiting for dQ and 900 for the next S/dP).
+      // Issue order per query tile i, software-pipelined against the compute warps (who, after publishing P_i / dS_i, drain
+      // dQ_{i-1} and then start on S_{i+1} / dP_{i+1}):
+      //   [P_i, dS_i ready]  S_{i+1}, dP_{i+1}  ->  dV += P_i^T dO_i  (P free)  ->  [dQ_{i-1} drained]  dQ_i = dS_i K
+      //                      ->  dK += dS_i^T Q_i  (dS free, Q_i / dO_i stage free)
+      // r2 ncu: with dQ drained right after its own tile the compute warps waited 15 % of their time for the dQ product,
+      // and a tile took 5300 cycles against 1280 cycles of tensor-core work.
       auto issue_sdp = [&](int it) {
         const int st = it & 1;
         mbar_wait(&qdo_full[st], (it >> 1) & 1);
@@ -614,21 +631,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), kAttTileBytes, 1024);
         const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
         mbar_wait_backoff(pds_ready, ph, 32);     // P_i, dS_i written; the compute warps are done with S_i / dP_i in TMEM
-        if (it > 0) mbar_wait(dq_empty, ph ^ 1);  // the compute warps have taken dQ_{i-1} out of TMEM
+        if (it + 1 < n_it) issue_sdp(it + 1);
         tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)         // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
+          umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        umma_commit(p_free);
+        if (it > 0) {
+          mbar_wait(dq_empty, ph ^ 1);      // the compute warps have taken dQ_{i-1} out of TMEM
+          tc_fence_after();
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k)         // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
           umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
         umma_commit(dq_full);
-        if (it + 1 < n_it) issue_sdp(it + 1);
-#pragma unroll
-        for (int k = 0; k < 8; ++k)         // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
-          umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
         for (int k = 0; k < 8; ++k)         // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
           umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        umma_commit(ds_free);
         umma_commit(&qdo_empty[st]);
-        umma_commit(pds_free);
       }
       umma_commit(dkv_full);
     }
@@ -639,17 +660,44 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const int ctid = threadIdx.x - 64;                          // 0..255
-    // row statistics of the NEXT query tile are fetched while the current one is processed (the loads were 1200 exposed
-    // cycles per tile when issued at the top of the tile)
+    // dQ_t: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator
+    auto drain_dq = [&](int t) {
+      mbar_wait(dq_full, t & 1);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_dq + lane_sel + half * 32, r);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_empty);
+      if (ctid == 0) tma_store_wait_read<0>();                  // the previous reduce has finished reading the staging buffer
+      named_bar_sync(1, 256);
+      uint8_t* blk = sdQ + half * kAttTileBytes;
+#pragma unroll
+      for (int q8 = 0; q8 < 8; ++q8) {
+        uint4 pk = {r[4 * q8 + 0], r[4 * q8 + 1], r[4 * q8 + 2], r[4 * q8 + 3]};
+        st_swizzled_row_piece(blk, row, q8, pk);
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 256);
+      if (ctid == 0) {
+        const int q0 = (jt + t) * kAttTile;
+        tma_reduce_add_4d(&tmDQ, sdQ, 0, q0, h, b);
+        tma_reduce_add_4d(&tmDQ, sdQ + kAttTileBytes, 32, q0, h, b);
+        tma_store_commit();
+      }
+    };
+    // row statistics of the NEXT query tile are fetched while the current one is processed
     float lse_nx = 0.f, dl_nx = 0.f;
     if (kv0 + row < p.T) {                                      // first query tile = the diagonal one: q0 = kv0
       lse_nx = __ldg(p.lse + (size_t)bh * p.T + kv0 + row);
       dl_nx = __ldg(p.delta + (size_t)bh * p.T + kv0 + row);
     }
+    uint8_t* pblk = sP + half * kAttTileBytes;
+    uint8_t* dsblk = sdS + half * kAttTileBytes;
     for (int it = 0; it < n_it; ++it) {
       const uint32_t ph = it & 1;
       const int q0 = (jt + it) * kAttTile;
-      const bool diag = (it == 0);
       const float lse2 = lse_nx * kLog2e, dl = dl_nx;
       lse_nx = 0.f;
       dl_nx = 0.f;
@@ -659,44 +707,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
       mbar_wait(sdp_full, ph);
       tc_fence_after();
-      uint8_t* pblk = sP + half * kAttTileBytes;
-      uint8_t* dsblk = sdS + half * kAttTileBytes;
-      if (diag) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
-                                       pds_free, ph ^ 1, it > 0);
+      if (it == 0) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
+                                          p_free, ds_free, ph ^ 1, false);
       else bwd_softmax_half<false>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
-                                   pds_free, ph ^ 1, it > 0);
+                                   p_free, ds_free, ph ^ 1, true);
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_ready);
-
-      // dQ_i: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator
-      mbar_wait(dq_full, ph);
-      tc_fence_after();
-      {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_dq + lane_sel + half * 32, r);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(dq_empty);
-        if (ctid == 0) tma_store_wait_read<0>();                // the previous reduce has finished reading the staging buffer
-        named_bar_sync(1, 256);
-        uint8_t* blk = sdQ + half * kAttTileBytes;
-#pragma unroll
-        for (int q8 = 0; q8 < 8; ++q8) {
-          uint4 pk = {r[4 * q8 + 0], r[4 * q8 + 1], r[4 * q8 + 2], r[4 * q8 + 3]};
-          st_swizzled_row_piece(blk, row, q8, pk);
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 256);
-        if (ctid == 0) {
-          tma_reduce_add_4d(&tmDQ, sdQ, 0, q0, h, b);
-          tma_reduce_add_4d(&tmDQ, sdQ + kAttTileBytes, 32, q0, h, b);
-          tma_store_commit();
-        }
-      }
+      if (it > 0) drain_dq(it - 1);           // its product finished while this tile's P / dS were computed
     }
+    drain_dq(n_it - 1);
     // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) -> bf16 -> TMA store into dqkv
     mbar_wait(dkv_full, 0);
     tc_fence_after();
