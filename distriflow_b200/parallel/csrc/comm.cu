@@ -58,7 +58,14 @@ __device__ __forceinline__ void red_add_v4_f32_sys(float* p, float a, float b, f
 // Signal pad layout (uint32 words) inside every rank's symmetric heap:
 //   [0, 8)    arrive-in  flags, one per source rank      [8, 16)   arrive-out flags
 //   [16]      local block counter                        [32, ...) async / work-queue words (see below)
-constexpr int kSigIn = 0, kSigOut = 8, kSigBlocks = 16;
+//   [17]      barrier time-out record: 1 + the rank that never arrived (0 = healthy)      [18] generation it was waited for
+constexpr int kSigIn = 0, kSigOut = 8, kSigBlocks = 16, kSigDead = 17, kSigDeadEpoch = 18;
+
+// Barrier waits are bounded: a peer that died (or never launched its kernel) must not leave every other GPU spinning inside a
+// kernel for ever, where not even the host watchdog can do more than print.  After `g_barrier_timeout_cycles` SM cycles the
+// waiter records WHO it was waiting for in its own signal pad and carries on; the step's result is garbage, but the kernel
+// ends, the stream drains and the host (`dfb_barrier_failures`, the engine's watchdog) can name the dead rank and stop.
+__device__ unsigned long long g_barrier_timeout_cycles = 40000000000ull;       // ~20 s at 2 GHz; dfb_set_barrier_timeout_us
 
 // Every block waits until all ranks have published `epoch` in this rank's `which` flags; block 0 publishes ours.
 __device__ __forceinline__ void rank_barrier(const PeerPtrs& sig, int rank, int R, int which, uint32_t epoch, bool do_signal) {
@@ -67,8 +74,17 @@ __device__ __forceinline__ void rank_barrier(const PeerPtrs& sig, int rank, int 
     st_release_sys(reinterpret_cast<uint32_t*>(sig.p[threadIdx.x]) + which + rank, epoch);
   }
   if (threadIdx.x < R) {
-    const uint32_t* mine = reinterpret_cast<const uint32_t*>(sig.p[rank]) + which + threadIdx.x;
+    uint32_t* pad = reinterpret_cast<uint32_t*>(sig.p[rank]);
+    const uint32_t* mine = pad + which + threadIdx.x;
+    const long long t0 = clock64();
+    const unsigned long long limit = g_barrier_timeout_cycles;
+    uint32_t polls = 0;
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((++polls & 1023u) == 0 && (unsigned long long)(clock64() - t0) > limit) {
+        pad[kSigDeadEpoch] = epoch;
+        st_release_sys(pad + kSigDead, 1u + threadIdx.x);        // rank threadIdx.x never published this generation
+        break;
+      }
     }
   }
   __syncthreads();
@@ -405,6 +421,8 @@ __global__ void step_close_kernel(PeerPtrs sig, int rank, int R, uint32_t epoch,
   __threadfence_system();
   rank_barrier(sig, rank, R, kSigOut, epoch, true);
 }
+
+__global__ void set_barrier_timeout_kernel(unsigned long long cycles) { g_barrier_timeout_cycles = cycles; }
 
 // Cross-rank barrier on its own (bootstrap, tests, end of async runs).
 __global__ void barrier_kernel(PeerPtrs sig, int rank, int R, uint32_t epoch) { rank_barrier(sig, rank, R, kSigIn, epoch, true); }
@@ -898,6 +916,26 @@ DFB_API int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes
   int grid = ctas > 0 ? ctas : 32;
   allgather_push_kernel<<<grid, 512, 0, stream>>>(a);
   DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Bound of every in-kernel cross-rank wait on the current device, in microseconds of SM time at the device's nominal clock.
+DFB_API int dfb_set_barrier_timeout_us(long long us, cudaStream_t stream) {
+  int dev = 0, khz = 0;
+  DFB_CUDA_CHECK(cudaGetDevice(&dev));
+  DFB_CUDA_CHECK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+  if (khz <= 0) khz = 1900000;
+  const unsigned long long cycles = (unsigned long long)us * (unsigned long long)khz / 1000ull;
+  DFB_REQUIRE(us > 0 && cycles > 0, "set_barrier_timeout: non-positive time-out");
+  set_barrier_timeout_kernel<<<1, 1, 0, stream>>>(cycles);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+// out2[0] = 0 (healthy) or 1 + the rank a barrier of this device gave up on, out2[1] = the generation; clears the record.
+DFB_API int dfb_barrier_failures(unsigned* pad, unsigned* host_out2, cudaStream_t stream) {
+  DFB_CUDA_CHECK(cudaMemcpyAsync(host_out2, pad + kSigDead, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  DFB_CUDA_CHECK(cudaStreamSynchronize(stream));
+  DFB_CUDA_CHECK(cudaMemsetAsync(pad + kSigDead, 0, 2 * sizeof(unsigned), stream));
   return 0;
 }
 

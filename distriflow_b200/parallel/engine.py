@@ -146,6 +146,8 @@ class DataParallelEngine:
             self.heap = heap or SymmetricHeap(total + 4096, self.rank, self.world, self.group, self.device, multicast=self.nvls)
             if self.nvls and not self.heap.mc_base:
                 raise RuntimeError("nvls: the supplied symmetric heap has no multicast mapping")
+            if self.world > 1 and self.device.type == "cuda":
+                self.heap.set_barrier_timeout(float(self.cfg["barrierTimeoutSeconds"]))
         for b in buckets:
             flat32 = torch.zeros(b.numel, dtype=torch.float32, device=self.device)
             for p, off in zip(b.params, b.offsets):
@@ -590,13 +592,30 @@ class DataParallelEngine:
         def on_stall(last: int, secs: float) -> None:
             self.stall_reports.append((last, secs))
             import sys
-            print(f"[distriflow_b200] rank {self.rank}: no step completed for {secs:.1f} s (last finished step {last}); "
-                  f"a peer may be down or a collective is stuck", file=sys.stderr, flush=True)
+            lost = self.peer_failure(_side=True)
+            who = f"rank {lost[0]} never reached barrier generation {lost[1]}" if lost else "a peer may be down or a collective is stuck"
+            print(f"[distriflow_b200] rank {self.rank}: no step completed for {secs:.1f} s (last finished step {last}); {who}",
+                  file=sys.stderr, flush=True)
             for cb in self.stallCallbacks:
                 cb(self.rank, last, secs)
 
         self.stallCallbacks: List[Callable[[int, int, float], None]] = []
         self.watchdog = ProgressWatchdog(read, seconds, on_stall).start()
+
+    def peer_failure(self, _side: bool = False) -> Optional[Tuple[int, int]]:
+        """(rank, barrier generation) when one of this rank's kernels gave up waiting for a peer (`barrierTimeoutSeconds`)
+        since the last call, else None.  The weights of such a step are not trustworthy: stop, or restore a checkpoint.
+        Reference: the server drops a worker whose socket closes (abstract_server.ts:118-126); between GPUs there is no
+        socket to close, so the waiter's time-out is the detector."""
+        if self.heap is None or self.device.type != "cuda" or self.world == 1:
+            return None
+        if _side:
+            if getattr(self, "_health_stream", None) is None:
+                self._health_stream = torch.cuda.Stream(device=self.device)
+            self.lost_peer = self.heap.barrier_failure(self._health_stream) or getattr(self, "lost_peer", None)
+            return self.lost_peer
+        self.lost_peer = self.heap.barrier_failure() or getattr(self, "lost_peer", None)
+        return self.lost_peer
 
     def on_stall(self, cb: Callable[[int, int, float], None]) -> None:
         """`cb(rank, last_finished_step, seconds)` from the watchdog thread (needs `watchdogSeconds > 0`)."""
@@ -645,6 +664,10 @@ def _comm_sigs():
         L.dfb_allgather_push.argtypes = [P, P, ctypes.c_long, ctypes.c_long, c_int, c_int, ctypes.c_uint, c_int, c_void_p]
         L.dfb_rank_barrier.restype = c_int
         L.dfb_rank_barrier.argtypes = [P, c_int, c_int, ctypes.c_uint, c_void_p]
+        L.dfb_set_barrier_timeout_us.restype = c_int
+        L.dfb_set_barrier_timeout_us.argtypes = [ctypes.c_int64, c_void_p]
+        L.dfb_barrier_failures.restype = c_int
+        L.dfb_barrier_failures.argtypes = [c_void_p, c_void_p, c_void_p]
         L.dfb_async_push.restype = c_int
         L.dfb_async_push.argtypes = [c_void_p, P, P, P, c_void_p, c_void_p, ctypes.c_long, ctypes.c_long, c_int, c_int, c_int,
                                      c_float, c_int, c_int, c_int, c_void_p, c_void_p]

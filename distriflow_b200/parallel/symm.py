@@ -250,6 +250,31 @@ class SymmetricHeap:
     def pad(self) -> torch.Tensor:
         return self.view(0, (PAD_BYTES // 4,), torch.int32)
 
+    # ---- failure detection ----------------------------------------------------------------------
+    def set_barrier_timeout(self, seconds: float) -> None:
+        """Bound of every in-kernel wait for a peer on this heap's device (abstract_client.ts:12-13: the reference's
+        connect / upload time-outs).  A kernel whose peer stays silent that long records the peer and finishes."""
+        from ..ops._lib import lib
+        L = lib()
+        L.dfb_set_barrier_timeout_us.restype = c_int
+        L.dfb_set_barrier_timeout_us.argtypes = [ctypes.c_int64, c_void_p]
+        with torch.cuda.device(self.device):
+            check(L.dfb_set_barrier_timeout_us(int(seconds * 1e6), c_void_p(torch.cuda.current_stream(self.device).cuda_stream)),
+                  "dfb_set_barrier_timeout_us")
+
+    def barrier_failure(self, stream: Optional["torch.cuda.Stream"] = None) -> Optional[tuple]:
+        """(silent rank, barrier generation) if a kernel of this rank gave up waiting since the last call, else None.
+        `stream`: pass a side stream to ask while the main stream is still busy (the watchdog thread does)."""
+        from ..ops._lib import lib
+        L = lib()
+        L.dfb_barrier_failures.restype = c_int
+        L.dfb_barrier_failures.argtypes = [c_void_p, c_void_p, c_void_p]
+        out = (ctypes.c_uint * 2)()
+        st = stream or torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            check(L.dfb_barrier_failures(self.pad_ptr(), out, c_void_p(st.cuda_stream)), "dfb_barrier_failures")
+        return (int(out[0]) - 1, int(out[1])) if out[0] else None
+
     def pad_ptr(self, rank: Optional[int] = None) -> c_void_p:
         return c_void_p(self.peer_bases[self.rank if rank is None else rank])
 

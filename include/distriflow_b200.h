@@ -127,6 +127,10 @@ int dfb_step_close(void* const* sig, int rank, int R, unsigned epoch, const unsi
 int dfb_allgather_push(void* const* bufs, void* const* sig, long n_bytes, long shard_bytes, int rank, int R, unsigned epoch,
                        int ctas, void* stream);
 int dfb_rank_barrier(void* const* sig, int rank, int R, unsigned epoch, void* stream);
+/* failure detection (abstract_client.ts:12-13,148-158: connect / upload time-outs): every in-kernel wait for a peer is bounded;
+ * a waiter that gives up records 1 + the silent rank in its signal pad, the kernel ends, the host reads the record. */
+int dfb_set_barrier_timeout_us(long long us, void* stream);
+int dfb_barrier_failures(unsigned* pad, unsigned* host_out2, void* stream);
 /* async path (asynchronousSGD_server.ts:65-108): push with staleness guard, in-place apply, pull */
 int dfb_async_push(const void* grad, void* const* acc0, void* const* acc1, void* const* sig, const unsigned* seen_version,
                    unsigned* push_state, long n, long shard, int rank, int R, int max_staleness, float scale, int policy_scale,

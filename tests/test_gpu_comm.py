@@ -275,3 +275,31 @@ def test_allgather_fused_gemm_emulated(R):
         assert err < 1e-2, err
     for h in heaps:
         h.close()
+
+
+def test_barrier_gives_up_on_a_silent_rank_and_names_it():
+    """Failure detection between GPUs: a rank that never launches its kernel must not leave the others spinning for ever.
+    Rank 0 of two emulated ranks enters a barrier alone with a 30 ms bound: the kernel ends, the pad names rank 1."""
+    import time
+    from distriflow_b200.parallel.engine import _comm_sigs
+    from distriflow_b200.parallel.symm import SymmetricHeap
+    L = _comm_sigs()
+    heaps = SymmetricHeap.emulated(2, 65536)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    try:
+        heaps[0].set_barrier_timeout(0.03)
+        t0 = time.time()
+        assert L.dfb_rank_barrier(heaps[0].ptrs(0), 0, 2, 1, st) == 0
+        torch.cuda.synchronize()
+        assert time.time() - t0 < 5.0
+        assert heaps[0].barrier_failure() == (1, 1)
+        assert heaps[0].barrier_failure() is None                      # reading clears the record
+        # rank 1 arrives later: rank 0's flag of generation 1 is already there, nothing to wait for, nothing recorded
+        assert L.dfb_rank_barrier(heaps[1].ptrs(0), 1, 2, 1, st) == 0
+        torch.cuda.synchronize()
+        assert heaps[1].barrier_failure() is None
+    finally:
+        heaps[0].set_barrier_timeout(20.0)
+        torch.cuda.synchronize()
+        for h in heaps:
+            h.close()

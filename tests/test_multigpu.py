@@ -246,6 +246,65 @@ def test_async_engine_invariants_two_gpus(tmp_path, graph):
         assert c["max_staleness_seen"] <= 4
 
 
+def _late_rank_worker(rank, world, port, out):
+    """Asynchronous mode with a rank that joins late and leaves early (worker churn, abstract_server.ts:108-126): the last
+    rank computes nothing until every other rank has FINISHED all its steps, then contributes a few gradients and stops."""
+    import time
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.models import mnist_mlp
+    from distriflow_b200.parallel.async_engine import AsyncEngine
+    torch.manual_seed(0)
+    net = mnist_mlp(softmax_output=False).to(dev)
+    ce = get_loss("softmaxCrossEntropy")
+    eng = AsyncEngine(net, lambda m, x, y: ce(y, m(x)), {"optimizer": "sgd", "learningRate": 1e-3, "maximumStaleness": 64,
+                                                          "dtype": "fp32", "gradDtype": "fp32"}, rank=rank, world=world, device=dev)
+    late = rank == world - 1
+    steps = 3 if late else 10
+    flag = out + ".early_done"
+    g = torch.Generator().manual_seed(rank)
+    waited = 0.0
+    if late:
+        t0 = time.time()
+        while sum(os.path.exists(f"{flag}{r}") for r in range(world - 1)) < world - 1 and time.time() - t0 < 120:
+            time.sleep(0.05)
+        waited = time.time() - t0
+    for _ in range(steps):
+        x = torch.rand(32, 28, 28, 1, generator=g).to(dev)
+        y = torch.randint(0, 10, (32,), generator=g).to(dev)
+        eng.step(x, y)
+    torch.cuda.synchronize()                       # the early ranks get here while the late one has not launched a kernel
+    if not late:
+        open(f"{flag}{rank}", "w").close()
+    eng.drain()
+    allc = [None] * world
+    dist.all_gather_object(allc, {"counters": eng.counters(), "waited": waited, "steps": steps, "lost": eng.state.heaps[0].barrier_failure()})
+    if rank == 0:
+        torch.save(allc, out)
+    dist.destroy_process_group()
+
+
+def test_async_engine_tolerates_a_rank_that_joins_late_and_leaves_early(tmp_path):
+    import torch.multiprocessing as mp
+    world = WORLD
+    if torch.cuda.device_count() < world:
+        pytest.skip("not enough GPUs")
+    out = str(tmp_path / "res.pt")
+    mp.spawn(_late_rank_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    res = torch.load(out)
+    assert res[-1]["waited"] < 100, "the early ranks never finished: they were blocked by the absent one"
+    pushes = sum(r["steps"] for r in res)
+    for r in res:
+        c = r["counters"]
+        assert c["applied"] + c["dropped"] == pushes, c           # nothing lost, nothing double counted
+        assert c["inflight"] == [0, 0] and c["arrived"] == [0, 0]
+        assert r["lost"] is None                                  # no barrier gave up: nobody ever waited for the late rank
+
+
 def _stress_worker(rank, world, port, out):
     """Cross-GPU signalling stress: many small buckets back to back, random per-rank delays before each launch, a
     sequence-numbered audit of every result."""
