@@ -60,6 +60,10 @@ struct GemmParams {
   void* aux;
   long aux_ld;
   int aux_mode;
+  // 2-CTA aux kernel only: every epilogue warp also writes the column sums of its 32-row slab of the (rounded) output to
+  // colsum_part[M/32 slabs][N]; a small reduce kernel adds the slabs in a fixed order.  This is the bias gradient of the
+  // layer whose pre-activation gradient the GEMM produces (K4: bias-grad out of the epilogue, no pass over the output).
+  float* colsum_part;
 };
 
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
@@ -747,6 +751,20 @@ gemm2_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           tma_store_2d(&tmD, slab, n0 + c * kChunkN, out_row0);
           tma_store_commit();
         }
+        if constexpr (kAux && kChunkN == 64) {
+          if (p.colsum_part != nullptr) {              // lane l: columns 2l, 2l+1 of the slab just staged (rows >= M hold zeros)
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(slab + r * 128 + ((((lane >> 2) ^ (r & 7)) << 4) | ((lane & 3) << 2)));
+              s0 += __uint_as_float(w << 16);
+              s1 += __uint_as_float(w & 0xffff0000u);
+            }
+            const int col = n0 + c * kChunkN + 2 * lane;
+            if (col < p.N)
+              *reinterpret_cast<float2*>(p.colsum_part + (long)(m_blk * 8 + (int)cta * 4 + quarter) * p.N + col) = make_float2(s0, s1);
+          }
+        }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -782,6 +800,24 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 }
 
 // out[m, n] = act(sum_s ws[s*split_rows + m, n] + bias[n]); ws fp32 with row pitch ldw.
+// out[col] = sum over the 32-row slabs of part[slab][col], fixed order: 32 columns x 32 slab groups per block.
+__global__ void __launch_bounds__(1024) colsum_part_reduce_kernel(const float* __restrict__ part, float* __restrict__ out, int slabs, int N) {
+  __shared__ float sh[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float t = 0.f;
+  if (c < N)
+    for (int b = ty; b < slabs; b += 32) t += part[(long)b * N + c];
+  sh[ty][tx] = t;
+  __syncthreads();
+  if (ty == 0 && c < N) {
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) tot += sh[k][tx];
+    out[c] = tot;
+  }
+}
+
 template <typename OutT>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, OutT* __restrict__ out, const void* __restrict__ bias,
                                      int bias_dtype, int M, int N, int ldw, int ldd, int splits, int split_rows, int act) {
@@ -869,8 +905,11 @@ DFB_API int dfb_gemm_pick_splits(int M, int N, int K, int block_n, int sms) {
 // See include/distriflow_b200.h.  `workspace` (fp32 scratch) is required iff splits > 1.
 static int gemm_impl(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda, int ldb,
                      int ldd, int a_mn_major, int b_mn_major, int out_dtype, int act, int block_n, int splits, void* workspace,
-                     size_t workspace_bytes, int max_ctas, void* aux, long aux_ld, int aux_mode, cudaStream_t stream) {
+                     size_t workspace_bytes, int max_ctas, void* aux, long aux_ld, int aux_mode, cudaStream_t stream,
+                     float* colsum_part = nullptr) {
   DFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %d x %d x %d", M, N, K);
+  DFB_REQUIRE(colsum_part == nullptr || (block_n == 512 && aux_mode == 2 && bias == nullptr && out_dtype == DT_BF16),
+              "gemm: epilogue column sums exist in the 2-CTA gelu'-epilogue kernel only (block_n 512, aux_mode 2, no bias)");
   DFB_REQUIRE(aux_mode == 0 || (aux != nullptr && out_dtype == DT_BF16 && (aux_ld % 8) == 0 && (N % 8) == 0 &&
                                 ((uintptr_t)aux % 16) == 0),
               "gemm: the aux epilogue needs bf16 output, N and aux pitch multiples of 8, 16-byte aligned aux");
@@ -891,7 +930,7 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, in
   memset(&p, 0, sizeof(p));
   p.bias = bias; p.bias_dtype = bias_dtype; p.M = M; p.N = N; p.K = K; p.a_mn = a_mn_major ? 1 : 0; p.b_mn = b_mn_major ? 1 : 0;
   p.act = act; p.splits = splits; p.kb_per_split = kb_per; p.split_rows = 0;
-  p.aux = aux; p.aux_ld = aux_ld; p.aux_mode = aux_mode;
+  p.aux = aux; p.aux_ld = aux_ld; p.aux_mode = aux_mode; p.colsum_part = colsum_part;
   DFB_REQUIRE(aux_mode == 0 || splits == 1, "gemm: the aux epilogue cannot be combined with split-K");
 
   CUtensorMap tmA, tmB, tmD;
@@ -969,6 +1008,24 @@ DFB_API int dfb_gemm_bf16_aux(const void* A, const void* B, void* D, const void*
                               long aux_ld, int aux_mode, int max_ctas, cudaStream_t stream) {
   return gemm_impl(A, B, D, bias, bias_dtype, M, N, K, lda, ldb, ldd, a_mn_major, b_mn_major, DT_BF16, act, block_n, 1, nullptr,
                    0, max_ctas, aux, aux_ld, aux_mode, stream);
+}
+
+// dgrad GEMM with the GELU backward in its epilogue (aux_mode 2) that ALSO produces the column sums of its output, i.e. the
+// bias gradient of the layer in front of the GELU: D = (A B^T) * gelu'(aux), colsum[n] = sum_m D[m, n] over the stored
+// (bf16-rounded) values.  `part`: fp32 scratch of dfb_gemm_colsum_part_bytes(M, N) bytes.  2-CTA kernel only.
+DFB_API size_t dfb_gemm_colsum_part_bytes(int M, int N) { return (size_t)ceil_div(M, 256) * 8 * (size_t)N * sizeof(float); }
+
+DFB_API int dfb_gemm_bf16_dgelu_colsum(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb, int ldd,
+                                       int a_mn_major, int b_mn_major, void* aux, long aux_ld, float* colsum, float* part,
+                                       size_t part_bytes, int max_ctas, cudaStream_t stream) {
+  DFB_REQUIRE(colsum != nullptr && part != nullptr && part_bytes >= dfb_gemm_colsum_part_bytes(M, N),
+              "gemm dgelu+colsum: scratch of %zu bytes required, got %zu", dfb_gemm_colsum_part_bytes(M, N), part_bytes);
+  int rc = gemm_impl(A, B, D, nullptr, 0, M, N, K, lda, ldb, ldd, a_mn_major, b_mn_major, DT_BF16, ACT_NONE, 512, 1, nullptr, 0,
+                     max_ctas, aux, aux_ld, 2, stream, part);
+  if (rc) return rc;
+  colsum_part_reduce_kernel<<<ceil_div(N, 32), 1024, 0, stream>>>(part, colsum, ceil_div(M, 256) * 8, N);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
 }
 
 // All-gather fused into the GEMM that first consumes the gathered weights (BASELINE north star, SURVEY K8+K1):

@@ -9,6 +9,7 @@
 //             dgamma = sum_rows dy * xhat,  dbeta = sum_rows dy   (per-block partials, then a reduce kernel)
 #include "common.cuh"
 #include "device_utils.cuh"
+#include "ptx_sm100.cuh"
 
 namespace dfb {
 
@@ -178,6 +179,134 @@ __global__ void __launch_bounds__(128, kSum ? 3 : 4) add_ln_bwd_kernel(const T* 
   }
 }
 
+
+// The same backward with the row operands staged through shared memory by the bulk-copy engine (r2: the register version
+// above ran at 53 % of the copy roofline, 59 us per launch at 32768 x 768: a warp loads, reduces, stores in turn, and its
+// 72 accumulator registers leave no room to prefetch the next row).  Every warp owns a ring of kStages rows x {s, dy, ds}
+// and one mbarrier per stage; lane 0 refills a stage as soon as the warp has taken its row into registers, so each SM keeps
+// blocks x 4 warps x kStages x 3 rows (166 KB at D = 768 bf16) in flight whatever the warps are doing.
+template <typename T, int NV, bool kSum, int kStages>
+__global__ void __launch_bounds__(128, kSum ? 3 : 4) add_ln_bwd_pipe_kernel(const T* __restrict__ dy, const T* __restrict__ ds,
+                                                                         const T* __restrict__ s, const T* __restrict__ gamma,
+                                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                         T* __restrict__ dx, float* __restrict__ part, int rows, int D) {
+  using V = Vec16<T>;
+  constexpr int VN = V::kN;
+  constexpr int kW = kSum ? 3 : 2;
+  extern __shared__ __align__(128) uint8_t sh_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t row_bytes = (uint32_t)D * sizeof(T);
+  const int n_op = ds != nullptr ? 3 : 2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sh_raw);                       // [4 warps][kStages]
+  uint8_t* ring = sh_raw + 128 + (size_t)warp * kStages * 3 * row_bytes;      // this warp's stages: s | dy | ds
+  uint64_t* my_bar = bars + warp * kStages;
+  if (lane == 0) {
+    for (int i = 0; i < kStages; ++i) mbar_init(&my_bar[i], 1);
+    fence_mbar_init();
+  }
+  __syncwarp();
+  const int row0 = blockIdx.x * 4 + warp, stride = gridDim.x * 4;
+  const int n_mine = row0 < rows ? (rows - row0 + stride - 1) / stride : 0;
+  auto issue = [&](int k) {                                                   // lane 0 only
+    const long row = row0 + (long)k * stride;
+    uint8_t* st = ring + (size_t)(k % kStages) * 3 * row_bytes;
+    uint64_t* b = &my_bar[k % kStages];
+    mbar_expect_tx(b, n_op * row_bytes);
+    bulk_load_1d(st, s + row * D, row_bytes, b);
+    bulk_load_1d(st + row_bytes, dy + row * D, row_bytes, b);
+    if (n_op == 3) bulk_load_1d(st + 2 * row_bytes, ds + row * D, row_bytes, b);
+  };
+  if (lane == 0)
+    for (int k = 0; k < kStages && k < n_mine; ++k) issue(k);
+  float dg[NV][VN], db[NV][VN], dxs[kSum ? NV : 1][VN];
+  V gam[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) gam[i].raw = *reinterpret_cast<const uint4*>(gamma + c);
+    else gam[i].raw = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      dg[i][j] = 0.f;
+      db[i][j] = 0.f;
+      if (kSum) dxs[i][j] = 0.f;
+    }
+  }
+  for (int k = 0; k < n_mine; ++k) {
+    const long row = row0 + (long)k * stride;
+    const uint8_t* st = ring + (size_t)(k % kStages) * 3 * row_bytes;
+    const float mu = __ldg(mean + row), rs = __ldg(rstd + row);
+    mbar_wait(&my_bar[k % kStages], (k / kStages) & 1);
+    V a[NV], b[NV], r[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+        a[i].raw = *reinterpret_cast<const uint4*>(st + c * sizeof(T));
+        b[i].raw = *reinterpret_cast<const uint4*>(st + row_bytes + c * sizeof(T));
+        if (n_op == 3) r[i].raw = *reinterpret_cast<const uint4*>(st + 2 * row_bytes + c * sizeof(T));
+      }
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          const float xhat = (a[i].get(j) - mu) * rs, d = b[i].get(j);
+          dg[i][j] += d * xhat;
+          db[i][j] += d;
+          const float g = d * gam[i].get(j);
+          s1 += g;
+          s2 += g * xhat;
+        }
+      }
+    }
+    s1 = warp_sum(s1) / (float)D;             // every lane's shared-memory reads have returned: their values went into the sums
+    s2 = warp_sum(s2) / (float)D;
+    if (lane == 0 && k + kStages < n_mine) issue(k + kStages);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * VN;
+      if (c < D) {
+        V o;
+#pragma unroll
+        for (int j = 0; j < VN; ++j) {
+          const float xhat = (a[i].get(j) - mu) * rs;
+          float val = rs * (b[i].get(j) * gam[i].get(j) - s1 - xhat * s2);
+          if (n_op == 3) val += r[i].get(j);
+          o.set(j, val);
+          if (kSum) dxs[i][j] += o.get(j);
+        }
+        *reinterpret_cast<uint4*>(dx + row * D + c) = o.raw;
+      }
+    }
+  }
+  __syncthreads();                             // every warp is done with its ring: the partials reuse that memory
+  float* sh = reinterpret_cast<float*>(sh_raw + 128);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * VN;
+    if (c < D) {
+#pragma unroll
+      for (int j = 0; j < VN; ++j) {
+        sh[(warp * kW + 0) * D + c + j] = dg[i][j];
+        sh[(warp * kW + 1) * D + c + j] = db[i][j];
+        if (kSum) sh[(warp * kW + 2) * D + c + j] = dxs[i][j];
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < kW * D; c += 128) {
+    const int which = c / D, col = c - which * D;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) t += sh[(w * kW + which) * D + col];
+    part[((long)blockIdx.x * kW + which) * D + col] = t;
+  }
+}
+
 // out[which][col] = sum_b part[b][which][col]: 32 columns x 32 partial-groups per block, fixed order (deterministic).
 template <typename T>
 __global__ void __launch_bounds__(1024) ln_param_grad_reduce_kernel(const float* __restrict__ part, T* __restrict__ dgamma,
@@ -232,9 +361,22 @@ static int launch_ln_fwd(const void* x, const void* r, const void* gamma, const 
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
+static int g_ln_bwd_pipe = 0;          // dfb_layernorm_bwd_staged(1): rows staged through shared memory by bulk copies (r2 A/B: no faster, 51.1 vs 50.2 us)
+
 template <typename T, int NV>
 static int launch_ln_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
                          void* dx, float* part, int nblocks, int rows, int D, bool want_sum, cudaStream_t st) {
+  // staged variant: ring of 4 (column-sum variant, 3 blocks per SM) / 3 (4 blocks per SM) rows per warp must fit beside its peers
+  const int stages = want_sum ? 4 : 3, per_sm = want_sum ? 3 : 4;
+  const long ring = 128 + 4L * stages * 3 * D * (long)sizeof(T), red = 128 + 4L * (want_sum ? 3 : 2) * D * (long)sizeof(float);
+  const long pipe_smem = ring > red ? ring : red;
+  if (g_ln_bwd_pipe && pipe_smem * per_sm + 1024 * per_sm <= 227 * 1024) {
+    auto pk = want_sum ? add_ln_bwd_pipe_kernel<T, NV, true, 4> : add_ln_bwd_pipe_kernel<T, NV, false, 3>;
+    DFB_CUDA_CHECK(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pipe_smem));
+    pk<<<nblocks, 128, pipe_smem, st>>>((const T*)dy, (const T*)ds, (const T*)s, (const T*)gamma, mean, rstd, (T*)dx, part, rows, D);
+    DFB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
   auto kern = want_sum ? add_ln_bwd_kernel<T, NV, true> : add_ln_bwd_kernel<T, NV, false>;
   const int smem = 4 * (want_sum ? 3 : 2) * D * (int)sizeof(float);
   if (smem > 48 * 1024) DFB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -265,6 +407,11 @@ DFB_API int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamm
   DFB_LN_FWD(1) DFB_LN_FWD(2) DFB_LN_FWD(3) DFB_LN_FWD(4) DFB_LN_FWD(8)
 #undef DFB_LN_FWD
   return 2;
+}
+
+DFB_API int dfb_layernorm_bwd_staged(int on) {
+  g_ln_bwd_pipe = on;
+  return 0;
 }
 
 DFB_API int dfb_layernorm_bwd_blocks(int rows) {

@@ -123,6 +123,23 @@ def gemm_aux(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int
     return out
 
 
+def gemm_dgelu_colsum(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool, b_mn: bool, M: int, N: int, K: int, aux: torch.Tensor):
+    """`(a·bᵀ) * gelu'(aux)` and, out of the same epilogue, its column sums (fp32 `[N]`): the pre-activation gradient of an
+    MLP and the bias gradient of its first layer in one kernel.  Returns (out, None) where the 2-CTA kernel does not apply."""
+    bn, sp = pick_tile(M, N, K)
+    if bn != 512 or sp != 1 or not FUSE_DGELU_COLSUM:
+        return gemm_aux(a, b, a_mn=a_mn, b_mn=b_mn, M=M, N=N, K=K, aux=aux, aux_mode=2), None
+    L = _lib.lib()
+    out = torch.empty((M, N), device=a.device, dtype=torch.bfloat16)
+    cs = torch.empty(N, dtype=torch.float32, device=a.device)
+    nbytes = int(L.dfb_gemm_colsum_part_bytes(M, N))
+    part = torch.empty(nbytes // 4, dtype=torch.float32, device=a.device)
+    check(L.dfb_gemm_bf16_dgelu_colsum(ptr(a), ptr(b), ptr(out), M, N, K, a.stride(0), b.stride(0), out.stride(0), int(a_mn),
+                                       int(b_mn), ptr(aux), ctypes.c_long(aux.stride(0)), ptr(cs), ptr(part), c_size_t(nbytes),
+                                       _MAX_CTAS, stream()), "dfb_gemm_bf16_dgelu_colsum")
+    return out, cs
+
+
 def take_colsum(dy: torch.Tensor, N: int) -> Optional[torch.Tensor]:
     """Column sums of `dy` that its producer already computed (fp32 `[N]`), or None.  The producer (LayerNorm backward for
     the residual branch, attention backward for the packed QKV gradient) hangs them on the gradient tensor it returns."""
@@ -164,6 +181,11 @@ def _init_sigs() -> None:
     L.dfb_gemm_bf16.restype = c_int
     L.dfb_gemm_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_void_p]
+    L.dfb_gemm_colsum_part_bytes.restype = ctypes.c_size_t
+    L.dfb_gemm_colsum_part_bytes.argtypes = [c_int, c_int]
+    L.dfb_gemm_bf16_dgelu_colsum.restype = c_int
+    L.dfb_gemm_bf16_dgelu_colsum.argtypes = [c_void_p, c_void_p, c_void_p] + [c_int] * 8 + [c_void_p, ctypes.c_long, c_void_p, c_void_p,
+                                                                                   c_size_t, c_int, c_void_p]
     L.dfb_gemm_simt.restype = c_int
     L.dfb_gemm_simt.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int] + [ctypes.c_long] * 5 + \
         [c_int] * 5 + [c_void_p]
@@ -322,13 +344,15 @@ class _MlpFn(torch.autograd.Function):
         # reduce-scatter + optimizer + all-gather kernel on the side stream, which OVERWRITES the working weights.  Every
         # kernel that still reads a weight (the data-gradient GEMMs) is therefore enqueued before that weight is reported.
         # fc2: dpre = (dy W2^T) * gelu'(pre)   <- GELU backward in the dgrad epilogue;  dW2 = h^T dy, db2 = colsum(dy)
-        dpre = gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2)
+        # ... and db1 = colsum(dpre) out of that same epilogue
+        dpre, dpre_colsum = gemm_dgelu_colsum(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre) if b1 is not None else \
+            (gemm_aux(dy2, w2d, a_mn=False, b_mn=False, M=M, N=H, K=N, aux=pre, aux_mode=2), None)
         dx = gemm(dpre, w1d, a_mn=False, b_mn=False, M=M, N=K, K=H).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dw2 = _wgrad(h, dy2, w2, H, N, M)
         db2 = _deliver(b2, pre_colsum if pre_colsum is not None else colsum(dy2)) if b2 is not None else None
         # fc1
         dw1 = _wgrad(x2, dpre, w1, K, H, M)
-        db1 = _deliver(b1, colsum(dpre)) if b1 is not None else None
+        db1 = _deliver(b1, dpre_colsum if dpre_colsum is not None else colsum(dpre)) if b1 is not None else None
         return dx, dw1, db1, dw2, db2
 
 
@@ -346,6 +370,7 @@ import os as _os
 # GELU in the GEMM epilogues (forward: pre-activation and activation stored in one pass; backward: gelu'(pre) multiplied into
 # the data-gradient).  `DFB_FUSE_GELU=0/1` overrides for A/B runs (scripts/bench_aux.py).
 FUSE_GELU = _os.environ.get("DFB_FUSE_GELU", "1") == "1"
+FUSE_DGELU_COLSUM = _os.environ.get("DFB_FUSE_DGELU_COLSUM", "1") == "1"     # fc1 bias gradient out of the gelu'-epilogue GEMM
 
 
 def mlp_cuda(x, w1, b1, w2, b2):

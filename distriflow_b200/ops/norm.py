@@ -24,6 +24,8 @@ def _sigs():
         L.dfb_add_layernorm_fwd.argtypes = [c_void_p] * 8 + [c_int, c_int, c_float, c_int, c_void_p]
         L.dfb_layernorm_bwd_blocks.restype = c_int
         L.dfb_layernorm_bwd_blocks.argtypes = [c_int]
+        L.dfb_layernorm_bwd_staged.restype = c_int
+        L.dfb_layernorm_bwd_staged.argtypes = [c_int]
         L.dfb_add_layernorm_bwd.restype = c_int
         L.dfb_add_layernorm_bwd.argtypes = [c_void_p] * 11 + [c_int, c_int, c_int, c_void_p]
         L.dfb_permute_rows.restype = c_int

@@ -34,6 +34,12 @@ int dfb_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int b
 int dfb_gemm_bf16_aux(const void* A, const void* B, void* D, const void* bias, int bias_dtype, int M, int N, int K, int lda,
                       int ldb, int ldd, int a_mn_major, int b_mn_major, int act, int block_n, void* aux, long aux_ld,
                       int aux_mode, int max_ctas, void* stream);
+/* aux_mode 2 (output = accumulator * gelu'(aux)) whose epilogue also emits the column sums of the stored output: the bias
+ * gradient of the layer in front of the GELU, with no extra pass over D.  2-CTA kernel; `part` is fp32 scratch. */
+size_t dfb_gemm_colsum_part_bytes(int M, int N);
+int dfb_gemm_bf16_dgelu_colsum(const void* A, const void* B, void* D, int M, int N, int K, int lda, int ldb, int ldd,
+                               int a_mn_major, int b_mn_major, void* aux, long aux_ld, float* colsum, float* part,
+                               size_t part_bytes, int max_ctas, void* stream);
 
 /* All-gather fused into the first consuming GEMM: D = act(A * W + bias) with W[K,N] sharded over ranks; two extra warps
  * per CTA pull the remote shards over NVLink into the local W buffer while the k-loop starts on local rows.
@@ -171,6 +177,7 @@ int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const floa
  * fused residual add + LayerNorm: s = x + r (r nullable), y = LN(s) * gamma + beta; mean / rstd: [rows] fp32 */
 int dfb_add_layernorm_fwd(const void* x, const void* r, const void* gamma, const void* beta, void* s_out, void* y, float* mean,
                           float* rstd, int rows, int D, float eps, int dtype, void* stream);
+int dfb_layernorm_bwd_staged(int on);   /* 1: rows staged through shared memory by bulk copies; 0 (default): register-only kernel */
 int dfb_layernorm_bwd_blocks(int rows);                     /* row blocks of the `part` scratch: 2 * D * blocks floats */
 int dfb_add_layernorm_bwd(const void* dy, const void* ds, const void* s, const void* gamma, const float* mean, const float* rstd,
                           void* dx, void* dgamma, void* dbeta,

@@ -345,6 +345,41 @@ def test_add_layer_norm(dtype, D, with_res):
     assert rel_err(g.grad, gr.grad) < tol and rel_err(b.grad, br.grad) < tol
 
 
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layer_norm_backward_staged_equals_register_kernel(with_res):
+    """The bulk-copy staged backward (ring of rows per warp, many ring wraps per warp at this size) does the arithmetic
+    of the register-only kernel in the same order: every output is bitwise equal."""
+    from distriflow_b200 import ops
+    from distriflow_b200.ops.norm import _sigs
+    L = _sigs()
+    torch.manual_seed(1)
+    rows, D = 20011, 768
+    x0 = torch.randn(rows, D, device=dev()).bfloat16()
+    r0 = torch.randn(rows, D, device=dev()).bfloat16()
+    g0 = (1 + 0.1 * torch.randn(D, device=dev())).bfloat16()
+    b0 = (0.1 * torch.randn(D, device=dev())).bfloat16()
+    gs, gy = torch.randn(rows, D, device=dev()).bfloat16(), torch.randn(rows, D, device=dev()).bfloat16()
+    res = []
+    try:
+        for staged in (1, 0):
+            L.dfb_layernorm_bwd_staged(staged)
+            x, r, g, b = (t.clone().requires_grad_(True) for t in (x0, r0, g0, b0))
+            if with_res:
+                s, y = ops.add_layer_norm(x, r, g, b, 1e-5)
+                torch.autograd.backward([s, y], [gs, gy])
+            else:
+                ops.layer_norm(x, g, b, 1e-5).backward(gy)
+            res.append((x.grad.clone(), g.grad.clone(), b.grad.clone()))
+    finally:
+        L.dfb_layernorm_bwd_staged(0)
+    for a, c in zip(*res):
+        assert torch.equal(a, c)
+    xr, gr, br = (t.float().requires_grad_(True) for t in (x0, g0, b0))
+    F.layer_norm(xr, (D,), gr, br, 1e-5).backward(gy.float())
+    if not with_res:
+        assert rel_err(res[0][0], xr.grad) < 2e-2 and rel_err(res[0][1], gr.grad) < 2e-2
+
+
 def test_attention_layout_kernels_match_torch():
     from distriflow_b200.ops.attention import causal_self_attention
     torch.manual_seed(0)
@@ -437,6 +472,26 @@ def test_fused_mlp_gelu_in_epilogues():
     assert rel_err(y, yr) < 2e-2
     for got, r in zip((x, w1, b1, w2, b2), ref):
         assert rel_err(got.grad, r.grad) < 3e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 3072, 768), (2000, 2560, 320)])
+def test_dgelu_gemm_emits_the_bias_gradient_from_its_epilogue(M, N, K):
+    """K4: the gelu'-epilogue dgrad GEMM also produces the column sums of what it stores (fc1's bias gradient)."""
+    from distriflow_b200.ops import dense
+    torch.manual_seed(0)
+    dy = torch.randn(M, K, device=dev()).bfloat16()
+    w2 = (torch.randn(N, K, device=dev()) * 0.05).bfloat16()
+    pre = torch.randn(M, N, device=dev()).bfloat16()
+    assert dense.pick_tile(M, N, K) == (512, 1)
+    out, cs = dense.gemm_dgelu_colsum(dy, w2, a_mn=False, b_mn=False, M=M, N=N, K=K, aux=pre)
+    plain = dense.gemm_aux(dy, w2, a_mn=False, b_mn=False, M=M, N=N, K=K, aux=pre, aux_mode=2)
+    assert cs is not None and torch.equal(out, plain)
+    assert rel_err(cs, out.float().sum(0)) < 1e-5
+    x = pre.float()
+    u = 0.7978845608028654 * (x + 0.044715 * x ** 3)
+    t = torch.tanh(u)
+    dgelu = 0.5 * (1 + t) + 0.5 * x * (1 - t * t) * 0.7978845608028654 * (1 + 3 * 0.044715 * x * x)
+    assert rel_err(out, (dy.float() @ w2.float().t()) * dgelu) < 2e-2
 
 
 def test_thin_channel_conv_stem_im2col_path():
