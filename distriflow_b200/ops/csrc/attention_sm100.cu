@@ -378,11 +378,11 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
   }
 }
 
-// dq_acc [B,T,H,64] fp32 -> dqkv[b,t,0,h,:] bf16, and the accumulator is cleared for the next call (it must start at zero).
+// dq_acc [B,T,H,64] fp32 (the sum of dS K without the 1/sqrt(D) factor) * scale -> dqkv[b,t,0,h,:] bf16, and the accumulator is cleared for the next call (it must start at zero).
 // A thread keeps ONE 8-column vector of the row and walks down the rows, so it can also sum its columns of dQ (the values as
 // stored) for the bias gradient of the QKV projection: `dbias` (nullable) fp32 [3*H*64], part [0, H*64) is added to.
 __global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long rows_bt,
-                                                              int H, float* __restrict__ dbias) {
+                                                              int H, float* __restrict__ dbias, float scale) {
   __shared__ float sh_sum[2048];                               // [H*64] block-level column sums (H*64 <= 2048)
   const int vpr = H * kAttD / 8;                               // 8-element vectors per (b, t) row
   const int rows_per_iter = blockDim.x / vpr;                  // blockDim is a multiple of vpr: a thread's columns never change
@@ -411,7 +411,8 @@ __global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict_
     for (int u = 0; u < U; ++u) {
       const long bt = bt0 + u * step;
       if (bt >= rows_bt) continue;
-      uint4 pk = {pack_bf16(a[u].x, a[u].y), pack_bf16(a[u].z, a[u].w), pack_bf16(b[u].x, b[u].y), pack_bf16(b[u].z, b[u].w)};
+      uint4 pk = {pack_bf16(scale * a[u].x, scale * a[u].y), pack_bf16(scale * a[u].z, scale * a[u].w),
+                  pack_bf16(scale * b[u].x, scale * b[u].y), pack_bf16(scale * b[u].z, scale * b[u].w)};
       *reinterpret_cast<uint4*>(dqkv + bt * 3 * H * kAttD + c * 8) = pk;
       float4* dst = reinterpret_cast<float4*>(dq_acc + bt * H * kAttD + c * 8);
       dst[0] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -443,6 +444,15 @@ __device__ __forceinline__ void tma_reduce_add_4d(const void* tmap, const void* 
                : "memory");
 }
 
+// A load the compiler may not sink towards its use: `asm volatile` statements keep their order, and the barrier waits
+// between this load and its use (one query tile later) are `asm volatile` too.  With plain `__ldg` the row statistics of the
+// next tile were fetched right before their first use and every tile waited ~700 cycles for them (12 % of the kernel, r2 ncu).
+__device__ __forceinline__ float ldg_pinned(const float* ptr) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];\n" : "=f"(v) : "l"(ptr));
+  return v;
+}
+
 struct AttnBwdParams {
   const float* lse;      // [B, H, T]
   const float* delta;    // [B, H, T]
@@ -453,42 +463,102 @@ struct AttnBwdParams {
   float scale_log2;      // scale * log2(e)
 };
 
-// P and dS for one query row and one half (64 key columns) of the tile, in two passes so that each shared-memory tile is
-// written as late as its previous reader allows:
-//   pass A   P  = exp2(S*c - lse*log2e)            -> sP   (first store waits for dV of the previous tile: `p_free`)
-//   pass B   dS = P (dP - delta) / sqrt(D)         -> sdS  (first store waits for dQ, dK of the previous tile: `ds_free`)
+// Packed fp32 pairs (one issue slot for two lanes of arithmetic; the compute warps are issue-bound, r2 ncu).
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
+// P and dS for one query row and one half (64 key columns) of the tile, in two passes; each TMEM operand is released as soon
+// as it is in registers and each shared-memory tile is written as late as its previous reader allows:
+//   pass A   [s_full]  S -> registers  (s_cons: S_{i+1} may be issued)   P = exp2(S*c - lse*log2e)  -> sP  [p_free]
+//   pass B   [dp_full] dP -> registers (dp_cons)   dS = P (dP - delta)   (p_ready)                  -> sdS [ds_free]
+// The proxy fence that publishes P runs after the dS arithmetic and the one that publishes dS after the dQ staging stores of
+// the previous tile (in the kernel), so neither waits for its own stores alone: r2 ncu showed the compute warps spending a
+// third of their time in `st.shared -> fence.proxy.async -> mbarrier.arrive` with nothing else in flight.
+// dS carries no 1/sqrt(D): the factor is applied once to dK (epilogue) and once to dQ (convert kernel), not per element here.
 template <bool kDiag>
-__device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t tmem_dp_lane, uint8_t* pblk, uint8_t* dsblk, int row,
-                                                 int half, float lse2, float dl, float scale, float scale_log2, uint64_t* p_free,
-                                                 uint64_t* ds_free, uint32_t free_parity, bool wait_free) {
+__device__ __forceinline__ void bwd_pass_a(float (&pv)[64], uint32_t tmem_s_lane, uint8_t* pblk, int row, int half, int lane, float lse2,
+                                           float scale_log2, uint64_t* s_full, uint64_t* s_cons, uint32_t ph, uint64_t* p_free,
+                                           bool wait_free, bool cta_sync, int ctid) {
   const int col0 = half * 64;
-  float pv[64];
+  mbar_wait(s_full, ph);
+  tc_fence_after();
   {
     uint32_t rs[64];
     tmem_ld_32x32(tmem_s_lane + col0, *reinterpret_cast<uint32_t(*)[32]>(&rs[0]));
     tmem_ld_32x32(tmem_s_lane + col0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rs[32]));
     tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(s_cons);
+    const uint64_t c2 = pack_f32x2(scale_log2, scale_log2), l2 = pack_f32x2(-lse2, -lse2);
 #pragma unroll
-    for (int i = 0; i < 64; ++i) {
-      float pe = exp2f(fmaf(__uint_as_float(rs[i]), scale_log2, -lse2));
-      if (kDiag && col0 + i > row) pe = 0.f;
-      pv[i] = pe;
+    for (int i = 0; i < 64; i += 2) {
+      float t0, t1;
+      unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), c2, l2), t0, t1);
+      float p0 = exp2f(t0), p1 = exp2f(t1);
+      if (kDiag && col0 + i > row) p0 = 0.f;
+      if (kDiag && col0 + i + 1 > row) p1 = 0.f;
+      pv[i] = p0;
+      pv[i + 1] = p1;
     }
   }
-  uint32_t rp[64];                                   // dP: in flight while P is packed and stored
-  tmem_ld_32x32(tmem_dp_lane + col0, *reinterpret_cast<uint32_t(*)[32]>(&rp[0]));
-  tmem_ld_32x32(tmem_dp_lane + col0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rp[32]));
-  if (wait_free) mbar_wait(p_free, free_parity);
+  if (wait_free) mbar_wait(p_free, ph ^ 1);
+  if (cta_sync) {     // first tile of an item: the P / dS tiles were the dV / dK staging of the previous item, stored by thread 0
+    if (ctid == 0) tma_store_wait_read<0>();                   // waited for here, behind the exponentials, not at the item's start
+    named_bar_sync(1, 256);
+  }
 #pragma unroll
   for (int q8 = 0; q8 < 8; ++q8) {
     uint4 pk = {pack_bf16(pv[8 * q8 + 0], pv[8 * q8 + 1]), pack_bf16(pv[8 * q8 + 2], pv[8 * q8 + 3]),
                 pack_bf16(pv[8 * q8 + 4], pv[8 * q8 + 5]), pack_bf16(pv[8 * q8 + 6], pv[8 * q8 + 7])};
     st_swizzled_row_piece(pblk, row, q8, pk);
   }
-  tmem_ld_wait();
+}
+
+__device__ __forceinline__ void bwd_pass_b(float (&pv)[64], uint32_t tmem_dp_lane, uint8_t* dsblk, int row, int half, int lane, float dl,
+                                           uint64_t* dp_full, uint64_t* dp_cons, uint64_t* p_ready, uint32_t ph, uint64_t* ds_free,
+                                           bool wait_free) {
+  const int col0 = half * 64;
+  mbar_wait(dp_full, ph);
+  tc_fence_after();
+  {
+    uint32_t rp[64];
+    tmem_ld_32x32(tmem_dp_lane + col0, *reinterpret_cast<uint32_t(*)[32]>(&rp[0]));
+    tmem_ld_32x32(tmem_dp_lane + col0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&rp[32]));
+    tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(dp_cons);
+    const uint64_t d2 = pack_f32x2(-dl, -dl);
 #pragma unroll
-  for (int i = 0; i < 64; ++i) pv[i] = pv[i] * (__uint_as_float(rp[i]) - dl) * scale;
-  if (wait_free) mbar_wait(ds_free, free_parity);
+    for (int i = 0; i < 64; i += 2) {
+      const uint64_t d = add_f32x2(pack_f32x2(__uint_as_float(rp[i]), __uint_as_float(rp[i + 1])), d2);
+      unpack_f32x2(mul_f32x2(pack_f32x2(pv[i], pv[i + 1]), d), pv[i], pv[i + 1]);
+    }
+  }
+  fence_proxy_async_smem();                // P: its stores were issued before the dP load and the arithmetic above
+  __syncwarp();
+  if (lane == 0) mbar_arrive(p_ready);
+  if (wait_free) mbar_wait(ds_free, ph ^ 1);
 #pragma unroll
   for (int q8 = 0; q8 < 8; ++q8) {
     uint4 dk = {pack_bf16(pv[8 * q8 + 0], pv[8 * q8 + 1]), pack_bf16(pv[8 * q8 + 2], pv[8 * q8 + 3]),
@@ -511,7 +581,31 @@ __device__ __forceinline__ void bwd_softmax_half(uint32_t tmem_s_lane, uint32_t 
 //   warps 2..9  softmax / dS, dQ drain, final dK / dV epilogue
 constexpr int kBwdThreads = 320;
 constexpr int kBwdStageBytes = 2 * kAttTileBytes;             // Q_i + dO_i
-constexpr int kBwdSmem = 2 * kAttTileBytes + 2 * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 256 + 1024;
+// Three {Q_i, dO_i} stages: a stage is released by the LAST product of its tile (dK) and S of the tile after next needs it
+// early (right after the compute warps have read S of the next tile); with two stages the load sat on that path and the
+// compute warps waited 12 % of their time for S (r2 ncu: try_wait on s_full).
+constexpr int kBwdStages = 3;
+// Operand pool: kBwdPool = 4 slots of 32 KiB, each holding either {K_j, V_j} of an item (pinned for the whole item) or
+// {Q_i, dO_i} of a tile.  Slots are handed out round robin, skipping the pinned one, so the NEXT item's K/V pair is loaded
+// into an ordinary slot while the current item's last tiles run (with a fixed K/V buffer every item started with a load + S
+// product that nothing overlapped: 14 % of the run at T = 1024, r2 ncu) and the old K/V slot joins the rotation afterwards.
+// Producer and MMA thread replay the same allocation sequence: K/V(w), tiles of w, K/V(w+1), ...
+// Tried and dropped (r2): a second fixed K/V buffer paid for by aliasing the dQ staging tile onto P: every P store then
+// waited for the TMA reduce issued a few hundred cycles earlier (0.378 vs 0.370 ms at T = 1024, 656 vs 762 TFLOP/s at 8192).
+constexpr int kBwdPool = kBwdStages + 1;
+constexpr int kBwdSmem = kBwdPool * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 256 + 1024;
+
+struct BwdPool {                      // the allocation sequence, replayed identically by the producer and the MMA thread
+  int next = 0;                       // round-robin cursor
+  uint32_t parity = 0, used = 0;      // bit s: (fills of slot s so far) & 1 = barrier phase of its next fill; slot filled before
+  __device__ __forceinline__ int take(int skip_a, int skip_b = -1) {
+    int s = next;
+    if (s == skip_a || s == skip_b) s = (s + 1) % kBwdPool;
+    if (s == skip_a || s == skip_b) s = (s + 1) % kBwdPool;
+    next = (s + 1) % kBwdPool;
+    return s;
+  }
+};
 constexpr uint32_t kBwdTmemCols = 512;
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
@@ -519,26 +613,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
                 const __grid_constant__ CUtensorMap tmDQKV, const __grid_constant__ CUtensorMap tmDQ, const AttnBwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem;
-  uint8_t* sV = smem + kAttTileBytes;
-  uint8_t* sQdO = smem + 2 * kAttTileBytes;                                   // stage s: Q at +s*32K, dO at +s*32K+16K
-  uint8_t* sP = sQdO + 2 * kBwdStageBytes;                                    // 32 KiB
+  uint8_t* sPool = smem;                                                      // slot s: K or Q at +s*32K, V or dO at +s*32K+16K
+  uint8_t* sP = sPool + kBwdPool * kBwdStageBytes;                            // 32 KiB
   uint8_t* sdS = sP + 2 * kAttTileBytes;                                      // 32 KiB
   uint8_t* sdQ = sdS + 2 * kAttTileBytes;                                     // 32 KiB fp32 staging: d columns [0,32) then [32,64)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sdQ + 2 * kAttTileBytes);
-  uint64_t* kv_full = bars + 0;
-  uint64_t* qdo_full = bars + 1;      // [2]
-  uint64_t* qdo_empty = bars + 3;     // [2]
-  uint64_t* sdp_full = bars + 5;
-  uint64_t* pds_ready = bars + 6;
+  uint64_t* slot_full = bars + 20;    // [kBwdPool] the slot's pair has landed
+  uint64_t* slot_empty = bars + 24;   // [kBwdPool] every product that reads the slot has completed
+  uint64_t* s_full = bars + 5;        // S_i complete in TMEM
+  uint64_t* p_ready = bars + 6;       // P_i written to sP
   uint64_t* dq_full = bars + 7;
   uint64_t* dq_empty = bars + 8;
   uint64_t* dkv_full = bars + 9;
   uint64_t* p_free = bars + 10;       // dV of the tile has read P: sP may be rewritten
   uint64_t* ds_free = bars + 11;      // dQ and dK of the tile have read dS: sdS may be rewritten
-  uint64_t* kv_empty = bars + 12;     // every product of the item that reads K_j / V_j has completed
   uint64_t* dkv_empty = bars + 13;    // the epilogue has taken dV / dK of the item out of TMEM
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* dp_full = bars + 16;      // dP_i complete in TMEM
+  uint64_t* s_cons = bars + 17;       // every compute warp has read S_i out of TMEM: S_{i+1} may overwrite it
+  uint64_t* dp_cons = bars + 18;      // ... and dP_i
+  uint64_t* ds_ready = bars + 19;     // dS_i written to sdS
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -556,14 +650,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     tma_prefetch_desc(&tmDO);
     tma_prefetch_desc(&tmDQKV);
     tma_prefetch_desc(&tmDQ);
-    mbar_init(kv_full, 1);
-    mbar_init(kv_empty, 1);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&qdo_full[i], 1);
-      mbar_init(&qdo_empty[i], 1);
+    for (int i = 0; i < kBwdPool; ++i) {
+      mbar_init(&slot_full[i], 1);
+      mbar_init(&slot_empty[i], 1);
     }
-    mbar_init(sdp_full, 1);
-    mbar_init(pds_ready, 8);      // one arrive per compute warp
+    mbar_init(s_full, 1);
+    mbar_init(dp_full, 1);
+    mbar_init(p_ready, 8);        // one arrive per compute warp
+    mbar_init(ds_ready, 8);
+    mbar_init(s_cons, 8);
+    mbar_init(dp_cons, 8);
     mbar_init(dq_full, 1);
     mbar_init(dq_empty, 8);
     mbar_init(dkv_full, 1);
@@ -583,24 +679,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   if (warp_idx == 0) {
     // ===================================================================== TMA producer
     if (elect_one()) {
-      int g0 = 0, wi = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++wi) {
+      BwdPool pool;
+      int kv_slot = -1;
+      auto fill = [&](int slot, const CUtensorMap* tm_a, int c2_a, const CUtensorMap* tm_b, int c2_b, int row0, int b) {
+        if ((pool.used >> slot) & 1u) mbar_wait_backoff(&slot_empty[slot], ((pool.parity >> slot) & 1u) ^ 1u, 128);
+        pool.used |= 1u << slot;
+        pool.parity ^= 1u << slot;
+        mbar_expect_tx(&slot_full[slot], kBwdStageBytes);
+        tma_load_4d(sPool + slot * kBwdStageBytes, tm_a, &slot_full[slot], 0, row0, c2_a, b);
+        tma_load_4d(sPool + slot * kBwdStageBytes + kAttTileBytes, tm_b, &slot_full[slot], 0, row0, c2_b, b);
+      };
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
         const int jt = w / bh_total, bh = w % bh_total;
         const int b = bh / p.H, h = bh % p.H;
         const int n_it = p.n_qt - jt;
-        if (wi > 0) mbar_wait_backoff(kv_empty, (wi - 1) & 1, 128);
-        mbar_expect_tx(kv_full, 2 * kAttTileBytes);
-        tma_load_4d(sK, &tmQKV, kv_full, 0, jt * kAttTile, p.H + h, b);
-        tma_load_4d(sV, &tmQKV, kv_full, 0, jt * kAttTile, 2 * p.H + h, b);
-        for (int it = 0; it < n_it; ++it) {
-          const int g = g0 + it, st = g & 1;
-          mbar_wait_backoff(&qdo_empty[st], ((g >> 1) & 1) ^ 1, 128);
-          mbar_expect_tx(&qdo_full[st], kBwdStageBytes);
-          const int q0 = (jt + it) * kAttTile;
-          tma_load_4d(sQdO + st * kBwdStageBytes, &tmQKV, &qdo_full[st], 0, q0, h, b);
-          tma_load_4d(sQdO + st * kBwdStageBytes + kAttTileBytes, &tmDO, &qdo_full[st], 0, q0, h, b);
-        }
-        g0 += n_it;
+        const int kv_prev = kv_slot;
+        kv_slot = pool.take(kv_prev);                           // not the slot the previous item's K/V still occupy
+        fill(kv_slot, &tmQKV, p.H + h, &tmQKV, 2 * p.H + h, jt * kAttTile, b);
+        // the item's first tile must not land in the previous item's K/V slot either (free only when that item ends): it is
+        // the tile whose S product should be running while the previous item's epilogue drains
+        for (int it = 0; it < n_it; ++it)
+          fill(pool.take(kv_slot, it == 0 ? kv_prev : -1), &tmQKV, h, &tmDO, h, (jt + it) * kAttTile, b);
       }
     }
   } else if (warp_idx == 1) {
@@ -609,53 +708,73 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);      // S, dP
       const uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);       // dV = P^T dO, dK = dS^T Q  (both operands MN-major)
       const uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);       // dQ = dS K
-      const uint64_t dk_kmaj = make_smem_desc_sw128(smem_u32(sK), 0, 1024);
-      const uint64_t dv_kmaj = make_smem_desc_sw128(smem_u32(sV), 0, 1024);
-      const uint64_t dk_mn = make_smem_desc_sw128(smem_u32(sK), kAttTileBytes, 1024);
+      uint64_t dk_kmaj = 0, dv_kmaj = 0, dk_mn = 0;                  // K_j / V_j descriptors: the current item's slot
+      BwdPool pool;
+      int kv_slot = -1, slot_cur = 0, slot_nxt = 0;                  // slots of the current and the next tile's {Q, dO}
+      auto claim = [&](int slot) {                                   // wait until the fill of `slot` that is next in sequence has landed
+        mbar_wait(&slot_full[slot], (pool.parity >> slot) & 1u);
+        pool.parity ^= 1u << slot;
+        tc_fence_after();
+      };
       const uint64_t dp_mn = make_smem_desc_sw128(smem_u32(sP), kAttTileBytes, 1024);         // A MN-major: two 64-wide atoms
       const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
       const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
       const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
-      // Issue order per query tile i, software-pipelined against the compute warps (who, after publishing P_i / dS_i, drain
-      // dQ_{i-1} and then start on S_{i+1} / dP_{i+1}):
-      //   [P_i, dS_i ready]  S_{i+1}, dP_{i+1}  ->  dV += P_i^T dO_i  (P free)  ->  [dQ_{i-1} drained]  dQ_i = dS_i K
-      //                      ->  dK += dS_i^T Q_i  (dS free, Q_i / dO_i stage free)
-      // r2 ncu: with dQ drained right after its own tile the compute warps waited 15 % of their time for the dQ product,
-      // and a tile took 5300 cycles against 1280 cycles of tensor-core work.
-      auto issue_sdp = [&](int g) {           // g: running tile index of this CTA (ring stage and phase)
-        const int st = g & 1;
-        mbar_wait(&qdo_full[st], (g >> 1) & 1);
-        tc_fence_after();
-        const uint64_t dq_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), 0, 1024);
-        const uint64_t ddo_kmaj = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), 0, 1024);
+      // Issue order per query tile i, software-pipelined against the compute warps.  S and dP have one TMEM buffer each, so
+      // the next tile's products are issued as soon as the compute warps have READ the current ones (not when they are done
+      // with them): S_{i+1} runs under the exponentials of tile i, dP_{i+1} under its dS arithmetic and the dQ drain.
+      //   [S_i read]   S_{i+1}   ->  [P_i in smem]  dV += P_i^T dO_i  (P free)
+      //   [dP_i read]  dP_{i+1}  ->  [dS_i in smem, dQ_{i-1} drained]  dQ_i = dS_i K  ->  dK += dS_i^T Q_i  (dS, Q_i / dO_i free)
+      // r2 ncu, before: S_{i+1} / dP_{i+1} were issued together after BOTH P_i and dS_i were stored; a tile took 4100 cycles
+      // against 1280 cycles of tensor-core work and ~2000 issue cycles of the compute warps, the rest was this round trip.
+      auto issue_s = [&](int slot) {          // the slot has been claimed
+        const uint64_t dq_kmaj = make_smem_desc_sw128(smem_u32(sPool + slot * kBwdStageBytes), 0, 1024);
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq_kmaj + (uint64_t)(k * 2), dk_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(s_full);
+      };
+      auto issue_dp = [&](int slot) {
+        const uint64_t ddo_kmaj = make_smem_desc_sw128(smem_u32(sPool + slot * kBwdStageBytes + kAttTileBytes), 0, 1024);
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16(tmem_dp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(sdp_full);
+        umma_commit(dp_full);
       };
       int g0 = 0, wi = 0;
       for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++wi) {
         const int n_it = p.n_qt - w / bh_total;
-        mbar_wait(kv_full, wi & 1);
-        issue_sdp(g0);                            // S / dP columns are free: the previous item's last pds_ready was waited for
+        const int kv_prev = kv_slot;
+        kv_slot = pool.take(kv_prev);
+        claim(kv_slot);
+        dk_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes), 0, 1024);
+        dv_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes + kAttTileBytes), 0, 1024);
+        dk_mn = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes), kAttTileBytes, 1024);
+        slot_cur = pool.take(kv_slot, kv_prev);
+        claim(slot_cur);
+        issue_s(slot_cur);                        // S / dP columns are free: the previous item's last s_cons / dp_cons were waited for
+        issue_dp(slot_cur);
         for (int it = 0; it < n_it; ++it) {
-          const int g = g0 + it, st = g & 1;
+          const int g = g0 + it;
           const uint32_t ph = g & 1;
-          const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes), kAttTileBytes, 1024);
-          const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sQdO + st * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
-          mbar_wait_backoff(pds_ready, ph, 32);   // P_i, dS_i written; the compute warps are done with S_i / dP_i in TMEM
-          if (it + 1 < n_it) issue_sdp(g + 1);
+          const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sPool + slot_cur * kBwdStageBytes), kAttTileBytes, 1024);
+          const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sPool + slot_cur * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
+          mbar_wait_backoff(s_cons, ph, 32);      // S_i is in the compute warps' registers
+          if (it + 1 < n_it) {
+            slot_nxt = pool.take(kv_slot);
+            claim(slot_nxt);
+            issue_s(slot_nxt);
+          }
+          mbar_wait_backoff(p_ready, ph, 32);     // P_i written
           if (it == 0 && wi > 0) mbar_wait(dkv_empty, (wi - 1) & 1);   // the previous item's dV / dK have left TMEM
           tc_fence_after();
 #pragma unroll
           for (int k = 0; k < 8; ++k)       // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
             umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
           umma_commit(p_free);
-          if (g > 0) {
-            mbar_wait(dq_empty, ph ^ 1);    // the compute warps have taken the previous dQ out of TMEM
-            tc_fence_after();
-          }
+          mbar_wait_backoff(dp_cons, ph, 32);     // dP_i is in registers
+          if (it + 1 < n_it) issue_dp(slot_nxt);
+          mbar_wait_backoff(ds_ready, ph, 32);    // dS_i written
+          if (g > 0) mbar_wait(dq_empty, ph ^ 1); // the compute warps have taken the previous dQ out of TMEM
+          tc_fence_after();
 #pragma unroll
           for (int k = 0; k < 8; ++k)       // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
             umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
@@ -664,9 +783,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           for (int k = 0; k < 8; ++k)       // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
             umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
           umma_commit(ds_free);
-          umma_commit(&qdo_empty[st]);
+          umma_commit(&slot_empty[slot_cur]);     // Q_i / dO_i: dK was their last reader
+          slot_cur = slot_nxt;
         }
-        umma_commit(kv_empty);
+        umma_commit(&slot_empty[kv_slot]);        // K_j / V_j
         umma_commit(dkv_full);
         g0 += n_it;
       }
@@ -681,23 +801,36 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     uint8_t* pblk = sP + half * kAttTileBytes;
     uint8_t* dsblk = sdS + half * kAttTileBytes;
     int g0 = 0, wi = 0;
+    float lse_first = 0.f, dl_first = 0.f;                      // row statistics of the first (diagonal) query tile of item `w`
+    auto fetch_first = [&](int w) {
+      lse_first = 0.f;
+      dl_first = 0.f;
+      if (w >= n_items) return;
+      const int r = (w / bh_total) * kAttTile + row;
+      if (r < p.T) {
+        lse_first = ldg_pinned(p.lse + (size_t)(w % bh_total) * p.T + r);
+        dl_first = ldg_pinned(p.delta + (size_t)(w % bh_total) * p.T + r);
+      }
+    };
+    fetch_first(blockIdx.x);
     for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++wi) {
       const int jt = w / bh_total, bh = w % bh_total;
       const int b = bh / p.H, h = bh % p.H;
       const int kv0 = jt * kAttTile;
       const int n_it = p.n_qt - jt;
-      // dQ of local tile t: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator
-      auto drain_dq = [&](int t) {
+      // dQ of local tile t: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator.  Every warp stages and reduces
+      // its own 32 rows x 32 columns (a 4 KiB slab of the swizzled staging tile): no barrier across warps in the tile loop.
+      // `publish_ds`: the fence that makes the staging slab visible to the TMA also publishes this warp's dS stores.
+      auto drain_dq = [&](int t, bool publish_ds) {
         mbar_wait(dq_full, (g0 + t) & 1);
         tc_fence_after();
         uint32_t r[32];
         tmem_ld_32x32(tmem_dq + lane_sel + half * 32, r);
         tmem_ld_wait();
         tc_fence_before();
+        if (lane == 0) tma_store_wait_read<0>();                // this warp's previous reduce has finished reading its slab
         __syncwarp();
         if (lane == 0) mbar_arrive(dq_empty);
-        if (ctid == 0) tma_store_wait_read<0>();                // the previous reduce has finished reading the staging buffer
-        named_bar_sync(1, 256);
         uint8_t* blk = sdQ + half * kAttTileBytes;
 #pragma unroll
         for (int q8 = 0; q8 < 8; ++q8) {
@@ -705,24 +838,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           st_swizzled_row_piece(blk, row, q8, pk);
         }
         fence_proxy_async_smem();
-        named_bar_sync(1, 256);
-        if (ctid == 0) {
-          const int q0 = (jt + t) * kAttTile;
-          tma_reduce_add_4d(&tmDQ, sdQ, 0, q0, h, b);
-          tma_reduce_add_4d(&tmDQ, sdQ + kAttTileBytes, 32, q0, h, b);
+        __syncwarp();
+        if (lane == 0) {
+          if (publish_ds) mbar_arrive(ds_ready);
+          tma_reduce_add_4d(&tmDQ, blk + quarter * 4096, half * 32, (jt + t) * kAttTile + quarter * 32, h, b);
           tma_store_commit();
         }
       };
-      // row statistics of the NEXT query tile are fetched while the current one is processed
-      float lse_nx = 0.f, dl_nx = 0.f;
-      if (kv0 + row < p.T) {                                    // first query tile = the diagonal one: q0 = kv0
-        lse_nx = __ldg(p.lse + (size_t)bh * p.T + kv0 + row);
-        dl_nx = __ldg(p.delta + (size_t)bh * p.T + kv0 + row);
-      }
-      if (wi > 0) {                 // the previous item's dK / dV stores have finished READING the sP / sdS staging tiles
-        if (ctid == 0) tma_store_wait_read<0>();
-        named_bar_sync(1, 256);
-      }
+      // row statistics of the NEXT query tile are fetched while the current one is processed (the first tile's while the
+      // previous item's epilogue ran)
+      float lse_nx = lse_first, dl_nx = dl_first;
       for (int it = 0; it < n_it; ++it) {
         const uint32_t ph = (g0 + it) & 1;
         const int q0 = (jt + it) * kAttTile;
@@ -730,22 +855,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         lse_nx = 0.f;
         dl_nx = 0.f;
         if (it + 1 < n_it && q0 + kAttTile + row < p.T) {
-          lse_nx = __ldg(p.lse + (size_t)bh * p.T + q0 + kAttTile + row);
-          dl_nx = __ldg(p.delta + (size_t)bh * p.T + q0 + kAttTile + row);
+          lse_nx = ldg_pinned(p.lse + (size_t)bh * p.T + q0 + kAttTile + row);
+          dl_nx = ldg_pinned(p.delta + (size_t)bh * p.T + q0 + kAttTile + row);
         }
-        mbar_wait(sdp_full, ph);
-        tc_fence_after();
-        if (it == 0) bwd_softmax_half<true>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale,
-                                            p.scale_log2, p_free, ds_free, ph ^ 1, false);
-        else bwd_softmax_half<false>(tmem_s + lane_sel, tmem_dp + lane_sel, pblk, dsblk, row, half, lse2, dl, p.scale, p.scale_log2,
-                                     p_free, ds_free, ph ^ 1, true);
-        tc_fence_before();
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(pds_ready);
-        if (it > 0) drain_dq(it - 1);         // its product finished while this tile's P / dS were computed
+        float pv[64];
+        if (it == 0) bwd_pass_a<true>(pv, tmem_s + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, false,
+                                      wi > 0, ctid);
+        else bwd_pass_a<false>(pv, tmem_s + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, true, false,
+                               ctid);
+        bwd_pass_b(pv, tmem_dp + lane_sel, dsblk, row, half, lane, dl, dp_full, dp_cons, p_ready, ph, ds_free, it > 0);
+        if (it > 0) {
+          drain_dq(it - 1, true);             // its product finished while this tile's P / dS were computed
+        } else {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(ds_ready);
+        }
       }
-      drain_dq(n_it - 1);
+      fetch_first(w + gridDim.x);
+      drain_dq(n_it - 1, false);
       // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) -> bf16 -> TMA store into dqkv
       mbar_wait(dkv_full, wi & 1);
       tc_fence_after();
@@ -759,33 +887,52 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(dkv_empty);                  // the next item's first dV / dK may overwrite the accumulators
+        const float sc = half == 0 ? 1.f : p.scale;             // dS was stored without 1/sqrt(D): dK takes the factor here
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 pk = {pack_bf16(__uint_as_float(r0[8 * q4 + 0]), __uint_as_float(r0[8 * q4 + 1])),
-                      pack_bf16(__uint_as_float(r0[8 * q4 + 2]), __uint_as_float(r0[8 * q4 + 3])),
-                      pack_bf16(__uint_as_float(r0[8 * q4 + 4]), __uint_as_float(r0[8 * q4 + 5])),
-                      pack_bf16(__uint_as_float(r0[8 * q4 + 6]), __uint_as_float(r0[8 * q4 + 7]))};
+          uint4 pk = {pack_bf16(sc * __uint_as_float(r0[8 * q4 + 0]), sc * __uint_as_float(r0[8 * q4 + 1])),
+                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 2]), sc * __uint_as_float(r0[8 * q4 + 3])),
+                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 4]), sc * __uint_as_float(r0[8 * q4 + 5])),
+                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 6]), sc * __uint_as_float(r0[8 * q4 + 7]))};
           st_swizzled_row_piece(stage, row, q4, pk);
-          uint4 pk1 = {pack_bf16(__uint_as_float(r1[8 * q4 + 0]), __uint_as_float(r1[8 * q4 + 1])),
-                       pack_bf16(__uint_as_float(r1[8 * q4 + 2]), __uint_as_float(r1[8 * q4 + 3])),
-                       pack_bf16(__uint_as_float(r1[8 * q4 + 4]), __uint_as_float(r1[8 * q4 + 5])),
-                       pack_bf16(__uint_as_float(r1[8 * q4 + 6]), __uint_as_float(r1[8 * q4 + 7]))};
+          uint4 pk1 = {pack_bf16(sc * __uint_as_float(r1[8 * q4 + 0]), sc * __uint_as_float(r1[8 * q4 + 1])),
+                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 2]), sc * __uint_as_float(r1[8 * q4 + 3])),
+                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 4]), sc * __uint_as_float(r1[8 * q4 + 5])),
+                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 6]), sc * __uint_as_float(r1[8 * q4 + 7]))};
           st_swizzled_row_piece(stage, row, 4 + q4, pk1);
         }
         fence_proxy_async_smem();
         named_bar_sync(1, 256);
         if (p.dbias != nullptr) {
-          // column sums of the two bf16 tiles just staged (the values as stored): thread = (tile, half of the rows, column)
-          const int tile = ctid >> 7, rh = (ctid >> 6) & 1, col = ctid & 63;
+          // column sums of the two bf16 tiles just staged (the values as stored): thread = (tile, 8 rows, 8-column chunk),
+          // 16-byte loads, the four row groups of a warp combined with shuffles, one atomic per column and warp
+          const int tile = ctid >> 7, t7 = ctid & 127, ch = t7 & 7, rg = t7 >> 3;
           const uint8_t* src8 = tile == 0 ? sP : sdS;
-          float acc = 0.f;
-#pragma unroll 8
-          for (int r0i = 0; r0i < 64; ++r0i) {
-            const int rr = rh * 64 + r0i;
-            const __nv_bfloat16 v = *reinterpret_cast<const __nv_bfloat16*>(src8 + rr * 128 + (((col >> 3) ^ (rr & 7)) << 4) + (col & 7) * 2);
-            acc += __bfloat162float(v);
+          float acc[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+          for (int r0i = 0; r0i < 8; ++r0i) {
+            const int rr = rg * 8 + r0i;
+            const uint4 q = *reinterpret_cast<const uint4*>(src8 + rr * 128 + ((ch ^ (rr & 7)) << 4));
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = __bfloat1622float2(h2[j]);
+              acc[2 * j] += f.x;
+              acc[2 * j + 1] += f.y;
+            }
           }
-          atomicAdd(p.dbias + ((tile == 0 ? 2 : 1) * p.H + h) * kAttD + col, acc);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 8);
+            acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 16);
+          }
+          if (lane < 8) {
+            float* dst = p.dbias + ((tile == 0 ? 2 : 1) * p.H + h) * kAttD + ch * 8;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) atomicAdd(dst + j, acc[j]);
+          }
         }
         if (ctid == 0) {
           tma_store_4d(&tmDQKV, sP, 0, kv0, 2 * p.H + h, b);    // dV
@@ -795,7 +942,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
       g0 += n_it;
     }
-    if (ctid == 0) tma_store_wait<0>();
+    if (lane == 0) tma_store_wait<0>();        // every warp issued dQ reduces of its own (warp 2 also the dK / dV stores)
   }
 
   tc_fence_before();
@@ -874,7 +1021,7 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
     const uint64_t row = (uint64_t)H * kAttD * 4;
     uint64_t dims[4] = {(uint64_t)kAttD, (uint64_t)T, (uint64_t)H, (uint64_t)B};
     uint64_t str[3] = {row, (uint64_t)kAttD * 4, (uint64_t)T * row};
-    uint32_t box[4] = {32, (uint32_t)kAttTile, 1, 1};
+    uint32_t box[4] = {32, 32, 1, 1};                           // one compute warp's slab: 32 query rows x 32 columns of d
     if (encode_tmap(&tmDQ, dq_acc, 1, 4, dims, str, box, nullptr, 1)) return 4;
   }
   AttnBwdParams p;
@@ -904,7 +1051,8 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
   const int cthreads = vpr * (256 / vpr);                      // whole rows per block iteration
   long blocks = ((long)B * T + (256 / vpr) - 1) / (256 / vpr);
   if (blocks > num_sms() * 4) blocks = num_sms() * 4;
-  attn_dq_convert_kernel<<<(unsigned)blocks, cthreads, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H, dbias);
+  attn_dq_convert_kernel<<<(unsigned)blocks, cthreads, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H, dbias,
+                                                                   p.scale);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
