@@ -382,7 +382,8 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // A thread keeps ONE 8-column vector of the row and walks down the rows, so it can also sum its columns of dQ (the values as
 // stored) for the bias gradient of the QKV projection: `dbias` (nullable) fp32 [3*H*64], part [0, H*64) is added to.
 __global__ void __launch_bounds__(256) attn_dq_convert_kernel(float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long rows_bt,
-                                                              int H, float* __restrict__ dbias, float scale) {
+                                                              int H, float* __restrict__ dbias, float scale, int* __restrict__ ticket) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) *ticket = 0;        // the backward kernel's item counter: zero again for the next call
   __shared__ float sh_sum[2048];                               // [H*64] block-level column sums (H*64 <= 2048)
   const int vpr = H * kAttD / 8;                               // 8-element vectors per (b, t) row
   const int rows_per_iter = blockDim.x / vpr;                  // blockDim is a multiple of vpr: a thread's columns never change
@@ -461,6 +462,8 @@ struct AttnBwdParams {
   int n_qt;
   float scale;           // 1 / sqrt(D)
   float scale_log2;      // scale * log2(e)
+  int* ticket;           // work-item counter of the persistent grid (zero on entry; the convert kernel clears it again)
+  long long* dbg;        // nullable: per-CTA cycle counters of compute warp 2 (dfb_attn_bwd_set_debug), 8 words per CTA
 };
 
 // Packed fp32 pairs (one issue slot for two lanes of arithmetic; the compute warps are issue-bound, r2 ncu).
@@ -593,7 +596,7 @@ constexpr int kBwdStages = 3;
 // Tried and dropped (r2): a second fixed K/V buffer paid for by aliasing the dQ staging tile onto P: every P store then
 // waited for the TMA reduce issued a few hundred cycles earlier (0.378 vs 0.370 ms at T = 1024, 656 vs 762 TFLOP/s at 8192).
 constexpr int kBwdPool = kBwdStages + 1;
-constexpr int kBwdSmem = kBwdPool * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 256 + 1024;
+constexpr int kBwdSmem = kBwdPool * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 512 + 1024;
 
 struct BwdPool {                      // the allocation sequence, replayed identically by the producer and the MMA thread
   int next = 0;                       // round-robin cursor
@@ -633,17 +636,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint64_t* s_cons = bars + 17;       // every compute warp has read S_i out of TMEM: S_{i+1} may overwrite it
   uint64_t* dp_cons = bars + 18;      // ... and dP_i
   uint64_t* ds_ready = bars + 19;     // dS_i written to sdS
+  uint64_t* item_bar = bars + 32;     // [8] the producer has published the CTA's k-th work item in item_ring[k & 7]
+  volatile int* item_ring = reinterpret_cast<volatile int*>(bars + 40);
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // Persistent: one CTA per SM walks the work items w = blockIdx.x, + gridDim.x, ... of the list (key tile, batch*head) sorted
-  // heaviest first (key tile 0 meets every query tile).  Barrier phases run on across items: `g0` = query tiles this CTA has
+  // Persistent: one CTA per SM walks work items of the list (key tile, batch*head) sorted heaviest first (key tile 0 meets
+  // every query tile).  The first item is blockIdx.x, the following ones come from a global ticket counter: the producer
+  // thread draws the CTA's next item when it moves on to it (about one item ahead of the compute warps) and publishes it in
+  // a small shared-memory ring for the MMA thread and the compute warps.  With the static list w += gridDim.x the slowest
+  // CTA took 12 % longer than the average one (r2 cycle counters: 517 k vs 462 k cycles).  Barrier phases run on across items: `g0` = query tiles this CTA has
   // processed before the item.  The producer and the MMA thread start on the next item (K/V, Q/dO, S/dP) while the compute
   // warps still drain the last dQ and store dK / dV of the previous one; one CTA per item spent ~8 us per CTA on launch, TMEM
   // allocation, first loads, pipeline ramp and store drain (half of the run at T = 1024).
   const int bh_total = p.B * p.H;
   const int n_items = p.n_qt * bh_total;
+  const bool dynamic = (int)gridDim.x < n_items;      // one CTA per item (long sequences): nothing to draw
+  auto item_of = [&](int k) {                         // the CTA's k-th work item (>= n_items: no more), as published by the producer
+    mbar_wait(&item_bar[k & 7], (k >> 3) & 1);
+    return (int)item_ring[k & 7];
+  };
 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
@@ -666,6 +679,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(dkv_empty, 8);
     mbar_init(p_free, 1);
     mbar_init(ds_free, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(&item_bar[i], 1);
     fence_mbar_init();
   }
   if (warp_idx == 1) tmem_alloc<kBwdTmemCols>(tmem_ptr);
@@ -689,7 +703,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         tma_load_4d(sPool + slot * kBwdStageBytes, tm_a, &slot_full[slot], 0, row0, c2_a, b);
         tma_load_4d(sPool + slot * kBwdStageBytes + kAttTileBytes, tm_b, &slot_full[slot], 0, row0, c2_b, b);
       };
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      int w = blockIdx.x;
+      for (int k = 0;; ++k) {
+        item_ring[k & 7] = w;                                   // published even when it is past the end: the others stop on it
+        mbar_arrive(&item_bar[k & 7]);
+        if (w >= n_items) break;
         const int jt = w / bh_total, bh = w % bh_total;
         const int b = bh / p.H, h = bh % p.H;
         const int n_it = p.n_qt - jt;
@@ -700,6 +718,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         // the tile whose S product should be running while the previous item's epilogue drains
         for (int it = 0; it < n_it; ++it)
           fill(pool.take(kv_slot, it == 0 ? kv_prev : -1), &tmQKV, h, &tmDO, h, (jt + it) * kAttTile, b);
+        w = dynamic ? (int)gridDim.x + atomicAdd(p.ticket, 1) : n_items;
       }
     }
   } else if (warp_idx == 1) {
@@ -740,7 +759,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         umma_commit(dp_full);
       };
       int g0 = 0, wi = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++wi) {
+      for (int w = item_of(0); w < n_items; w = item_of(++wi)) {
         const int n_it = p.n_qt - w / bh_total;
         const int kv_prev = kv_slot;
         kv_slot = pool.take(kv_prev);
@@ -812,8 +831,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         dl_first = ldg_pinned(p.delta + (size_t)(w % bh_total) * p.T + r);
       }
     };
-    fetch_first(blockIdx.x);
-    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++wi) {
+    int w_next = item_of(0);
+    fetch_first(w_next);
+    const bool dbg_on = p.dbg != nullptr && ctid == 0;
+    long long t_k0 = dbg_on ? clock64() : 0, t_loop = 0, t_epi = 0, t_first = 0, t_wait_tail = 0, t_item0 = 0;
+    for (int w = w_next; w < n_items; w = w_next, ++wi) {
+      if (dbg_on) t_item0 = clock64();
       const int jt = w / bh_total, bh = w % bh_total;
       const int b = bh / p.H, h = bh % p.H;
       const int kv0 = jt * kAttTile;
@@ -870,13 +893,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(ds_ready);
+          if (dbg_on) t_first += clock64() - t_item0;
         }
       }
-      fetch_first(w + gridDim.x);
-      drain_dq(n_it - 1, false);
+      long long t_e0 = 0;
+      if (dbg_on) { t_e0 = clock64(); t_loop += t_e0 - t_item0; }
+      w_next = item_of(wi + 1);             // drawn by the producer when it moved on to that item: long published
+      fetch_first(w_next);
+      drain_dq(n_it - 1, false);            // (after the dK / dV epilogue instead: measured slower, 6200 vs 4500 cycles per item tail)
       // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) -> bf16 -> TMA store into dqkv
       mbar_wait(dkv_full, wi & 1);
       tc_fence_after();
+      if (dbg_on) t_wait_tail += clock64() - t_e0;
       {
         uint8_t* stage = half == 0 ? sP : sdS;                  // both free: every MMA of the item has completed
         const uint32_t src = (half == 0 ? tmem_dv : tmem_dk) + lane_sel;
@@ -941,6 +969,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
       }
       g0 += n_it;
+      if (dbg_on) t_epi += clock64() - t_e0;
+    }
+    if (dbg_on) {
+      long long* d = p.dbg + (size_t)blockIdx.x * 8;
+      d[0] = clock64() - t_k0; d[1] = t_loop; d[2] = t_epi; d[3] = t_first; d[4] = t_wait_tail; d[5] = g0; d[6] = wi;
     }
     if (lane == 0) tma_store_wait<0>();        // every warp issued dQ reduces of its own (warp 2 also the dK / dV stores)
   }
@@ -997,10 +1030,18 @@ DFB_API int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, i
   return 0;
 }
 
+// Profiling aid: compute warp 2 of every CTA of the backward kernel writes cycle counters {kernel, tile loops, item tails,
+// first tiles, tail waits, tiles, items} to buf[cta * 8 ..] (int64, >= 8 * CTAs words); nullptr switches it off.
+static long long* g_attn_bwd_dbg = nullptr;
+DFB_API int dfb_attn_bwd_set_debug(long long* buf) {
+  g_attn_bwd_dbg = buf;
+  return 0;
+}
+
 DFB_API size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D) {
   // delta [B,H,T] fp32 (rounded to 256 B) + dQ accumulator [B,T,H,D] fp32
   const size_t delta = (((size_t)B * H * T * 4) + 255) / 256 * 256;
-  return delta + (size_t)B * T * H * D * 4;
+  return delta + (size_t)B * T * H * D * 4 + 256;               // + the work-item counter of the persistent grid
 }
 
 // dqkv [B,T,3,H,64] bf16 (fully written).  `scratch` holds delta and the fp32 dQ accumulator; the accumulator part
@@ -1029,6 +1070,8 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
   p.n_qt = ceil_div(T, kAttTile);
   p.scale = 1.f / sqrtf((float)D);
   p.scale_log2 = p.scale * kLog2e;
+  p.dbg = g_attn_bwd_dbg;
+  p.ticket = reinterpret_cast<int*>(reinterpret_cast<char*>(scratch) + delta_bytes + (size_t)B * T * H * D * 4);
   static bool attr_done[64] = {};
   int dev = 0;
   DFB_CUDA_CHECK(cudaGetDevice(&dev));
@@ -1052,7 +1095,7 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
   long blocks = ((long)B * T + (256 / vpr) - 1) / (256 / vpr);
   if (blocks > num_sms() * 4) blocks = num_sms() * 4;
   attn_dq_convert_kernel<<<(unsigned)blocks, cthreads, 0, stream>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), (long)B * T, H, dbias,
-                                                                   p.scale);
+                                                                   p.scale, p.ticket);
   DFB_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -168,6 +168,7 @@ int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long ro
  * must be zero on entry and is zero again on return. */
 int dfb_attn_supported(int B, int T, int H, int D);
 int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
+int dfb_attn_bwd_set_debug(long long* buf);   /* profiling aid: per-CTA cycle counters of the backward kernel (8 int64 per CTA), NULL = off */
 size_t dfb_attn_bwd_scratch_bytes(int B, int T, int H, int D);
 int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv,
                  float* dbias /* nullable, fp32 [3*H*D]: receives the column sums of dqkv = bias gradient of the QKV projection */,
