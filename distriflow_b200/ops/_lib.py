@@ -14,7 +14,8 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdistriflow_b200.so")
+# DFB_LIB_PATH: another build of the same library (A/B runs of two kernel versions on one box); default: the in-tree build
+LIB_PATH = os.environ.get("DFB_LIB_PATH") or os.path.join(_HERE, "libdistriflow_b200.so")
 _lib: Optional[ctypes.CDLL] = None
 _err: Optional[str] = None
 

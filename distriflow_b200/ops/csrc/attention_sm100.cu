@@ -570,41 +570,43 @@ __device__ __forceinline__ void bwd_pass_b(float (&pv)[64], uint32_t tmem_dp_lan
   }
 }
 
-// Work item = (128 key rows, head, batch), one persistent CTA per SM.  K_j and V_j stay in shared memory; the CTA walks the query
-// tiles i = j .. n-1 (causal) and per tile issues five products:
-//     S  = Q_i K_j^T          dP = dO_i V_j^T                      (fresh accumulators, TMEM columns [0,128) / [128,256))
-//     dV += P^T dO_i          dK += dS^T Q_i                        (accumulate over i, columns [256,320) / [320,384))
-//     dQ_i = dS K_j                                                  (fresh, columns [384,448); added to the fp32 dQ
-//                                                                     accumulator in global memory with a TMA reduce-add)
-// with P = exp2(S*c - lse*log2e) and dS = P * (dP - delta) / sqrt(D) computed by eight warps between the two groups
-// (thread = query row x half of the key columns).  P and dS are written once to shared memory and read by the tensor core
-// both as K-major (dS K) and as MN-major (P^T dO, dS^T Q) operands.
-//   warp 0      TMA producer: K_j, V_j, then a 2-stage ring of {Q_i, dO_i}
+// Work item = (PAIR of adjacent 128-row key tiles ja = 2*jp, jb = ja + 1, head, batch), one persistent CTA per SM.  Both
+// K/V pairs stay in shared memory; the CTA walks the query tiles i = ja .. n-1 (causal) and per query tile runs one
+// sub-iteration per key tile of the pair that the query tile can see (jb only from i = jb on), each with five products:
+//     S  = Q_i K^T            dP = dO_i V^T                         (fresh, ONE shared TMEM buffer, columns [0,128): dP is
+//                                                                     issued once S is in registers, the next S once dP is)
+//     dV += P^T dO_i          dK += dS^T Q_i                        (accumulate over i; per key tile: columns [128,384))
+//     dQ_i (+)= dS K                                                 (columns [384,448): fresh for the first key tile of
+//                                                                     the pair, accumulated for the second, and only then
+//                                                                     added to the fp32 dQ accumulator in global memory)
+// with P = exp2(S*c - lse*log2e) and dS = P * (dP - delta) computed by eight warps between the two groups (thread = query
+// row x half of the key columns).  P and dS are written once to shared memory and read by the tensor core both as K-major
+// (dS K) and as MN-major (P^T dO, dS^T Q) operands.
+// Why pairs: the fp32 dQ TMA reduce-add traffic (one 32 KiB tile per (query tile, key tile), 453 MB per call at the GPT-2
+// shape) bounded the one-key-tile kernel, 503 k cycles against 343 k with the reduce switched off (r2 cycle counters).
+// Summing the two key tiles of a pair in TMEM first removes 44 % of it and halves the number of work items.
+//   warp 0      TMA producer: K/V of the pair, then {Q_i, dO_i} through the free slots of the operand pool
 //   warp 1      TMEM allocation + MMA issue
 //   warps 2..9  softmax / dS, dQ drain, final dK / dV epilogue
 constexpr int kBwdThreads = 320;
-constexpr int kBwdStageBytes = 2 * kAttTileBytes;             // Q_i + dO_i
-// Three {Q_i, dO_i} stages: a stage is released by the LAST product of its tile (dK) and S of the tile after next needs it
-// early (right after the compute warps have read S of the next tile); with two stages the load sat on that path and the
-// compute warps waited 12 % of their time for S (r2 ncu: try_wait on s_full).
-constexpr int kBwdStages = 3;
-// Operand pool: kBwdPool = 4 slots of 32 KiB, each holding either {K_j, V_j} of an item (pinned for the whole item) or
-// {Q_i, dO_i} of a tile.  Slots are handed out round robin, skipping the pinned one, so the NEXT item's K/V pair is loaded
-// into an ordinary slot while the current item's last tiles run (with a fixed K/V buffer every item started with a load + S
-// product that nothing overlapped: 14 % of the run at T = 1024, r2 ncu) and the old K/V slot joins the rotation afterwards.
-// Producer and MMA thread replay the same allocation sequence: K/V(w), tiles of w, K/V(w+1), ...
+constexpr int kBwdStageBytes = 2 * kAttTileBytes;             // {K, V} or {Q_i, dO_i}
+// Operand pool: 4 slots of 32 KiB.  Two are pinned by the item's K/V pairs, {Q_i, dO_i} alternate between the other two (a
+// query tile lasts two sub-iterations, so its successor's load has time).  Slots are handed out round robin, skipping the
+// pinned ones, so the NEXT item's first K/V pair is loaded into the slot the last-but-one query tile left, while the item's
+// last tile runs.  Producer and MMA thread replay the same allocation sequence.
 // Tried and dropped (r2): a second fixed K/V buffer paid for by aliasing the dQ staging tile onto P: every P store then
 // waited for the TMA reduce issued a few hundred cycles earlier (0.378 vs 0.370 ms at T = 1024, 656 vs 762 TFLOP/s at 8192).
-constexpr int kBwdPool = kBwdStages + 1;
+constexpr int kBwdPool = 4;
 constexpr int kBwdSmem = kBwdPool * kBwdStageBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 2 * kAttTileBytes + 512 + 1024;
 
 struct BwdPool {                      // the allocation sequence, replayed identically by the producer and the MMA thread
   int next = 0;                       // round-robin cursor
   uint32_t parity = 0, used = 0;      // bit s: (fills of slot s so far) & 1 = barrier phase of its next fill; slot filled before
-  __device__ __forceinline__ int take(int skip_a, int skip_b = -1) {
+  __device__ __forceinline__ int take(uint32_t skip_mask) {      // never all four
     int s = next;
-    if (s == skip_a || s == skip_b) s = (s + 1) % kBwdPool;
-    if (s == skip_a || s == skip_b) s = (s + 1) % kBwdPool;
+#pragma unroll
+    for (int t = 0; t < kBwdPool - 1; ++t)
+      if ((skip_mask >> s) & 1u) s = (s + 1) % kBwdPool;
     next = (s + 1) % kBwdPool;
     return s;
   }
@@ -621,37 +623,36 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   uint8_t* sdS = sP + 2 * kAttTileBytes;                                      // 32 KiB
   uint8_t* sdQ = sdS + 2 * kAttTileBytes;                                     // 32 KiB fp32 staging: d columns [0,32) then [32,64)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sdQ + 2 * kAttTileBytes);
-  uint64_t* slot_full = bars + 20;    // [kBwdPool] the slot's pair has landed
-  uint64_t* slot_empty = bars + 24;   // [kBwdPool] every product that reads the slot has completed
-  uint64_t* s_full = bars + 5;        // S_i complete in TMEM
-  uint64_t* p_ready = bars + 6;       // P_i written to sP
-  uint64_t* dq_full = bars + 7;
+  uint64_t* s_full = bars + 5;        // S of the sub-iteration complete in TMEM
+  uint64_t* p_ready = bars + 6;       // P written to sP
+  uint64_t* dq_full = bars + 7;       // dQ_i complete (both key tiles of the pair)
   uint64_t* dq_empty = bars + 8;
   uint64_t* dkv_full = bars + 9;
-  uint64_t* p_free = bars + 10;       // dV of the tile has read P: sP may be rewritten
-  uint64_t* ds_free = bars + 11;      // dQ and dK of the tile have read dS: sdS may be rewritten
+  uint64_t* p_free = bars + 10;       // dV of the sub-iteration has read P: sP may be rewritten
+  uint64_t* ds_free = bars + 11;      // dQ and dK of the sub-iteration have read dS: sdS may be rewritten
   uint64_t* dkv_empty = bars + 13;    // the epilogue has taken dV / dK of the item out of TMEM
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 15);
-  uint64_t* dp_full = bars + 16;      // dP_i complete in TMEM
-  uint64_t* s_cons = bars + 17;       // every compute warp has read S_i out of TMEM: S_{i+1} may overwrite it
-  uint64_t* dp_cons = bars + 18;      // ... and dP_i
-  uint64_t* ds_ready = bars + 19;     // dS_i written to sdS
+  uint64_t* dp_full = bars + 16;      // dP complete in TMEM
+  uint64_t* s_cons = bars + 17;       // every compute warp has read S out of TMEM: dP may overwrite it
+  uint64_t* dp_cons = bars + 18;      // ... and dP: the next S may overwrite it
+  uint64_t* ds_ready = bars + 19;     // dS written to sdS
+  uint64_t* slot_full = bars + 20;    // [kBwdPool] the slot's pair has landed
+  uint64_t* slot_empty = bars + 24;   // [kBwdPool] every product that reads the slot has completed
   uint64_t* item_bar = bars + 32;     // [8] the producer has published the CTA's k-th work item in item_ring[k & 7]
   volatile int* item_ring = reinterpret_cast<volatile int*>(bars + 40);
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // Persistent: one CTA per SM walks work items of the list (key tile, batch*head) sorted heaviest first (key tile 0 meets
+  // Persistent: one CTA per SM walks work items of the list (key-tile pair, batch*head) sorted heaviest first (pair 0 meets
   // every query tile).  The first item is blockIdx.x, the following ones come from a global ticket counter: the producer
   // thread draws the CTA's next item when it moves on to it (about one item ahead of the compute warps) and publishes it in
   // a small shared-memory ring for the MMA thread and the compute warps.  With the static list w += gridDim.x the slowest
-  // CTA took 12 % longer than the average one (r2 cycle counters: 517 k vs 462 k cycles).  Barrier phases run on across items: `g0` = query tiles this CTA has
-  // processed before the item.  The producer and the MMA thread start on the next item (K/V, Q/dO, S/dP) while the compute
-  // warps still drain the last dQ and store dK / dV of the previous one; one CTA per item spent ~8 us per CTA on launch, TMEM
-  // allocation, first loads, pipeline ramp and store drain (half of the run at T = 1024).
+  // CTA took 12 % longer than the average one (r2 cycle counters: 517 k vs 462 k cycles).  Barrier phases run on across
+  // items: `gu0` / `gq0` = sub-iterations / query tiles this CTA has processed before the item.
   const int bh_total = p.B * p.H;
-  const int n_items = p.n_qt * bh_total;
+  const int n_pairs = (p.n_qt + 1) / 2;
+  const int n_items = n_pairs * bh_total;
   const bool dynamic = (int)gridDim.x < n_items;      // one CTA per item (long sequences): nothing to draw
   auto item_of = [&](int k) {                         // the CTA's k-th work item (>= n_items: no more), as published by the producer
     mbar_wait(&item_bar[k & 7], (k >> 3) & 1);
@@ -687,14 +688,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tmem_s = tmem_base, tmem_dp = tmem_base + 128, tmem_dv = tmem_base + 256, tmem_dk = tmem_base + 320,
-                 tmem_dq = tmem_base + 384;
+  const uint32_t tmem_sdp = tmem_base, tmem_acc = tmem_base + 128, tmem_dq = tmem_base + 384;
+  // accumulators of key tile c of the pair: dV at tmem_acc + c*128, dK at tmem_acc + c*128 + 64
 
   if (warp_idx == 0) {
     // ===================================================================== TMA producer
     if (elect_one()) {
       BwdPool pool;
-      int kv_slot = -1;
+      uint32_t pins = 0;
       auto fill = [&](int slot, const CUtensorMap* tm_a, int c2_a, const CUtensorMap* tm_b, int c2_b, int row0, int b) {
         if ((pool.used >> slot) & 1u) mbar_wait_backoff(&slot_empty[slot], ((pool.parity >> slot) & 1u) ^ 1u, 128);
         pool.used |= 1u << slot;
@@ -708,16 +709,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         item_ring[k & 7] = w;                                   // published even when it is past the end: the others stop on it
         mbar_arrive(&item_bar[k & 7]);
         if (w >= n_items) break;
-        const int jt = w / bh_total, bh = w % bh_total;
+        const int jp = w / bh_total, bh = w % bh_total;
         const int b = bh / p.H, h = bh % p.H;
-        const int n_it = p.n_qt - jt;
-        const int kv_prev = kv_slot;
-        kv_slot = pool.take(kv_prev);                           // not the slot the previous item's K/V still occupy
-        fill(kv_slot, &tmQKV, p.H + h, &tmQKV, 2 * p.H + h, jt * kAttTile, b);
-        // the item's first tile must not land in the previous item's K/V slot either (free only when that item ends): it is
-        // the tile whose S product should be running while the previous item's epilogue drains
-        for (int it = 0; it < n_it; ++it)
-          fill(pool.take(kv_slot, it == 0 ? kv_prev : -1), &tmQKV, h, &tmDO, h, (jt + it) * kAttTile, b);
+        const int ja = 2 * jp, jb = ja + 1;
+        const bool has_b = jb < p.n_qt;
+        const uint32_t old_pins = pins;                         // still in use until the previous item ends
+        const int kva = pool.take(old_pins);
+        fill(kva, &tmQKV, p.H + h, &tmQKV, 2 * p.H + h, ja * kAttTile, b);
+        pins = 1u << kva;
+        if (has_b) {
+          const int kvb = pool.take(old_pins | pins);
+          fill(kvb, &tmQKV, p.H + h, &tmQKV, 2 * p.H + h, jb * kAttTile, b);
+          pins |= 1u << kvb;
+        }
+        for (int i = ja; i < p.n_qt; ++i) fill(pool.take(pins), &tmQKV, h, &tmDO, h, i * kAttTile, b);
         w = dynamic ? (int)gridDim.x + atomicAdd(p.ticket, 1) : n_items;
       }
     }
@@ -727,87 +732,104 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);      // S, dP
       const uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);       // dV = P^T dO, dK = dS^T Q  (both operands MN-major)
       const uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);       // dQ = dS K
-      uint64_t dk_kmaj = 0, dv_kmaj = 0, dk_mn = 0;                  // K_j / V_j descriptors: the current item's slot
+      const uint64_t dp_mn = make_smem_desc_sw128(smem_u32(sP), kAttTileBytes, 1024);         // A MN-major: two 64-wide atoms
+      const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
+      const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
+      const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
       BwdPool pool;
-      int kv_slot = -1, slot_cur = 0, slot_nxt = 0;                  // slots of the current and the next tile's {Q, dO}
+      uint32_t pins = 0;
       auto claim = [&](int slot) {                                   // wait until the fill of `slot` that is next in sequence has landed
         mbar_wait(&slot_full[slot], (pool.parity >> slot) & 1u);
         pool.parity ^= 1u << slot;
         tc_fence_after();
       };
-      const uint64_t dp_mn = make_smem_desc_sw128(smem_u32(sP), kAttTileBytes, 1024);         // A MN-major: two 64-wide atoms
-      const uint64_t dds_mn = make_smem_desc_sw128(smem_u32(sdS), kAttTileBytes, 1024);
-      const uint64_t dds_k0 = make_smem_desc_sw128(smem_u32(sdS), 0, 1024);                    // A K-major: two 64-k blocks
-      const uint64_t dds_k1 = make_smem_desc_sw128(smem_u32(sdS + kAttTileBytes), 0, 1024);
-      // Issue order per query tile i, software-pipelined against the compute warps.  S and dP have one TMEM buffer each, so
-      // the next tile's products are issued as soon as the compute warps have READ the current ones (not when they are done
-      // with them): S_{i+1} runs under the exponentials of tile i, dP_{i+1} under its dS arithmetic and the dQ drain.
-      //   [S_i read]   S_{i+1}   ->  [P_i in smem]  dV += P_i^T dO_i  (P free)
-      //   [dP_i read]  dP_{i+1}  ->  [dS_i in smem, dQ_{i-1} drained]  dQ_i = dS_i K  ->  dK += dS_i^T Q_i  (dS, Q_i / dO_i free)
-      // r2 ncu, before: S_{i+1} / dP_{i+1} were issued together after BOTH P_i and dS_i were stored; a tile took 4100 cycles
-      // against 1280 cycles of tensor-core work and ~2000 issue cycles of the compute warps, the rest was this round trip.
-      auto issue_s = [&](int slot) {          // the slot has been claimed
+      // Issue order per sub-iteration u (query tile i, key tile c), software-pipelined against the compute warps:
+      //   [S_u read]   dP_u      ->  [P_u in smem]   dV_c += P_u^T dO_i  (P free)
+      //   [dP_u read]  S_{u+1}   ->  [dS_u in smem; first key tile of i: dQ_{i-1} drained]  dQ_i (+)= dS_u K_c  ->  dK_c += dS_u^T Q_i
+      // so dP runs under the exponentials of its own sub-iteration and the next S under the dS arithmetic and the dQ drain.
+      auto issue_s = [&](int slot, int kv) {  // both slots have been claimed
         const uint64_t dq_kmaj = make_smem_desc_sw128(smem_u32(sPool + slot * kBwdStageBytes), 0, 1024);
+        const uint64_t dk_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv * kBwdStageBytes), 0, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_f16(tmem_s, dq_kmaj + (uint64_t)(k * 2), dk_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) umma_f16(tmem_sdp, dq_kmaj + (uint64_t)(k * 2), dk_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
-      auto issue_dp = [&](int slot) {
+      auto issue_dp = [&](int slot, int kv) {
         const uint64_t ddo_kmaj = make_smem_desc_sw128(smem_u32(sPool + slot * kBwdStageBytes + kAttTileBytes), 0, 1024);
+        const uint64_t dv_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv * kBwdStageBytes + kAttTileBytes), 0, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_f16(tmem_dp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) umma_f16(tmem_sdp, ddo_kmaj + (uint64_t)(k * 2), dv_kmaj + (uint64_t)(k * 2), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(dp_full);
       };
-      int g0 = 0, wi = 0;
+      int gu = 0, gq = 0, wi = 0;
       for (int w = item_of(0); w < n_items; w = item_of(++wi)) {
-        const int n_it = p.n_qt - w / bh_total;
-        const int kv_prev = kv_slot;
-        kv_slot = pool.take(kv_prev);
-        claim(kv_slot);
-        dk_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes), 0, 1024);
-        dv_kmaj = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes + kAttTileBytes), 0, 1024);
-        dk_mn = make_smem_desc_sw128(smem_u32(sPool + kv_slot * kBwdStageBytes), kAttTileBytes, 1024);
-        slot_cur = pool.take(kv_slot, kv_prev);
+        const int ja = 2 * (w / bh_total), jb = ja + 1;
+        const bool has_b = jb < p.n_qt;
+        const uint32_t old_pins = pins;
+        const int kva = pool.take(old_pins);
+        pins = 1u << kva;
+        int kvb = kva;
+        if (has_b) {
+          kvb = pool.take(old_pins | pins);
+          pins |= 1u << kvb;
+        }
+        bool kvb_claimed = false;                 // claimed when its first S is due: its load may have started late
+        claim(kva);
+        int slot_cur = pool.take(pins), slot_nxt = 0;
         claim(slot_cur);
-        issue_s(slot_cur);                        // S / dP columns are free: the previous item's last s_cons / dp_cons were waited for
-        issue_dp(slot_cur);
-        for (int it = 0; it < n_it; ++it) {
-          const int g = g0 + it;
-          const uint32_t ph = g & 1;
+        issue_s(slot_cur, kva);                   // the S/dP columns are free: the previous item's last dp_cons was waited for
+        for (int i = ja; i < p.n_qt; ++i, ++gq) {
+          const int nsub = (has_b && i >= jb) ? 2 : 1;
           const uint64_t dq_mn = make_smem_desc_sw128(smem_u32(sPool + slot_cur * kBwdStageBytes), kAttTileBytes, 1024);
           const uint64_t ddo_mn = make_smem_desc_sw128(smem_u32(sPool + slot_cur * kBwdStageBytes + kAttTileBytes), kAttTileBytes, 1024);
-          mbar_wait_backoff(s_cons, ph, 32);      // S_i is in the compute warps' registers
-          if (it + 1 < n_it) {
-            slot_nxt = pool.take(kv_slot);
-            claim(slot_nxt);
-            issue_s(slot_nxt);
+          for (int c = 0; c < nsub; ++c, ++gu) {
+            const uint32_t ph = gu & 1;
+            const int kv = c == 0 ? kva : kvb;
+            const bool first_use = c == 0 ? i == ja : i == jb;          // of this key tile's dV / dK accumulators in the item
+            const uint32_t tmem_dv = tmem_acc + c * 128, tmem_dk = tmem_dv + 64;
+            const uint64_t dk_mn = make_smem_desc_sw128(smem_u32(sPool + kv * kBwdStageBytes), kAttTileBytes, 1024);
+            mbar_wait_backoff(s_cons, ph, 32);    // S is in the compute warps' registers
+            tc_fence_after();
+            issue_dp(slot_cur, kv);
+            mbar_wait_backoff(p_ready, ph, 32);   // P written
+            if (i == ja && wi > 0) mbar_wait(dkv_empty, (wi - 1) & 1);   // the previous item's dV / dK have left TMEM
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < 8; ++k)     // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
+              umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (!first_use || k > 0) ? 1u : 0u);
+            umma_commit(p_free);
+            mbar_wait_backoff(dp_cons, ph, 32);   // dP is in registers: the next S may take the columns
+            tc_fence_after();
+            if (c + 1 < nsub) {
+              if (!kvb_claimed) {
+                claim(kvb);
+                kvb_claimed = true;
+              }
+              issue_s(slot_cur, kvb);
+            } else if (i + 1 < p.n_qt) {
+              slot_nxt = pool.take(pins);
+              claim(slot_nxt);
+              issue_s(slot_nxt, kva);
+            }
+            mbar_wait_backoff(ds_ready, ph, 32);  // dS written
+            if (c == 0 && gq > 0) mbar_wait(dq_empty, (gq & 1) ^ 1);   // the compute warps have taken the previous dQ out of TMEM
+            tc_fence_after();
+#pragma unroll
+            for (int k = 0; k < 8; ++k)     // dQ[q, d] (+)= sum_kv dS[q, kv] K[kv, d]
+              umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q,
+                       (c > 0 || k > 0) ? 1u : 0u);
+            if (c + 1 == nsub) umma_commit(dq_full);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)     // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
+              umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (!first_use || k > 0) ? 1u : 0u);
+            umma_commit(ds_free);
           }
-          mbar_wait_backoff(p_ready, ph, 32);     // P_i written
-          if (it == 0 && wi > 0) mbar_wait(dkv_empty, (wi - 1) & 1);   // the previous item's dV / dK have left TMEM
-          tc_fence_after();
-#pragma unroll
-          for (int k = 0; k < 8; ++k)       // dV[kv, d] += sum_q P[q, kv] dO[q, d]: 16 query rows per step in both operands
-            umma_f16(tmem_dv, dp_mn + (uint64_t)(k * 128), ddo_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
-          umma_commit(p_free);
-          mbar_wait_backoff(dp_cons, ph, 32);     // dP_i is in registers
-          if (it + 1 < n_it) issue_dp(slot_nxt);
-          mbar_wait_backoff(ds_ready, ph, 32);    // dS_i written
-          if (g > 0) mbar_wait(dq_empty, ph ^ 1); // the compute warps have taken the previous dQ out of TMEM
-          tc_fence_after();
-#pragma unroll
-          for (int k = 0; k < 8; ++k)       // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
-            umma_f16(tmem_dq, (k < 4 ? dds_k0 : dds_k1) + (uint64_t)((k & 3) * 2), dk_mn + (uint64_t)(k * 128), idesc_q, k > 0 ? 1u : 0u);
-          umma_commit(dq_full);
-#pragma unroll
-          for (int k = 0; k < 8; ++k)       // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
-            umma_f16(tmem_dk, dds_mn + (uint64_t)(k * 128), dq_mn + (uint64_t)(k * 128), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
-          umma_commit(ds_free);
-          umma_commit(&slot_empty[slot_cur]);     // Q_i / dO_i: dK was their last reader
+          umma_commit(&slot_empty[slot_cur]);     // Q_i / dO_i: the last dK was their last reader
           slot_cur = slot_nxt;
         }
-        umma_commit(&slot_empty[kv_slot]);        // K_j / V_j
+        umma_commit(&slot_empty[kva]);            // K / V of the pair
+        if (has_b) umma_commit(&slot_empty[kvb]);
         umma_commit(dkv_full);
-        g0 += n_it;
       }
     }
   } else {
@@ -819,13 +841,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const int ctid = threadIdx.x - 64;                          // 0..255
     uint8_t* pblk = sP + half * kAttTileBytes;
     uint8_t* dsblk = sdS + half * kAttTileBytes;
-    int g0 = 0, wi = 0;
+    int gu = 0, gq0 = 0, wi = 0;
     float lse_first = 0.f, dl_first = 0.f;                      // row statistics of the first (diagonal) query tile of item `w`
     auto fetch_first = [&](int w) {
       lse_first = 0.f;
       dl_first = 0.f;
       if (w >= n_items) return;
-      const int r = (w / bh_total) * kAttTile + row;
+      const int r = 2 * (w / bh_total) * kAttTile + row;
       if (r < p.T) {
         lse_first = ldg_pinned(p.lse + (size_t)(w % bh_total) * p.T + r);
         dl_first = ldg_pinned(p.delta + (size_t)(w % bh_total) * p.T + r);
@@ -837,15 +859,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     long long t_k0 = dbg_on ? clock64() : 0, t_loop = 0, t_epi = 0, t_first = 0, t_wait_tail = 0, t_item0 = 0;
     for (int w = w_next; w < n_items; w = w_next, ++wi) {
       if (dbg_on) t_item0 = clock64();
-      const int jt = w / bh_total, bh = w % bh_total;
+      const int jp = w / bh_total, bh = w % bh_total;
       const int b = bh / p.H, h = bh % p.H;
-      const int kv0 = jt * kAttTile;
-      const int n_it = p.n_qt - jt;
-      // dQ of local tile t: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator.  Every warp stages and reduces
-      // its own 32 rows x 32 columns (a 4 KiB slab of the swizzled staging tile): no barrier across warps in the tile loop.
+      const int ja = 2 * jp, jb = ja + 1;
+      const bool has_b = jb < p.n_qt;
+      const int n_q = p.n_qt - ja;
+      // dQ of local query tile t: TMEM -> fp32 staging -> TMA reduce-add into the global accumulator.  Every warp stages and
+      // reduces its own 32 rows x 32 columns (a 4 KiB slab of the swizzled staging tile): no barrier across warps in the loop.
       // `publish_ds`: the fence that makes the staging slab visible to the TMA also publishes this warp's dS stores.
       auto drain_dq = [&](int t, bool publish_ds) {
-        mbar_wait(dq_full, (g0 + t) & 1);
+        mbar_wait(dq_full, (gq0 + t) & 1);
         tc_fence_after();
         uint32_t r[32];
         tmem_ld_32x32(tmem_dq + lane_sel + half * 32, r);
@@ -864,91 +887,103 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         __syncwarp();
         if (lane == 0) {
           if (publish_ds) mbar_arrive(ds_ready);
-          tma_reduce_add_4d(&tmDQ, blk + quarter * 4096, half * 32, (jt + t) * kAttTile + quarter * 32, h, b);
+          tma_reduce_add_4d(&tmDQ, blk + quarter * 4096, half * 32, (ja + t) * kAttTile + quarter * 32, h, b);
           tma_store_commit();
         }
       };
       // row statistics of the NEXT query tile are fetched while the current one is processed (the first tile's while the
       // previous item's epilogue ran)
       float lse_nx = lse_first, dl_nx = dl_first;
-      for (int it = 0; it < n_it; ++it) {
-        const uint32_t ph = (g0 + it) & 1;
-        const int q0 = (jt + it) * kAttTile;
+      bool first_u = true;
+      for (int t = 0; t < n_q; ++t) {
+        const int i = ja + t;
+        const int q0 = i * kAttTile;
         const float lse2 = lse_nx * kLog2e, dl = dl_nx;
         lse_nx = 0.f;
         dl_nx = 0.f;
-        if (it + 1 < n_it && q0 + kAttTile + row < p.T) {
+        if (t + 1 < n_q && q0 + kAttTile + row < p.T) {
           lse_nx = ldg_pinned(p.lse + (size_t)bh * p.T + q0 + kAttTile + row);
           dl_nx = ldg_pinned(p.delta + (size_t)bh * p.T + q0 + kAttTile + row);
         }
-        float pv[64];
-        if (it == 0) bwd_pass_a<true>(pv, tmem_s + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, false,
-                                      wi > 0, ctid);
-        else bwd_pass_a<false>(pv, tmem_s + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, true, false,
-                               ctid);
-        bwd_pass_b(pv, tmem_dp + lane_sel, dsblk, row, half, lane, dl, dp_full, dp_cons, p_ready, ph, ds_free, it > 0);
-        if (it > 0) {
-          drain_dq(it - 1, true);             // its product finished while this tile's P / dS were computed
-        } else {
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(ds_ready);
-          if (dbg_on) t_first += clock64() - t_item0;
+        const int nsub = (has_b && i >= jb) ? 2 : 1;
+        for (int c = 0; c < nsub; ++c, ++gu) {
+          const uint32_t ph = gu & 1;
+          const bool diag = c == 0 ? i == ja : i == jb;
+          float pv[64];
+          if (diag) bwd_pass_a<true>(pv, tmem_sdp + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, !first_u,
+                                     first_u && wi > 0, ctid);
+          else bwd_pass_a<false>(pv, tmem_sdp + lane_sel, pblk, row, half, lane, lse2, p.scale_log2, s_full, s_cons, ph, p_free, !first_u,
+                                 false, ctid);
+          bwd_pass_b(pv, tmem_sdp + lane_sel, dsblk, row, half, lane, dl, dp_full, dp_cons, p_ready, ph, ds_free, !first_u);
+          if (c == 0 && t > 0) {
+            drain_dq(t - 1, true);            // its products finished while this sub-iteration's P / dS were computed
+          } else {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(ds_ready);
+          }
+          if (dbg_on && first_u) t_first += clock64() - t_item0;
+          first_u = false;
         }
       }
       long long t_e0 = 0;
       if (dbg_on) { t_e0 = clock64(); t_loop += t_e0 - t_item0; }
       w_next = item_of(wi + 1);             // drawn by the producer when it moved on to that item: long published
       fetch_first(w_next);
-      drain_dq(n_it - 1, false);            // (after the dK / dV epilogue instead: measured slower, 6200 vs 4500 cycles per item tail)
-      // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) -> bf16 -> TMA store into dqkv
+      drain_dq(n_q - 1, false);             // (after the dK / dV epilogue instead: measured slower, 6200 vs 4500 cycles per item tail)
+      // dK / dV epilogue: warps with half == 0 drain dV, half == 1 drain dK (64 columns each) of both key tiles -> bf16 -> TMA
+      // store into dqkv.  Staging: dV of key tile c in sP + c*16K, dK in sdS + c*16K (both free: every MMA of the item is done).
       mbar_wait(dkv_full, wi & 1);
       tc_fence_after();
       if (dbg_on) t_wait_tail += clock64() - t_e0;
       {
-        uint8_t* stage = half == 0 ? sP : sdS;                  // both free: every MMA of the item has completed
-        const uint32_t src = (half == 0 ? tmem_dv : tmem_dk) + lane_sel;
-        uint32_t r0[32], r1[32];
-        tmem_ld_32x32(src, r0);
-        tmem_ld_32x32(src + 32, r1);
-        tmem_ld_wait();
+        const float sc = half == 0 ? 1.f : p.scale;             // dS was stored without 1/sqrt(D): dK takes the factor here
+        for (int c = 0; c < (has_b ? 2 : 1); ++c) {
+          uint8_t* stage = (half == 0 ? sP : sdS) + c * kAttTileBytes;
+          const uint32_t src = tmem_acc + c * 128 + half * 64 + lane_sel;
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32(src, r0);
+          tmem_ld_32x32(src + 32, r1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            uint4 pk = {pack_bf16(sc * __uint_as_float(r0[8 * q4 + 0]), sc * __uint_as_float(r0[8 * q4 + 1])),
+                        pack_bf16(sc * __uint_as_float(r0[8 * q4 + 2]), sc * __uint_as_float(r0[8 * q4 + 3])),
+                        pack_bf16(sc * __uint_as_float(r0[8 * q4 + 4]), sc * __uint_as_float(r0[8 * q4 + 5])),
+                        pack_bf16(sc * __uint_as_float(r0[8 * q4 + 6]), sc * __uint_as_float(r0[8 * q4 + 7]))};
+            st_swizzled_row_piece(stage, row, q4, pk);
+            uint4 pk1 = {pack_bf16(sc * __uint_as_float(r1[8 * q4 + 0]), sc * __uint_as_float(r1[8 * q4 + 1])),
+                         pack_bf16(sc * __uint_as_float(r1[8 * q4 + 2]), sc * __uint_as_float(r1[8 * q4 + 3])),
+                         pack_bf16(sc * __uint_as_float(r1[8 * q4 + 4]), sc * __uint_as_float(r1[8 * q4 + 5])),
+                         pack_bf16(sc * __uint_as_float(r1[8 * q4 + 6]), sc * __uint_as_float(r1[8 * q4 + 7]))};
+            st_swizzled_row_piece(stage, row, 4 + q4, pk1);
+          }
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(dkv_empty);                  // the next item's first dV / dK may overwrite the accumulators
-        const float sc = half == 0 ? 1.f : p.scale;             // dS was stored without 1/sqrt(D): dK takes the factor here
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 pk = {pack_bf16(sc * __uint_as_float(r0[8 * q4 + 0]), sc * __uint_as_float(r0[8 * q4 + 1])),
-                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 2]), sc * __uint_as_float(r0[8 * q4 + 3])),
-                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 4]), sc * __uint_as_float(r0[8 * q4 + 5])),
-                      pack_bf16(sc * __uint_as_float(r0[8 * q4 + 6]), sc * __uint_as_float(r0[8 * q4 + 7]))};
-          st_swizzled_row_piece(stage, row, q4, pk);
-          uint4 pk1 = {pack_bf16(sc * __uint_as_float(r1[8 * q4 + 0]), sc * __uint_as_float(r1[8 * q4 + 1])),
-                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 2]), sc * __uint_as_float(r1[8 * q4 + 3])),
-                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 4]), sc * __uint_as_float(r1[8 * q4 + 5])),
-                       pack_bf16(sc * __uint_as_float(r1[8 * q4 + 6]), sc * __uint_as_float(r1[8 * q4 + 7]))};
-          st_swizzled_row_piece(stage, row, 4 + q4, pk1);
-        }
         fence_proxy_async_smem();
         named_bar_sync(1, 256);
         if (p.dbias != nullptr) {
-          // column sums of the two bf16 tiles just staged (the values as stored): thread = (tile, 8 rows, 8-column chunk),
-          // 16-byte loads, the four row groups of a warp combined with shuffles, one atomic per column and warp
+          // column sums of the bf16 tiles just staged (the values as stored), both key tiles together: thread = (dV | dK, 8 rows,
+          // 8-column chunk), 16-byte loads, the four row groups of a warp combined with shuffles, one atomic per column and warp
           const int tile = ctid >> 7, t7 = ctid & 127, ch = t7 & 7, rg = t7 >> 3;
-          const uint8_t* src8 = tile == 0 ? sP : sdS;
           float acc[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+          for (int c = 0; c < (has_b ? 2 : 1); ++c) {
+            const uint8_t* src8 = (tile == 0 ? sP : sdS) + c * kAttTileBytes;
 #pragma unroll
-          for (int r0i = 0; r0i < 8; ++r0i) {
-            const int rr = rg * 8 + r0i;
-            const uint4 q = *reinterpret_cast<const uint4*>(src8 + rr * 128 + ((ch ^ (rr & 7)) << 4));
-            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+            for (int r0i = 0; r0i < 8; ++r0i) {
+              const int rr = rg * 8 + r0i;
+              const uint4 q = *reinterpret_cast<const uint4*>(src8 + rr * 128 + ((ch ^ (rr & 7)) << 4));
+              const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float2 f = __bfloat1622float2(h2[j]);
-              acc[2 * j] += f.x;
-              acc[2 * j + 1] += f.y;
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = __bfloat1622float2(h2[j]);
+                acc[2 * j] += f.x;
+                acc[2 * j + 1] += f.y;
+              }
             }
           }
 #pragma unroll
@@ -963,17 +998,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           }
         }
         if (ctid == 0) {
-          tma_store_4d(&tmDQKV, sP, 0, kv0, 2 * p.H + h, b);    // dV
-          tma_store_4d(&tmDQKV, sdS, 0, kv0, p.H + h, b);       // dK
+          tma_store_4d(&tmDQKV, sP, 0, ja * kAttTile, 2 * p.H + h, b);          // dV
+          tma_store_4d(&tmDQKV, sdS, 0, ja * kAttTile, p.H + h, b);             // dK
+          if (has_b) {
+            tma_store_4d(&tmDQKV, sP + kAttTileBytes, 0, jb * kAttTile, 2 * p.H + h, b);
+            tma_store_4d(&tmDQKV, sdS + kAttTileBytes, 0, jb * kAttTile, p.H + h, b);
+          }
           tma_store_commit();                                    // not waited for here: the next item overlaps the drain
         }
       }
-      g0 += n_it;
+      gq0 += n_q;
       if (dbg_on) t_epi += clock64() - t_e0;
     }
     if (dbg_on) {
       long long* d = p.dbg + (size_t)blockIdx.x * 8;
-      d[0] = clock64() - t_k0; d[1] = t_loop; d[2] = t_epi; d[3] = t_first; d[4] = t_wait_tail; d[5] = g0; d[6] = wi;
+      d[0] = clock64() - t_k0; d[1] = t_loop; d[2] = t_epi; d[3] = t_first; d[4] = t_wait_tail; d[5] = gu; d[6] = wi;
     }
     if (lane == 0) tma_store_wait<0>();        // every warp issued dQ reduces of its own (warp 2 also the dK / dV stores)
   }
@@ -1088,7 +1127,7 @@ DFB_API int dfb_attn_bwd(const void* qkv, const void* out, const void* d_out, co
   // Short sequences (few query tiles per item): one persistent CTA per SM walks a strided list of items, which removes the
   // per-CTA launch / allocation / store-drain cost (0.382 vs 0.401 ms at T = 1024).  Long sequences: one CTA per item, so the
   // hardware scheduler balances the very unequal items (0.676 vs 0.734 ms at T = 8192 with the static list).
-  long grid = (long)p.n_qt * B * H;
+  long grid = (long)((p.n_qt + 1) / 2) * B * H;               // work items: pairs of key tiles
   if (p.n_qt <= 16 && grid > num_sms()) grid = num_sms();
   attn_bwd_kernel<<<(unsigned)grid, kBwdThreads, kBwdSmem, stream>>>(tmQKV, tmDO, tmDQKV, tmDQ, p);
   const int cthreads = vpr * (256 / vpr);                      // whole rows per block iteration
