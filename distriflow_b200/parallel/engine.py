@@ -31,6 +31,10 @@ _OPT = {"sgd": 0, "momentum": 1, "adam": 2, "none": 3}
 _ALIGN = 64          # elements; every parameter starts 128-byte aligned inside its bucket (TMA needs 16)
 
 
+class PeerLostError(RuntimeError):
+    """A cross-GPU wait inside a kernel timed out: the named rank is down or hopelessly late."""
+
+
 class Bucket:
     def __init__(self, index: int):
         self.index = index
@@ -446,8 +450,17 @@ class DataParallelEngine:
         b.param_buf.copy_(b.master)
 
     # ------------------------------------------------------------------------------------ state
+    def check_health(self) -> None:
+        """Raise `PeerLostError` if a kernel of this rank ever gave up waiting for a peer (`barrierTimeoutSeconds`): the steps
+        since then averaged incomplete gradients.  Called wherever weights leave the engine (checkpoints, `full_precision_weights`)."""
+        lost = self.peer_failure()
+        if lost is not None:
+            raise PeerLostError(f"rank {self.rank}: rank {lost[0]} never reached barrier generation {lost[1]} within "
+                                f"{self.cfg['barrierTimeoutSeconds']} s; weights since then are not trustworthy")
+
     def full_precision_weights(self) -> List[torch.Tensor]:
         """fp32 master weights of every parameter, in `model.parameters()` order (gathers the shards)."""
+        self.check_health()
         out: Dict[int, torch.Tensor] = {}
         for b in self.buckets:
             if self.backend == "p2p" and self.world > 1:
@@ -498,6 +511,7 @@ class DataParallelEngine:
         """Everything a resumed run needs: version (= optimizer step count), fp32 masters and optimizer moments per
         parameter.  Shards are gathered, so the result does not depend on the world size it was saved at (collective: call
         on every rank).  The reference checkpoints weights only (server/models.ts:132-138); optimizer state is new."""
+        self.check_health()
         names = {id(p): n for n, p in self.model.named_parameters()}
         params: Dict[str, Dict[str, torch.Tensor]] = {}
         for b in self.buckets:

@@ -238,9 +238,11 @@ def test_gather_batch_from_ticket():
     assert t.batch == 2 and torch.equal(out, data[8:12])
 
 
-@pytest.mark.parametrize("R", [2, 8])
-def test_allgather_fused_gemm_emulated(R):
-    """Each emulated rank holds only its own slice of W; the fused GEMM must pull the rest and produce x @ W."""
+@pytest.mark.parametrize("R,pad_after", [(2, 0), (4, 0), (8, 0), (4, 5), (8, 3)])
+def test_allgather_fused_gemm_emulated(R, pad_after):
+    """Each emulated rank holds only its own slice of W; the fused GEMM must pull the rest and produce x @ W.
+    `pad_after` > 0: W is a small part of a large bucket (the one-bucket layout), so it lies inside a few shards only and
+    some ranks own none of it."""
     from distriflow_b200.ops.dense import _init_sigs, ag_gemm
     from distriflow_b200.parallel.ag_fusion import build_plan
     from distriflow_b200.parallel.symm import SymmetricHeap
@@ -249,7 +251,7 @@ def test_allgather_fused_gemm_emulated(R):
     M, K, N = 1024, 768, 2304
     w_off = 64 * 5                                    # W does not start at the bucket start
     numel = K * N
-    total = ((w_off + numel + 64 * 3 + R * 64 - 1) // (R * 64)) * (R * 64)
+    total = ((w_off + numel * (1 + pad_after) + 64 * 3 + R * 64 - 1) // (R * 64)) * (R * 64)
     shard = total // R
     heaps = SymmetricHeap.emulated(R, total * 2 + 65536)
     offs = [h.alloc(total * 2) for h in heaps][0]
@@ -267,7 +269,7 @@ def test_allgather_fused_gemm_emulated(R):
         bases = [hh.base + offs for hh in heaps]
         plan = build_plan(K, N, 2, w_off, shard, r, R, bases, dev())
         w_local = h.view(offs, (total,), torch.bfloat16)[w_off:w_off + numel].view(K, N)
-        assert plan.num_pieces > 0 and plan.remote_bytes > 0
+        assert plan.remote_bytes > 0 or (r * shard <= w_off and w_off + numel <= (r + 1) * shard)
         y = ag_gemm(x, w_local, plan, bias, "relu")
         torch.cuda.synchronize()
         assert torch.equal(w_local, W), "gathered weights differ"

@@ -49,7 +49,8 @@ def _sync_worker(rank, world, port, out, variants=("p2p", "nccl", "p2p-graph")):
             torch.cuda.synchronize()
             masters = eng.full_precision_weights()
             live = [p for p in model.parameters() if p.requires_grad]
-            res["working_equals_master"] = all(torch.equal(p.data, m.to(p.dtype)) for p, m in zip(live, masters))
+            res["working_equals_master"] = res.get("working_equals_master", True) and \
+                all(torch.equal(p.data, m.to(p.dtype)) for p, m in zip(live, masters))       # every p2p variant, not the last one
             res["fused"] = getattr(model.first_dense_kernel(), "_dfb_ag", None) is not None
         w = torch.cat([t.reshape(-1) for t in eng.full_precision_weights()])
         res[backend] = (losses, w.cpu())
@@ -101,11 +102,14 @@ def test_sync_engine_bucket_sizes_and_barrier_modes(tmp_path):
     res = torch.load(out)
     ln, wn = res["nccl"]
     moved = float((wn - res["w_init"]).norm())
+    dist_to_nccl = {v: round(float((res[v][1] - wn).norm()) / moved, 3) for v in variants[1:]}
+    print("distance to the NCCL arm / distance moved:", dist_to_nccl)
     for v in variants[1:]:
         lv, wv = res[v]
         assert res[v + "_same"], f"{v}: replicas diverged"
         assert max(abs(a - b) for a, b in zip(lv, ln)) < 5e-2, (v, lv, ln)
-        assert float((wv - wn).norm()) <= 0.2 * moved, (v, float((wv - wn).norm()), moved)
+        # bf16 + Adam turns rounding noise into +-lr steps; 6 steps from the same start stay within a fraction of the way moved
+        assert float((wv - wn).norm()) <= 0.2 * moved, (v, dist_to_nccl)
     assert res["working_equals_master"]
 
 
