@@ -21,7 +21,7 @@ def stock_ops():
     """Route distriflow_b200.ops through PyTorch library kernels (baseline arm only)."""
     from distriflow_b200 import ops
     names = ("linear", "conv2d_nhwc", "maxpool2d_nhwc", "softmax_cross_entropy", "batch_norm_nhwc", "mlp", "layer_norm",
-             "add_layer_norm", "causal_self_attention")
+             "add_layer_norm", "causal_self_attention", "embedding")
     saved = tuple(getattr(ops, n) for n in names)
     from distriflow_b200.ops.norm import batch_norm_reference
 
@@ -70,7 +70,10 @@ def stock_ops():
         q, k, v = qkv.view(B, T, 3, n_head, D).permute(2, 0, 3, 1, 4)
         return F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, T, n_head * D)
 
-    for n, f in zip(names, (linear, conv, pool, ce, bn, mlp, layer_norm, add_layer_norm, attention)):
+    def embedding(idx, table):
+        return F.embedding(idx, table)
+
+    for n, f in zip(names, (linear, conv, pool, ce, bn, mlp, layer_norm, add_layer_norm, attention, embedding)):
         setattr(ops, n, f)
     try:
         yield

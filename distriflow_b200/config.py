@@ -82,6 +82,7 @@ DEFAULT_ENGINE_CONFIG: Dict[str, Any] = {
     "nvls": False,                # gradients reduced and weights broadcast inside the NVSwitch (multicast heap; bf16 only)
     "cudaGraph": False,           # capture the whole step (forward, backward, bucket kernels) into a CUDA graph after warm-up
     "trace": False,               # CUDA-event phase timers + NVTX ranges (forward / backward / collective tail); eager steps only
+    "deterministic": False,       # True: reproducible embedding gradient (sorted reduction instead of in-place vector reductions)
     "barrierTimeoutSeconds": 20.0,  # bound of every in-kernel wait for a peer GPU; a waiter that gives up records the silent rank
     "watchdogSeconds": 0.0,       # > 0: host thread reports a rank whose device-written step counter stops advancing
     "reserveSMs": 0,              # SMs the GEMMs leave free during backward (0: rely on co-residency)

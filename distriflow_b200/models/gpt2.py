@@ -13,6 +13,8 @@ import math
 from dataclasses import dataclass
 from typing import Optional
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -70,7 +72,13 @@ class GPT2(nn.Module):
         self.wpe = nn.Parameter(torch.empty(c.n_positions, c.n_embd))
         nn.init.normal_(self.wte, std=0.02)
         nn.init.normal_(self.wpe, std=0.02)
-        self.wte._dfb_shared = True          # used by the embedding gather AND the LM head: autograd accumulates
+        # used by the embedding gather AND the LM head.  Under an engine both gradients go straight into the bucket slice: the
+        # head's weight-gradient GEMM writes it, the embedding backward adds its token rows on top (two ready() calls).
+        # Without an engine (no sink) plain autograd accumulates the two dense gradients.
+        if os.environ.get("DFB_EMBEDDING_SCATTER", "1") == "1":
+            self.wte._dfb_grad_parts = 2
+        else:                                # A/B: dense embedding gradient, accumulated by autograd, copied by the hook
+            self.wte._dfb_shared = True
         self.h = nn.ModuleList([Block(c, i) for i in range(c.n_layer)])
         self.ln_f = L.LayerNorm(c.n_embd, name="ln_f")
         self.input_shape = [c.n_positions]
@@ -87,7 +95,7 @@ class GPT2(nn.Module):
     def forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor] = None):
         B, T = idx.shape
         pos = torch.arange(T, device=idx.device)
-        x = F.embedding(idx, self.wte) + self.wpe[pos]
+        x = ops.embedding(idx, self.wte) + self.wpe[pos]
         h = self.h[0].ln_1(x)
         for i, blk in enumerate(self.h):
             x, m = blk(x, h)

@@ -48,6 +48,15 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     return _act_cpu(y, activation)
 
 
+def embedding(idx: torch.Tensor, table: torch.Tensor) -> torch.Tensor:
+    """`table[idx]`.  Under an engine (the table has a gradient sink in a bucket) the backward pass adds the token rows
+    straight into that sink with vector reductions instead of building a dense `[V, D]` gradient."""
+    if table.is_cuda and getattr(table, "_dfb_grad_sink", None) is not None and torch.is_grad_enabled() and table.requires_grad:
+        from .embed import embedding_cuda
+        return embedding_cuda(idx, table)
+    return F.embedding(idx, table)
+
+
 def mlp(x: torch.Tensor, w1: torch.Tensor, b1: Optional[torch.Tensor], w2: torch.Tensor, b2: Optional[torch.Tensor]) -> torch.Tensor:
     """Transformer feed-forward block `gelu(x @ w1 + b1) @ w2 + b2` (tanh GELU) with the activation fused into the GEMM
     epilogues on CUDA (forward: dual output; backward: gelu' applied in the dgrad epilogue)."""

@@ -273,6 +273,58 @@ DFB_API int dfb_maxpool_nhwc_bwd(const void* x, const void* dy, void* dx, int N,
 
 // label_kind: 0 = int64 indices, 1 = int32 indices, 2 = dense rows of the prediction dtype.
 // Accumulates into slot[0] (matches) and slot[1] (rows); the caller zeroes or rotates ring slots.
+// ---------------------------------------------------------------------------------------------- embedding backward
+// table_grad[idx[t], :] += dy[t, :] for every token t, added IN PLACE with vector reductions (`red.global.add.v4.bf16x2`,
+// 16 bytes per operation) to a gradient buffer that already holds another contribution: the tied LM head's weight gradient
+// is written first into the same bucket slice, the token embedding's gradient lands on top of it.  No dense [V, D]
+// temporary, no sort (PyTorch's embedding_dense_backward + accumulate + copy into the bucket cost 0.6 ms of the GPT-2 step
+// and moved 0.5 GB).  Repeated tokens add in an arbitrary order: the sum is rounded per addition in the table's dtype.
+// One warp per token row.  Reference call site: the Flatten/Dense input of /root/reference/experiment/mnist/model.json has
+// no embedding; GPT-2 (BASELINE.json config 5) does.
+__device__ __forceinline__ void red_add_v4_bf16x2(void* p, uint4 v) {
+  asm volatile("red.relaxed.gpu.global.add.noftz.v4.bf16x2 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_v4_f32(float* p, float4 v) {
+  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_bwd_scatter_kernel(const T* __restrict__ dy, const long long* __restrict__ idx,
+                                                                    T* __restrict__ table_grad, long n_tok, int D, long V) {
+  const int lane = threadIdx.x & 31;
+  const long warp = (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), n_warps = (long)gridDim.x * (blockDim.x >> 5);
+  constexpr int VN = 16 / (int)sizeof(T);
+  for (long t = warp; t < n_tok; t += n_warps) {
+    const long row = idx[t];
+    if (row < 0 || row >= V) continue;
+    const T* src = dy + t * D;
+    T* dst = table_grad + row * D;
+    for (int c = lane * VN; c < D; c += 32 * VN) {
+      if constexpr (sizeof(T) == 2) red_add_v4_bf16x2(dst + c, *reinterpret_cast<const uint4*>(src + c));
+      else red_add_v4_f32(reinterpret_cast<float*>(dst + c), *reinterpret_cast<const float4*>(src + c));
+    }
+  }
+}
+
+// D a multiple of 8 (bf16) / 4 (fp32); dy rows contiguous (pitch D); idx int64.
+DFB_API int dfb_embedding_bwd_scatter(const void* dy, const long long* idx, void* table_grad, long n_tok, int D, long V, int dtype,
+                                      cudaStream_t stream) {
+  DFB_REQUIRE(dtype == DT_BF16 || dtype == DT_F32, "embedding_bwd: dtype");
+  DFB_REQUIRE(n_tok > 0 && D > 0 && D % (dtype == DT_BF16 ? 8 : 4) == 0, "embedding_bwd: D=%d must be a multiple of %d", D,
+              dtype == DT_BF16 ? 8 : 4);
+  DFB_REQUIRE(((uintptr_t)dy % 16) == 0 && ((uintptr_t)table_grad % 16) == 0, "embedding_bwd: 16-byte alignment");
+  long blocks = (n_tok + 7) / 8;
+  if (blocks > num_sms() * 16L) blocks = num_sms() * 16L;
+  if (dtype == DT_BF16)
+    embedding_bwd_scatter_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, stream>>>((const __nv_bfloat16*)dy, idx, (__nv_bfloat16*)table_grad,
+                                                                                    n_tok, D, V);
+  else
+    embedding_bwd_scatter_kernel<float><<<(unsigned)blocks, 256, 0, stream>>>((const float*)dy, idx, (float*)table_grad, n_tok, D, V);
+  DFB_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 DFB_API int dfb_accuracy(const void* pred, const void* labels, int label_kind, float* slot, int rows, int C, long ldp, long ldl,
                          int dtype, cudaStream_t stream) {
   DFB_REQUIRE(rows > 0 && C > 0, "accuracy: empty");

@@ -276,6 +276,8 @@ class _LinearFn(torch.autograd.Function):
             if sink is not None:
                 gemm(args["a"], args["b"], a_mn=True, b_mn=True, M=args["M"], N=args["N"], K=M,
                      out=sink.view(args["M"], args["N"]))
+                if getattr(weight, "_dfb_grad_parts", 1) > 1:   # tied weight: another producer adds on top of this (ops/embed.py)
+                    weight._dfb_sink_filled = True
                 weight._dfb_grad_ready()
             else:
                 dw = gemm(args["a"], args["b"], a_mn=True, b_mn=True, M=args["M"], N=args["N"], K=M, out_dtype=weight.dtype)

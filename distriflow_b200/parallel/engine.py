@@ -87,6 +87,8 @@ class DataParallelEngine:
         self.versionCallbacks: List[Callable[[int, int], None]] = []
         self._build_buckets(heap)
         self._install_hooks()
+        from ..ops import embed as _embed                  # process-wide, like the closing-barrier switch of the bucket kernels
+        _embed.DETERMINISTIC = bool(self.cfg["deterministic"]) or _embed.DETERMINISTIC_ENV
         if self.cfg["fuseAllGather"]:
             first = getattr(model, "first_dense_kernel", None)
             w = first() if callable(first) else None
@@ -189,14 +191,16 @@ class DataParallelEngine:
                 sink = b.grad_buf[off:off + p.numel()]
                 if not getattr(p, "_dfb_shared", False):
                     p._dfb_grad_sink = sink                    # ops write the weight gradient here and call ready()
-                p._dfb_grad_ready = (lambda bb=b: self._param_ready(bb))
+                p._dfb_grad_ready = (lambda bb=b, pp=p: self._param_ready(bb, pp))
 
                 def hook(param, sink=sink, bb=b):              # parameters whose gradient comes from plain autograd
                     if param.grad is None:                     # autograd fires the hook even for an undefined gradient:
                         return                                 # that parameter went through the sink path already
                     sink.copy_(param.grad.reshape(-1))
                     param.grad = None
-                    self._param_ready(bb)
+                    # a tied weight (`_dfb_grad_parts` producers) whose gradients were accumulated by autograd reports them all
+                    for _ in range(max(1, int(getattr(param, "_dfb_grad_parts", 1)) - int(getattr(param, "_dfb_reported", 0)))):
+                        self._param_ready(bb, param)
 
                 p.register_post_accumulate_grad_hook(hook)
 
@@ -219,7 +223,9 @@ class DataParallelEngine:
     def on_new_version(self, cb: Callable[[int, int], None]) -> None:
         self.versionCallbacks.append(cb)
 
-    def _param_ready(self, b: Bucket) -> None:
+    def _param_ready(self, b: Bucket, p: Optional[nn.Parameter] = None) -> None:
+        if p is not None and getattr(p, "_dfb_grad_parts", 1) > 1:
+            p._dfb_reported = int(getattr(p, "_dfb_reported", 0)) + 1
         b.pending -= 1
         if self._accumulating:                                 # micro-batch of an unfinished version: nothing is launched
             return
@@ -237,7 +243,10 @@ class DataParallelEngine:
 
     def zero_pending(self) -> None:
         for b in self.buckets:
-            b.pending = len(b.params)
+            b.pending = sum(int(getattr(p, "_dfb_grad_parts", 1)) for p in b.params)   # a tied weight reports once per producer
+            for p in b.params:
+                if getattr(p, "_dfb_grad_parts", 1) > 1:
+                    p._dfb_reported = 0
             b.launched = False
 
     def step(self, *batch: Any) -> torch.Tensor:

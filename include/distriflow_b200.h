@@ -101,6 +101,10 @@ int dfb_maxpool_nhwc(const void* x, void* y, int N, int H, int W, int C, int OH,
 int dfb_maxpool_nhwc_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, int OH, int OW, int kh, int kw,
                          int sh, int sw, int pt, int pl, int dtype, void* stream);
 /* metrics into a device ring slot (replaces model.evaluate(...).dataSync(): models.ts:106-115) */
+/* table_grad[idx[t], :] += dy[t, :] in place (vector reductions): the token embedding's gradient added on top of the tied
+ * LM head's weight gradient inside the gradient bucket.  idx int64; D a multiple of 8 (bf16) / 4 (fp32). */
+int dfb_embedding_bwd_scatter(const void* dy, const long long* idx, void* table_grad, long n_tok, int D, long V, int dtype,
+                              void* stream);
 int dfb_accuracy(const void* pred, const void* labels, int label_kind, float* slot, int rows, int C, long ldp, long ldl,
                  int dtype, void* stream);
 

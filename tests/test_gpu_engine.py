@@ -217,7 +217,8 @@ def test_engine_state_resume_on_gpu(tmp_path, graph):
     g = torch.Generator(device="cuda").manual_seed(5)
     idx = torch.randint(0, cfg.vocab_size, (4, 65), device=dev(), generator=g)
     x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
-    conf = {"optimizer": "adam", "learningRate": 1e-3, "bucketBytes": 1 << 18, "cudaGraph": graph}
+    # `deterministic`: the resumed run must reproduce the original one, so the embedding gradient takes the sorted reduction
+    conf = {"optimizer": "adam", "learningRate": 1e-3, "bucketBytes": 1 << 18, "cudaGraph": graph, "deterministic": True}
     torch.manual_seed(0)
     eng = DataParallelEngine(GPT2(cfg).to(dev()), gpt2_loss, conf, device=dev())
     for _ in range(5):

@@ -494,6 +494,35 @@ def test_dgelu_gemm_emits_the_bias_gradient_from_its_epilogue(M, N, K):
     assert rel_err(out, (dy.float() @ w2.float().t()) * dgelu) < 2e-2
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_embedding_backward_scatters_into_a_filled_gradient_slice(dtype, monkeypatch):
+    """The token embedding's gradient is added IN PLACE on top of what the slice already holds (the tied LM head's weight
+    gradient), with repeated tokens; and a parameter without a sink takes the plain autograd path."""
+    from distriflow_b200 import ops
+    from distriflow_b200.ops import embed
+    monkeypatch.setattr(embed, "DETERMINISTIC", False)
+    torch.manual_seed(0)
+    V, D, n = 300, 64, 4096                                   # every row is hit ~14 times
+    table = torch.nn.Parameter(torch.randn(V, D, device=dev()).to(dtype))
+    idx = torch.randint(0, V, (8, n // 8), device=dev())
+    dy = torch.randn(8, n // 8, D, device=dev()).to(dtype)
+    head = torch.randn(V, D, device=dev()).to(dtype)
+    sink = head.clone().reshape(-1)
+    calls = []
+    table._dfb_grad_sink, table._dfb_grad_ready, table._dfb_sink_filled = sink, (lambda: calls.append(1)), True
+    ops.embedding(idx, table).backward(dy)
+    ref = head.float().index_add(0, idx.reshape(-1), dy.reshape(-1, D).float())
+    assert calls == [1] and table.grad is None and table._dfb_sink_filled is False
+    assert rel_err(sink.view(V, D), ref) < (2e-2 if dtype == torch.bfloat16 else 1e-5)
+    sink.fill_(7.0)                                           # nobody wrote the slice first: it is cleared, not added to
+    ops.embedding(idx, table).backward(dy)
+    ref0 = torch.zeros(V, D, device=dev()).index_add(0, idx.reshape(-1), dy.reshape(-1, D).float())
+    assert rel_err(sink.view(V, D), ref0) < (2e-2 if dtype == torch.bfloat16 else 1e-5)
+    plain = torch.nn.Parameter(table.detach().clone())
+    ops.embedding(idx, plain).backward(dy)
+    assert rel_err(plain.grad, ref0) < (2e-2 if dtype == torch.bfloat16 else 1e-5)
+
+
 def test_thin_channel_conv_stem_im2col_path():
     from distriflow_b200 import ops
     torch.manual_seed(0)

@@ -12,6 +12,11 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 WORLD = int(os.environ.get("DFB_TEST_WORLD", "2"))        # DFB_TEST_WORLD=8 runs the same tests on a whole box
 
 
+# The arms of these tests are compared with each other: keep the one order-dependent kernel of the GPT-2 step (the in-place
+# embedding-gradient scatter) out of the comparison; spawned workers inherit the variable.
+os.environ.setdefault("DFB_EMBEDDING_DETERMINISTIC", "1")
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
