@@ -137,3 +137,33 @@ def test_set_learning_rate_takes_effect_on_cpu():
     eng.set_learning_rate(0.1)
     eng.step(*_batch(2))
     assert not all(torch.equal(a, b) for a, b in zip(w0, eng.full_precision_weights()))
+
+
+def test_tied_weight_reports_once_per_producer_and_matches_plain_autograd():
+    """GPT-2's `wte` feeds the embedding gather AND the LM head (`_dfb_grad_parts = 2`).  On the plain-autograd path both
+    gradients are accumulated by autograd and delivered by ONE hook call, which must report both parts: the bucket is
+    launched, and the step equals a plain PyTorch step on the same weights."""
+    from distriflow_b200.models.gpt2 import GPT2, GPT2Config, gpt2_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    cfg = GPT2Config.tiny()
+    torch.manual_seed(0)
+    model = GPT2(cfg)
+    assert getattr(model.wte, "_dfb_grad_parts", 1) == 2
+    torch.manual_seed(0)
+    ref = GPT2(cfg)
+    opt = torch.optim.SGD([p for p in ref.parameters() if p.requires_grad], lr=0.1)
+    eng = DataParallelEngine(model, gpt2_loss, {"optimizer": "sgd", "learningRate": 0.1, "dtype": "fp32", "gradDtype": "fp32"},
+                             device=torch.device("cpu"))
+    g = torch.Generator().manual_seed(1)
+    idx = torch.randint(0, cfg.vocab_size, (2, 33), generator=g)
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    for _ in range(3):
+        l_eng = float(eng.step(x, y))
+        assert all(b.pending == 0 for b in eng.buckets)
+        opt.zero_grad()
+        l_ref = gpt2_loss(ref, x, y)
+        l_ref.backward()
+        opt.step()
+        assert abs(l_eng - float(l_ref)) < 1e-5
+    for a, b in zip(eng.full_precision_weights(), [p for p in ref.parameters() if p.requires_grad]):
+        assert torch.allclose(a, b.detach(), atol=1e-6)
