@@ -454,6 +454,8 @@ __device__ __forceinline__ float ldg_pinned(const float* ptr) {
   return v;
 }
 
+constexpr bool kBwdPolyExp = true;      // half of the backward's exponentials on the FMA pipes (exp2_poly_f32x2)
+
 struct AttnBwdParams {
   const float* lse;      // [B, H, T]
   const float* delta;    // [B, H, T]
@@ -489,6 +491,28 @@ __device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
   return r;
 }
 
+// 2^x for a pair of exponents on the FMA pipes (Cody-Waite: x = n + f with n = round(x), f in [-0.5, 0.5]; 2^f by a degree-4
+// polynomial, relative error 4e-5, far below the bf16 rounding of P; 2^n by adding n to the exponent field).  Every other pair
+// of a row takes this path, so the MUFU unit (16 lanes per SM: 8 cycles per warp instruction) sees half of the
+// exponentials: r2 ncu had 18 % of the backward kernel's stall samples on the exp2 line, `mio` throttle (MUFU queue full).
+__device__ __forceinline__ void exp2_poly_f32x2(float x0, float x1, float& r0, float& r1) {
+  x0 = fmaxf(x0, -125.f);
+  x1 = fmaxf(x1, -125.f);
+  const uint64_t magic = pack_f32x2(12582912.f, 12582912.f), nmagic = pack_f32x2(-12582912.f, -12582912.f);
+  const uint64_t x = pack_f32x2(x0, x1);
+  const uint64_t xf = add_f32x2(x, magic);                       // low mantissa bits = round(x)
+  const uint64_t f = add_f32x2(x, mul_f32x2(add_f32x2(xf, nmagic), pack_f32x2(-1.f, -1.f)));   // x - round(x)
+  uint64_t pq = fma_f32x2(f, pack_f32x2(0.009618129f, 0.009618129f), pack_f32x2(0.05550411f, 0.05550411f));
+  pq = fma_f32x2(pq, f, pack_f32x2(0.2402265f, 0.2402265f));
+  pq = fma_f32x2(pq, f, pack_f32x2(0.6931472f, 0.6931472f));
+  pq = fma_f32x2(pq, f, pack_f32x2(1.f, 1.f));
+  float p0, p1, n0, n1;
+  unpack_f32x2(pq, p0, p1);
+  unpack_f32x2(xf, n0, n1);
+  r0 = __int_as_float(__float_as_int(p0) + (__float_as_int(n0) << 23));
+  r1 = __int_as_float(__float_as_int(p1) + (__float_as_int(n1) << 23));
+}
+
 // P and dS for one query row and one half (64 key columns) of the tile, in two passes; each TMEM operand is released as soon
 // as it is in registers and each shared-memory tile is written as late as its previous reader allows:
 //   pass A   [s_full]  S -> registers  (s_cons: S_{i+1} may be issued)   P = exp2(S*c - lse*log2e)  -> sP  [p_free]
@@ -517,7 +541,13 @@ __device__ __forceinline__ void bwd_pass_a(float (&pv)[64], uint32_t tmem_s_lane
     for (int i = 0; i < 64; i += 2) {
       float t0, t1;
       unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), c2, l2), t0, t1);
-      float p0 = exp2f(t0), p1 = exp2f(t1);
+      float p0, p1;
+      if ((i & 2) && kBwdPolyExp) {
+        exp2_poly_f32x2(t0, t1, p0, p1);
+      } else {
+        p0 = exp2f(t0);
+        p1 = exp2f(t1);
+      }
       if (kDiag && col0 + i > row) p0 = 0.f;
       if (kDiag && col0 + i + 1 > row) p1 = 0.f;
       pv[i] = p0;
