@@ -74,6 +74,55 @@ constexpr float kRescaleThreshold = 8.0f;                     // log2 domain
 
 // `mask_from`: first key column (tile-relative) that is masked for query row 0 of the CTA, i.e. column i is masked for
 // `row` when i - mask_from > row - 0  <=>  i + kv0 > row + q0.  kMask = false: nothing is masked (tiles left of the diagonal).
+// Packed fp32 pairs (one issue slot for two lanes of arithmetic; the compute warps are issue-bound, r2 ncu).
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
+// 2^x for a pair of exponents on the FMA pipes (Cody-Waite: x = n + f with n = round(x), f in [-0.5, 0.5]; 2^f by a degree-4
+// polynomial, relative error 4e-5, far below the bf16 rounding of P; 2^n by adding n to the exponent field).  Every other pair
+// of a row takes this path, so the MUFU unit (16 lanes per SM: 8 cycles per warp instruction) sees half of the
+// exponentials: r2 ncu had 18 % of the backward kernel's stall samples on the exp2 line, `mio` throttle (MUFU queue full).
+__device__ __forceinline__ void exp2_poly_f32x2(float x0, float x1, float& r0, float& r1) {
+  x0 = fmaxf(x0, -125.f);
+  x1 = fmaxf(x1, -125.f);
+  const uint64_t magic = pack_f32x2(12582912.f, 12582912.f), nmagic = pack_f32x2(-12582912.f, -12582912.f);
+  const uint64_t x = pack_f32x2(x0, x1);
+  const uint64_t xf = add_f32x2(x, magic);                       // low mantissa bits = round(x)
+  const uint64_t f = add_f32x2(x, mul_f32x2(add_f32x2(xf, nmagic), pack_f32x2(-1.f, -1.f)));   // x - round(x)
+  uint64_t pq = fma_f32x2(f, pack_f32x2(0.009618129f, 0.009618129f), pack_f32x2(0.05550411f, 0.05550411f));
+  pq = fma_f32x2(pq, f, pack_f32x2(0.2402265f, 0.2402265f));
+  pq = fma_f32x2(pq, f, pack_f32x2(0.6931472f, 0.6931472f));
+  pq = fma_f32x2(pq, f, pack_f32x2(1.f, 1.f));
+  float p0, p1, n0, n1;
+  unpack_f32x2(pq, p0, p1);
+  unpack_f32x2(xf, n0, n1);
+  r0 = __int_as_float(__float_as_int(p0) + (__float_as_int(n0) << 23));
+  r1 = __int_as_float(__float_as_int(p1) + (__float_as_int(n1) << 23));
+}
+
+// Forward: measured SLOWER with half of the exponentials on the FMA pipes (0.125 vs 0.117 ms at T = 1024, 621 vs 684 TFLOP/s at
+// T = 8192, r2): its softmax warps are bound by instruction issue, not by the MUFU queue.  Off.
+constexpr bool kFwdPolyExp = false;
+
 template <bool kMask>
 __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t tmem_o_lane, uint8_t* sPslot, int row, int col_shift,
                                                  float c, bool first, float& m_ref, float& l) {
@@ -123,7 +172,15 @@ __device__ __forceinline__ void fwd_softmax_tile(uint32_t tmem_s_lane, uint32_t 
   for (int q8 = 0; q8 < kKvTile / 8; ++q8) {
     float e[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) e[i] = exp2f(fmaf(__uint_as_float(s[8 * q8 + i]), c, -mc));
+    for (int i = 0; i < 8; i += 2) {
+      const float t0 = fmaf(__uint_as_float(s[8 * q8 + i]), c, -mc), t1 = fmaf(__uint_as_float(s[8 * q8 + i + 1]), c, -mc);
+      if ((i & 2) && kFwdPolyExp) {
+        exp2_poly_f32x2(t0, t1, e[i], e[i + 1]);               // a masked score (-inf) comes out as 2^-125: nothing in bf16 sums
+      } else {
+        e[i] = exp2f(t0);
+        e[i + 1] = exp2f(t1);
+      }
+    }
     sum0 += e[0] + e[1];
     sum1 += e[2] + e[3];
     sum2 += e[4] + e[5];
@@ -467,51 +524,6 @@ struct AttnBwdParams {
   int* ticket;           // work-item counter of the persistent grid (zero on entry; the convert kernel clears it again)
   long long* dbg;        // nullable: per-CTA cycle counters of compute warp 2 (dfb_attn_bwd_set_debug), 8 words per CTA
 };
-
-// Packed fp32 pairs (one issue slot for two lanes of arithmetic; the compute warps are issue-bound, r2 ncu).
-__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
-  uint64_t r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
-__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-
-// 2^x for a pair of exponents on the FMA pipes (Cody-Waite: x = n + f with n = round(x), f in [-0.5, 0.5]; 2^f by a degree-4
-// polynomial, relative error 4e-5, far below the bf16 rounding of P; 2^n by adding n to the exponent field).  Every other pair
-// of a row takes this path, so the MUFU unit (16 lanes per SM: 8 cycles per warp instruction) sees half of the
-// exponentials: r2 ncu had 18 % of the backward kernel's stall samples on the exp2 line, `mio` throttle (MUFU queue full).
-__device__ __forceinline__ void exp2_poly_f32x2(float x0, float x1, float& r0, float& r1) {
-  x0 = fmaxf(x0, -125.f);
-  x1 = fmaxf(x1, -125.f);
-  const uint64_t magic = pack_f32x2(12582912.f, 12582912.f), nmagic = pack_f32x2(-12582912.f, -12582912.f);
-  const uint64_t x = pack_f32x2(x0, x1);
-  const uint64_t xf = add_f32x2(x, magic);                       // low mantissa bits = round(x)
-  const uint64_t f = add_f32x2(x, mul_f32x2(add_f32x2(xf, nmagic), pack_f32x2(-1.f, -1.f)));   // x - round(x)
-  uint64_t pq = fma_f32x2(f, pack_f32x2(0.009618129f, 0.009618129f), pack_f32x2(0.05550411f, 0.05550411f));
-  pq = fma_f32x2(pq, f, pack_f32x2(0.2402265f, 0.2402265f));
-  pq = fma_f32x2(pq, f, pack_f32x2(0.6931472f, 0.6931472f));
-  pq = fma_f32x2(pq, f, pack_f32x2(1.f, 1.f));
-  float p0, p1, n0, n1;
-  unpack_f32x2(pq, p0, p1);
-  unpack_f32x2(xf, n0, n1);
-  r0 = __int_as_float(__float_as_int(p0) + (__float_as_int(n0) << 23));
-  r1 = __int_as_float(__float_as_int(p1) + (__float_as_int(n1) << 23));
-}
 
 // P and dS for one query row and one half (64 key columns) of the tile, in two passes; each TMEM operand is released as soon
 // as it is in registers and each shared-memory tile is written as late as its previous reader allows:
