@@ -94,7 +94,15 @@ def main(argv: Optional[List[str]] = None) -> int:
     sched = (lambda step: args.lr * min(1.0, (step + 1) / args.warmup_steps)) if args.warmup_steps > 0 else None
     tr = Trainer(eng, x, y, {"batchSize": args.batch, "epochs": args.epochs, "saveDir": args.save_dir,
                              "checkpointEvery": args.checkpoint_every, "logPath": args.log}, lr_schedule=sched)
-    out = tr.fit()
+    from .parallel.engine import PeerLostError
+    try:
+        out = tr.fit()
+    except PeerLostError as e:
+        # restart-based recovery: exit with EX_TEMPFAIL so a supervisor (`torch.distributed.run --max-restarts N`, or the same
+        # command on the surviving GPUs) relaunches; the new run resumes from `<save-dir>/current`, the last version written
+        # BEFORE the loss (Trainer.save refuses to checkpoint after it), at whatever world size it is given
+        print(f"[distriflow_b200] {e}; last good version: {tr.latest()}", file=sys.stderr, flush=True)
+        os._exit(75)
     if args.trace:
         out["phases_ms"] = {k: round(v["mean_ms_max_over_ranks"], 3) for k, v in eng.trace_summary().items()}
     eng.close()

@@ -92,6 +92,12 @@ class Trainer:
         save_dir = self.cfg["saveDir"]
         if not save_dir:
             return None
+        # A step that averaged incomplete gradients (a peer GPU was lost: `PeerLostError`) must never become a resume point:
+        # the last good version stays `current`, a supervisor restarts the job on the surviving ranks and `fit()` resumes
+        # from it (the state is independent of the world size).  Reference: a worker may leave at any time and the lost
+        # batches are re-issued (/root/reference/src/server/dataset.ts:57-60, asynchronousSGD_server.ts:54-57).
+        if hasattr(self.engine, "check_health"):
+            self.engine.check_health()
         version = None
         if self.rank == 0:
             os.makedirs(save_dir, exist_ok=True)

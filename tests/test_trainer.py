@@ -148,3 +148,44 @@ def test_command_line_trainer_on_cpu(tmp_path, capsys):
                      "--optimizer", "momentum", "--save-dir", str(tmp_path / "ck")])
     out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
     assert rc == 0 and out["resumed_from"] == 8 and out["steps_this_call"] == 0
+
+
+def _shrink_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    x, y = _data(64)
+    eng = DataParallelEngine(_net(0), _loss, {**CFG, "backend": "gloo"}, rank=rank, world=world, device=torch.device("cpu"))
+    Trainer(eng, x, y, {"batchSize": 4, "epochs": 2, "saveDir": os.path.join(out_dir, "ck"), "checkpointEvery": 3}).fit(max_steps=6)
+    dist.destroy_process_group()
+
+
+def test_run_started_on_two_ranks_resumes_on_one(tmp_path):
+    """Restart-based recovery after a rank is lost: the checkpoint (fp32 masters, Adam moments, step) does not depend on the
+    world size, so the job continues on the surviving rank with the global batch kept (4 x 2 ranks -> 8 x 1) and ends where
+    an uninterrupted single-rank run ends."""
+    import torch.multiprocessing as mp
+    mp.spawn(_shrink_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    x, y = _data(64)
+    eng = DataParallelEngine(_net(5), _loss, CFG, device=torch.device("cpu"))           # different init: the state replaces it
+    out = Trainer(eng, x, y, {"batchSize": 8, "epochs": 2, "saveDir": os.path.join(str(tmp_path), "ck"), "checkpointEvery": 3}).fit()
+    assert out["resumed_from"] == 6 and out["finished"] and out["steps"] == 16
+    solo = DataParallelEngine(_net(0), _loss, CFG, device=torch.device("cpu"))
+    Trainer(solo, x, y, {"batchSize": 8, "epochs": 2}).fit()
+    assert torch.allclose(_weights(solo), _weights(eng), atol=1e-5)
+
+
+def test_no_checkpoint_is_written_after_a_peer_was_lost(tmp_path):
+    """`Trainer.save` asks the engine first: a step taken after an in-kernel barrier gave up must not become a resume point,
+    the previous version stays `current` and the error reaches the caller (the CLI turns it into exit code 75)."""
+    from distriflow_b200.parallel.engine import PeerLostError
+    x, y = _data(64)
+    eng = DataParallelEngine(_net(0), _loss, CFG, device=torch.device("cpu"))
+    tr = Trainer(eng, x, y, {"batchSize": 8, "epochs": 2, "saveDir": str(tmp_path / "ck"), "checkpointEvery": 4})
+    tr.fit(max_steps=4)
+    good = os.path.realpath(os.path.join(str(tmp_path / "ck"), "current"))
+    eng.peer_failure = lambda _side=False: (1, 42)                       # what a timed-out barrier leaves in the signal pad
+    with pytest.raises(PeerLostError, match="rank 1 never reached barrier generation 42"):
+        tr.fit(max_steps=4)
+    assert os.path.realpath(os.path.join(str(tmp_path / "ck"), "current")) == good
+    assert len([d for d in os.listdir(str(tmp_path / "ck")) if d != "current"]) == 1
