@@ -4,20 +4,19 @@ Not in the reference (it ships only the MNIST models); needed as a named workloa
 layers in the `[in, out]` layout (GPT-2's own Conv1D layout) running the tcgen05 GEMM, GELU and the bias are in
 the GEMM path, the tied LM head runs the same kernel on the `[vocab, d]` embedding table (K-major B operand), the
 loss is the fused softmax-CE kernel writing the logit gradient in place, causal attention (forward and backward) is the
-tcgen05 kernel of `ops/csrc/attention_sm100.cu` on the packed QKV tensor, LayerNorm + residual adds are fused kernels; only
-the embedding gather stays on a PyTorch op.
+tcgen05 kernel of `ops/csrc/attention_sm100.cu` on the packed QKV tensor, LayerNorm + residual adds are fused kernels; the
+tied table's gradient is built in place in the gradient bucket (LM-head weight-gradient GEMM, then the token rows added by
+`ops/embed.py`); only the forward embedding gather and the position add stay on PyTorch ops.
 """
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Optional
 
-import os
-
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from .. import ops
 from . import layers as L
