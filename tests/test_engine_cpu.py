@@ -167,3 +167,19 @@ def test_tied_weight_reports_once_per_producer_and_matches_plain_autograd():
         assert abs(l_eng - float(l_ref)) < 1e-5
     for a, b in zip(eng.full_precision_weights(), [p for p in ref.parameters() if p.requires_grad]):
         assert torch.allclose(a, b.detach(), atol=1e-6)
+
+
+def test_deterministic_key_switches_the_embedding_gradient_path_per_engine():
+    """`deterministic: True` selects the sorted embedding-gradient reduction process-wide; the next engine built without it
+    switches back (the flag follows the most recently built engine, like the closing-barrier mode of the bucket kernels)."""
+    import torch.nn.functional as F
+    from distriflow_b200.ops import embed
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    net = torch.nn.Linear(4, 3)
+    loss = lambda m, x, y: F.mse_loss(m(x), y)               # noqa: E731
+    DataParallelEngine(net, loss, {"optimizer": "sgd", "learningRate": 0.1, "dtype": "fp32", "gradDtype": "fp32",
+                                   "deterministic": True}, device=torch.device("cpu"))
+    assert embed.DETERMINISTIC is True
+    DataParallelEngine(torch.nn.Linear(4, 3), loss, {"optimizer": "sgd", "learningRate": 0.1, "dtype": "fp32", "gradDtype": "fp32"},
+                       device=torch.device("cpu"))
+    assert embed.DETERMINISTIC is embed.DETERMINISTIC_ENV
