@@ -168,8 +168,9 @@ int dfb_gather_batch(const void* src, void* dst, const unsigned* ticket, long ro
 /* ---- causal self-attention on the packed QKV projection (no counterpart in the reference: its models have no attention;
  * hot path of BASELINE.json config 5).  tcgen05 + TMEM + TMA, head dimension 64, bf16, scale 1/sqrt(D).
  * qkv / dqkv: [B,T,3,H,D]; out / d_out: [B,T,H,D]; lse: [B,H,T] fp32.
- * scratch (dfb_attn_bwd_scratch_bytes): delta [B,H,T] fp32 rounded to 256 B, then the fp32 dQ accumulator [B,T,H,D], which
- * must be zero on entry and is zero again on return. */
+ * scratch (dfb_attn_bwd_scratch_bytes): delta [B,H,T] fp32 rounded to 256 B, then the fp32 dQ accumulator [B,T,H,D] and the
+ * 256-byte work-item counter of the persistent grid; accumulator and counter must be zero on entry and are zero again on
+ * return (allocate the buffer zero-filled once per shape and keep it). */
 int dfb_attn_supported(int B, int T, int H, int D);
 int dfb_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
 int dfb_attn_bwd_set_debug(long long* buf);   /* profiling aid: per-CTA cycle counters of the backward kernel (8 int64 per CTA), NULL = off */
