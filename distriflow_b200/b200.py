@@ -100,10 +100,11 @@ class B200Server:
         for k in config:
             if k not in _CONFIG_KEYS:
                 raise ValueError(f'Unrecognized server config key "{k}"')
-        if mode not in ("sync", "async"):
-            raise ValueError(f'backend "b200" runs modes "sync" and "async", got {mode!r}')
-        if dataset is None:
-            raise ValueError("the b200 back end owns the dataset (DistriServer {model, dataset, workerIDs})")
+        if mode not in ("sync", "async", "federated"):
+            raise ValueError(f'backend "b200" runs modes "sync", "async" and "federated", got {mode!r}')
+        if dataset is None and mode != "federated":
+            raise ValueError("the b200 back end owns the dataset (DistriServer {model, dataset, workerIDs}); only federated "
+                             "workers bring their own data")
         self.mode, self.dataset, self.group = mode, dataset, group
         self.clientHyperparams = client_hyperparams(config.get("clientHyperparams"))
         shp = dict(config.get("serverHyperparams") or {})
@@ -189,7 +190,9 @@ class B200Server:
         if not cuda or next(self.module.parameters()).dtype == torch.float32:
             ecfg.update({"dtype": "fp32", "gradDtype": "fp32"})
         ecfg.update(self.engine_overrides)
-        if self.mode == "sync":
+        if self.mode in ("sync", "federated"):
+            # federated (federated_server.ts:71-116): `minUpdatesPerVersion` uploads are buffered and averaged into one version;
+            # here every rank contributes the same number of them, from its OWN examples (`B200Worker.federated_update`)
             from .parallel.engine import DataParallelEngine
             self.microBatchesPerVersion = max(1, math.ceil(int(self.serverHyperparams["minUpdatesPerVersion"]) / self.world))
             if self.microBatchesPerVersion > 1:
@@ -203,6 +206,15 @@ class B200Server:
             self.engine = AsyncEngine(self.module, loss_fn, {**ecfg, "mode": "async"}, rank=self.rank, world=self.world,
                                       group=self.group, device=self.device)
         ds = self.dataset
+        if ds is None:                                  # federated: no server-owned data, no dispatcher
+            self.batchSize, self.batches, self.epochs = int(self.clientHyperparams["examplesPerUpdate"]), 0, 0
+            if cuda and self.sendMetrics:
+                from .utils.metrics import DeviceMetricRing
+                self.ring = DeviceMetricRing(slots=64, device=self.device)
+            self._lag = []
+            self._last_host_batch = None
+            self.log(f"setup: {self.numClients} federated workers, {self.microBatchesPerVersion} uploads per rank and version")
+            return
         self.batchSize, self.batches, self.epochs = ds.batchSize, ds.batches, ds.epochs
         self.x_all, self.y_all = ds.x.to(self.device), ds.y.to(self.device)
         if cuda:
@@ -337,6 +349,32 @@ class B200Server:
             self._new_version(old)
         return loss
 
+    def federated_upload(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """Federated mode, ONE upload of this rank from the worker's own examples (collective when world > 1: every rank
+        uploads the same number of times per version).  `minUpdatesPerVersion` uploads over all ranks make a version:
+        the earlier ones are summed into `savedGradient` on the GPU, the closing one runs the fused mean + update kernels
+        (/root/reference/src/server/federated_server.ts:71-116; client side federated_client.ts:85-128)."""
+        if self.mode != "federated":
+            raise RuntimeError('federated_upload() needs mode "federated"')
+        if self.engine is None:
+            self.setup()
+        x, y = x.to(self.device), y.to(self.device)
+        closes = self.engine.savedCount + 1 >= self.microBatchesPerVersion
+        old = int(self.engine.version)
+        loss = self.engine.step(x, y) if closes else self.engine.accumulate(x, y)
+        self.numUpdates += 1
+        self.lastLoss = loss
+        metrics = None
+        if self.sendMetrics and self._out is not None:
+            out, yy = self._out
+            lab = yy if yy.dim() == out.dim() - 1 else yy.argmax(-1)
+            metrics = [float(loss), float((out.detach().argmax(-1) == lab).float().mean())]
+        if self.uploadCallbacks:
+            self._fire_upload(None, None, metrics)
+        if closes:
+            self._new_version(old)
+        return loss
+
     def step(self) -> Optional[torch.Tensor]:
         """Uploads until the next model version exists; returns the loss of its last micro-batch (None when done)."""
         if self.engine is None:
@@ -353,6 +391,8 @@ class B200Server:
         if self.engine is None:
             self.setup()
         start = int(self.engine.version)
+        if self.mode == "federated":
+            raise RuntimeError("a federated server has no data of its own: workers call federated_update(x, y)")
         if self.mode == "sync":
             while max_versions is None or int(self.engine.version) - start < max_versions:
                 if self.step() is None:
@@ -391,6 +431,8 @@ class B200Worker:
         if cfg.get("clientId"):
             server.clientId = str(cfg["clientId"])
         self._versions = 0
+        self._fx: Optional[torch.Tensor] = None           # federated mode: examples waiting for `examplesPerUpdate`
+        self._fy: Optional[torch.Tensor] = None
         server.on_new_version(lambda old, new: setattr(self, "_versions", self._versions + 1))
 
     @property
@@ -409,6 +451,30 @@ class B200Worker:
         return self.server.model.version
 
     modelVersion = model_version
+
+    # federated mode: the worker's own examples (federated_client.ts:85-128) ----------------------------------------
+    def federated_update(self, x: torch.Tensor, y: torch.Tensor) -> int:
+        """Add examples; whenever `examplesPerUpdate` have gathered, fit on them and upload (one `federated_upload`).
+        Returns the number of uploads made by this call.  Leftover examples wait for the next call."""
+        self.setup()
+        if x.shape[0] != y.shape[0]:
+            raise ValueError("x and y must have the same number of examples")
+        self._fx = x if self._fx is None else torch.cat([self._fx, x])
+        self._fy = y if self._fy is None else torch.cat([self._fy, y])
+        n = int(self.server.clientHyperparams["examplesPerUpdate"])
+        made = 0
+        while self._fx.shape[0] >= n:
+            self.server.federated_upload(self._fx[:n], self._fy[:n])
+            self._fx, self._fy = self._fx[n:], self._fy[n:]
+            made += 1
+        return made
+
+    federatedUpdate = federated_update
+
+    def num_examples(self) -> int:
+        return 0 if self._fx is None else int(self._fx.shape[0])
+
+    numExamples = num_examples
 
     def num_updates(self) -> int:
         return self.server.numUpdates

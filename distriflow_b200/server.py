@@ -328,7 +328,7 @@ def DistriServer(endpoint: Any, model: Any, dataset: Optional[DistriDataset] = N
                  config: Optional[Dict[str, Any]] = None, mode: str = "async", backend: str = "host", **kw: Any):
     """README facade: `mode` in {'async', 'sync', 'federated'}.  `backend="host"`: the message protocol over `endpoint`
     (in-process hub or TCP).  `backend="b200"`: every rank of the job builds the same server, which is then sharded across
-    the GPU ranks (`b200.B200Server`; `endpoint` is unused and may be None; modes 'sync' and 'async')."""
+    the GPU ranks (`b200.B200Server`; `endpoint` is unused and may be None; 'federated': no dataset, workers bring their examples)."""
     if backend == "b200":
         from .b200 import B200Server
         return B200Server(model, dataset, config, mode=mode, **kw)

@@ -93,3 +93,40 @@ def test_unknown_backend_and_keys_are_rejected():
         DistriServer(None, mnist_mlp(), ds, {"bogus": 1}, mode="sync", backend="b200")
     with pytest.raises(ValueError):
         DistriServer(None, mnist_mlp(), None, {}, mode="sync", backend="b200")
+
+
+def test_federated_mode_workers_bring_their_own_examples():
+    """`mode="federated"` on the engine path (CPU back end here): no server-owned dataset; the worker buffers its own examples
+    until `examplesPerUpdate`, every full buffer is one upload, `minUpdatesPerVersion` uploads make a version
+    (/root/reference/src/client/federated_client.ts:85-128, /root/reference/src/server/federated_server.ts:71-116)."""
+    x, y = synthetic_mnist(40, seed=2)
+    x, y = torch.from_numpy(x) / 255.0, torch.from_numpy(y)
+    torch.manual_seed(0)
+    server = DistriServer(None, mnist_mlp(softmax_output=False), None,
+                          {"modelCompileConfig": {"loss": "softmaxCrossEntropy", "learningRate": 0.05},
+                           "clientHyperparams": {"examplesPerUpdate": 8},
+                           "serverHyperparams": {"minUpdatesPerVersion": 2}, "sendMetrics": True},
+                          mode="federated", backend="b200", device=torch.device("cpu"))
+    worker = DistriWorker(server, backend="b200")
+    versions, uploads = [], []
+    server.on_new_version(lambda old, new: versions.append((old, new)))
+    server.on_upload(lambda m: uploads.append(m))
+    assert worker.federated_update(x[:5], y[:5]) == 0 and worker.num_examples() == 5          # not enough yet
+    assert worker.federated_update(x[5:20], y[5:20]) == 2 and worker.num_examples() == 4     # 20 examples: two uploads, 4 left
+    assert versions == [("0", "1")] and len(uploads) == 2 and uploads[0].metrics is not None
+    assert worker.federated_update(x[20:40], y[20:40]) == 3 and worker.num_examples() == 0
+    assert [v[1] for v in versions] == ["1", "2"] and server.model.savedCount == 1            # the fifth upload waits for a sixth
+    with pytest.raises(RuntimeError):
+        server.run()
+    # a version is the MEAN of its uploads: same result as one step on the 16 examples of the two buffers
+    torch.manual_seed(0)
+    from distriflow_b200.losses import get_loss
+    from distriflow_b200.parallel.engine import DataParallelEngine
+    ref = mnist_mlp(softmax_output=False)
+    ce = get_loss("softmaxCrossEntropy")
+    eng = DataParallelEngine(ref, lambda m, a, b: ce(b, m(a)), {"optimizer": "sgd", "learningRate": 0.05, "dtype": "fp32",
+                                                               "gradDtype": "fp32"}, device=torch.device("cpu"))
+    eng.step(x[:16], y[:16])
+    eng.step(x[16:32], y[16:32])
+    for a, b in zip(server.model.get_vars(), eng.full_precision_weights()):
+        assert torch.allclose(a, b, atol=1e-6)
