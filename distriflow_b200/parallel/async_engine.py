@@ -186,7 +186,9 @@ class AsyncEngine:
         self.grad_flat = torch.zeros(self.state.n, dtype=self.grad_dtype, device=self.device)
         for p, off in zip(self.params, self.offsets):
             p.data = lo.params[off:off + p.numel()].view(p.shape)
-            if not getattr(p, "_dfb_shared", False):
+            # a tied weight (two gradient producers, `_dfb_grad_parts`) keeps the plain path here: autograd accumulates both
+            # parts and the hook below copies the sum (the in-place two-producer protocol is the sync engine's)
+            if not getattr(p, "_dfb_shared", False) and int(getattr(p, "_dfb_grad_parts", 1)) == 1:
                 p._dfb_grad_sink = self.grad_flat[off:off + p.numel()]
             p._dfb_grad_ready = lambda: None
 
