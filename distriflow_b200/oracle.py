@@ -291,10 +291,16 @@ def simulate_sync(model: MlpOracle, x: np.ndarray, y: np.ndarray, *, batch_size:
     return out
 
 
-def timed_cpu_baseline(steps: int = 200, batch_size: int = 32, seed: int = 0) -> Dict[str, float]:
-    """Samples/s of the oracle on this CPU for the MNIST dense config (the 'timed CPU baseline' of BASELINE.md)."""
-    x, y = synthetic_mnist(batch_size * 8, seed=seed)
-    m = MlpOracle(seed=seed)
+def timed_cpu_baseline(steps: int = 200, batch_size: int = 32, seed: int = 0, model: str = "mlp") -> Dict[str, float]:
+    """Samples/s of the oracle on this CPU (the 'timed CPU baseline' of BASELINE.md): `model="mlp"` the MNIST dense config,
+    `model="cnn"` the `model.json` CNN topology (inputs / 255, softmax cross-entropy)."""
+    if model == "cnn":
+        x, y = synthetic_mnist(batch_size * 8, classes=10, seed=seed)
+        x = (x / 255.0).astype(np.float32).reshape(-1, 28, 28, 1)
+        m: Any = CnnOracle(classes=10, seed=seed, loss="softmaxCrossEntropy")
+    else:
+        x, y = synthetic_mnist(batch_size * 8, seed=seed)
+        m = MlpOracle(seed=seed)
     t0 = time.perf_counter()
     for s in range(steps):
         b = s % 8
