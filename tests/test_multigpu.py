@@ -13,7 +13,11 @@ WORLD = int(os.environ.get("DFB_TEST_WORLD", "2"))        # DFB_TEST_WORLD=8 run
 
 
 # The arms of these tests are compared with each other: keep the one order-dependent kernel of the GPT-2 step (the in-place
-# embedding-gradient scatter) out of the comparison; spawned workers inherit the variable.
+# embedding-gradient scatter) out of the comparison; spawned workers inherit the variable.  Set at import, so it also holds
+# for every other test of the same pytest process (collection imports this file first): the engine tests there compare runs
+# with each other too (resume, graph vs eager).  The scatter path itself is covered by
+# test_gpu_kernels.py::test_embedding_backward_scatters_into_a_filled_gradient_slice (which switches it back on), by
+# smoke() and by every bench run (separate processes without the variable).
 os.environ.setdefault("DFB_EMBEDDING_DETERMINISTIC", "1")
 
 
